@@ -1,0 +1,153 @@
+/*
+ * vslam_b200 — C ABI of the B200-native dense RGB-D direct-alignment path.
+ *
+ * Drop-in boundary for phildue/vslam's aligner (paths relative to
+ * /root/reference/src/vslam/src/):
+ *   - odometry/src/AlignmentSE3.h:22-26            AlignmentSE3::align(from, to)
+ *   - odometry/src/direct_image_alignment/SE3Alignment.h:33-39   SE3Alignment(minGradient, solver, loss,
+ *     includePrior); align(from, to); align(vector<from>, to)
+ *   - core/src/Frame.h:35-37, Frame.cpp:215-275     Frame ctor, computePyramid, computeDerivatives, computePcl
+ *   - least_squares/src/{GaussNewton.h:35, Loss.h:54-116, Scaler.h:30-74}  solver / loss / scaler parameters
+ *
+ * Plain pointers and sizes only; every function returns 0 on success or a negative
+ * VSLAMB200_E* code, with a message available from vslamb200_last_error().  There is no CPU
+ * fallback: creation fails if no CUDA device is usable.
+ */
+#ifndef VSLAM_B200_H_
+#define VSLAM_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define VSLAMB200_MAX_LEVELS 8
+#define VSLAMB200_TRACE_STRIDE 64
+
+/* error codes */
+#define VSLAMB200_OK 0
+#define VSLAMB200_EINVAL (-1)      /* bad argument */
+#define VSLAMB200_ECUDA (-2)       /* CUDA runtime failure */
+#define VSLAMB200_ENOFRAME (-3)    /* unknown frame id */
+#define VSLAMB200_EDIMS (-4)       /* image / depth / camera inconsistent (Frame.cpp:150-155) or pyramid sizes disagree */
+
+/* least_squares::Loss family (Loss.h:54-116); NONE == loss nullptr (InverseCompositional.cpp:129) */
+enum { VSLAMB200_LOSS_NONE = 0, VSLAMB200_LOSS_QUADRATIC = 1, VSLAMB200_LOSS_TUKEY = 2, VSLAMB200_LOSS_HUBER = 3, VSLAMB200_LOSS_TDIST = 4 };
+/* least_squares::Scaler family (Scaler.h:30-74) */
+enum { VSLAMB200_SCALER_IDENTITY = 0, VSLAMB200_SCALER_MEDIAN = 1, VSLAMB200_SCALER_MEAN = 2, VSLAMB200_SCALER_TDIST = 3 };
+/* GaussNewton::solve stop reasons per level (GaussNewton.cpp:53-98) */
+enum { VSLAMB200_STOP_MAXITER = 0, VSLAMB200_STOP_CONSTRAINTS = 1, VSLAMB200_STOP_HESSIAN = 2, VSLAMB200_STOP_CHI2 = 3, VSLAMB200_STOP_CONVERGED = 4, VSLAMB200_STOP_NAN = 5 };
+/* host image layouts / depth element types accepted by frame upload */
+enum { VSLAMB200_ROW_MAJOR = 0, VSLAMB200_COL_MAJOR = 1 };   /* COL_MAJOR == Eigen default (core/src/types.h:33-35) */
+enum { VSLAMB200_DEPTH_F32 = 0, VSLAMB200_DEPTH_F64 = 1 };
+
+typedef struct vslamb200_ctx vslamb200_ctx;
+
+/* SE3Alignment ctor arguments + GaussNewton(minStepSize, maxIterations) + loss / scaler parameters */
+typedef struct vslamb200_config
+{
+  double min_gradient;   /* SE3Alignment.h:33; compared squared against dIx^2+dIy^2 (SE3Alignment.cpp:54,89) */
+  int loss_kind;         /* VSLAMB200_LOSS_* */
+  double huber_c;        /* HuberLoss::_c (Loss.h:85) */
+  double loss_v;         /* LossTDistribution nu (Loss.h:103) */
+  int scaler_kind;       /* VSLAMB200_SCALER_* */
+  double scaler_v;       /* ScalerTDistribution nu (Scaler.h:61) */
+  double min_step_size;  /* GaussNewton.cpp:24-29: also min gradient and min chi2 reduction */
+  int max_iterations;    /* GaussNewton.h:35 */
+  int include_prior;     /* MotionPrior (SE3Alignment.cpp:27-52) */
+} vslamb200_config;
+
+/* One alignment: SE3Alignment::align(from, to) (n_from == 1, multi == 0) or the vector overload (multi != 0).
+ * Poses are Sophus SE3d::data() order: quaternion x,y,z,w then translation (P_frame = pose * P_world, Frame.h:94). */
+typedef struct vslamb200_job
+{
+  uint64_t to;                 /* frame id of the target ("to") frame */
+  double to_pose[7];           /* to->pose(): the initial guess */
+  int n_from;                  /* number of keyframes (1 for the single-frame overload) */
+  int multi;                   /* 0: SE3Alignment.cpp:64-105; 1: SE3Alignment.cpp:106-146 */
+  const uint64_t * from;       /* n_from frame ids */
+  const double * from_poses;   /* n_from x 7 */
+} vslamb200_job;
+
+typedef struct vslamb200_result
+{
+  double pose[7];                      /* aligned pose of the "to" frame */
+  double cov[36];                      /* inverse of the last normal-equation matrix (SE3Alignment.cpp:101) */
+  int status;                          /* 0 ok; 1: a level ended before one Gauss-Newton step completed
+                                          (reference: out_of_range / UB) -> input pose, identity covariance */
+  int iters[VSLAMB200_MAX_LEVELS];     /* completed Gauss-Newton steps per level */
+  int stop[VSLAMB200_MAX_LEVELS];      /* VSLAMB200_STOP_* per level */
+} vslamb200_result;
+
+/* counters of the work done since creation / the last reset (bench roofline accounting) */
+typedef struct vslamb200_stats
+{
+  uint64_t kernel_launches;      /* kernels of this library launched */
+  uint64_t pixel_iterations;     /* sum over views, levels, Gauss-Newton iterations of W_l*H_l */
+  uint64_t point_iterations;     /* same, counting only retained interest points */
+  uint64_t gn_iterations;        /* Gauss-Newton iterations over all jobs and levels */
+  uint64_t frames_uploaded;
+  uint64_t h2d_bytes, d2h_bytes;
+  double ms_residual, ms_accumulate, ms_preprocess, ms_lists;  /* filled only when timing is enabled */
+} vslamb200_stats;
+
+const char * vslamb200_last_error(void);
+int vslamb200_version(void);
+
+int vslamb200_create(const vslamb200_config * cfg, int device, vslamb200_ctx ** out);
+void vslamb200_destroy(vslamb200_ctx * ctx);
+int vslamb200_set_config(vslamb200_ctx * ctx, const vslamb200_config * cfg);
+/* run on a caller-owned cudaStream_t (passed as void*); NULL selects the context's own stream */
+int vslamb200_set_stream(vslamb200_ctx * ctx, void * cuda_stream);
+
+/* Frame ctor + computePyramid(n_levels) + computeDerivatives() + computePcl() (node order,
+ * src/ros/nodes/NodeRgbdAlignment.cpp:194-197) for n frames of identical size.  gray / depth are HOST
+ * pointers to n consecutive images (gray_stride / depth_stride = bytes between consecutive frames; 0 =
+ * tightly packed).  cams: n x 4 (fx, fy, cx, cy).  A frame id that already exists is replaced. */
+int vslamb200_frames_upload(
+  vslamb200_ctx * ctx, int n, const uint64_t * ids, int W, int H, const uint8_t * gray, size_t gray_stride,
+  const void * depth, int depth_type, size_t depth_stride, int layout, const double * cams, int n_levels);
+/* same, gray / depth already resident on the context's device (row-major u8 / f32) */
+int vslamb200_frames_upload_device(
+  vslamb200_ctx * ctx, int n, const uint64_t * ids, int W, int H, const uint8_t * d_gray, const float * d_depth,
+  const double * cams, int n_levels);
+int vslamb200_frame_release(vslamb200_ctx * ctx, uint64_t id);
+int vslamb200_frame_release_all(vslamb200_ctx * ctx);
+/* dims4 = intensity W, H, depth W, H at that level (they differ at odd sizes: Frame.cpp:264 vs algorithm.h:93-94) */
+int vslamb200_frame_dims(vslamb200_ctx * ctx, uint64_t id, int level, int * dims4);
+/* copy one pyramid level back (any pointer may be NULL): intensity(l), depth(l), single-frame masked depth,
+ * dIx(l), dIy(l) as row-major planes */
+int vslamb200_frame_download(
+  vslamb200_ctx * ctx, uint64_t id, int level, uint8_t * intensity, float * depth, float * depth_sf, int16_t * dIx,
+  int16_t * dIy);
+
+/* SE3Alignment::align for n_jobs independent alignments in one batch */
+int vslamb200_align(vslamb200_ctx * ctx, const vslamb200_job * jobs, int n_jobs, vslamb200_result * out);
+
+/* Solver::Results history (Solver.h:49-60): when enabled, align() records per job / level / iteration a
+ * 64-double record: 0 valid, 1 nConstraints, 2 chi2, 3 stepSize, 4 scale, 5 offset, 6..11 x, 12..17 b,
+ * 18..53 A (row major), 54..59 dx.  get_trace copies job's records: n_levels * max_iterations * 64 doubles. */
+int vslamb200_set_trace(vslamb200_ctx * ctx, int enable);
+int vslamb200_get_trace(vslamb200_ctx * ctx, int job, double * out);
+
+/* One InverseCompositional::computeNormalEquations (InverseCompositional.cpp:105-154) of keyframe `from`
+ * against `to` on `level` at the relative transform se3 (pose7), without prior.  rcode: W*H int16 plane
+ * (-32768 not an interest point, -32767 interest point not visible, else the residual); ne64: n, chi2,
+ * scale, offset, b[6], A[36] (normalised by n). */
+int vslamb200_evaluate(
+  vslamb200_ctx * ctx, uint64_t from, uint64_t to, int level, const double * se3_pose7, int multi_mask,
+  int16_t * rcode, double * ne64);
+
+int vslamb200_get_stats(vslamb200_ctx * ctx, vslamb200_stats * out);
+int vslamb200_reset_stats(vslamb200_ctx * ctx);
+/* 1: bracket kernel groups with CUDA events so get_stats reports per-kernel milliseconds (adds syncs) */
+int vslamb200_set_timing(vslamb200_ctx * ctx, int enable);
+/* block until everything queued on the context's stream has finished */
+int vslamb200_synchronize(vslamb200_ctx * ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VSLAM_B200_H_ */

@@ -1,0 +1,223 @@
+// Frame preprocessing on the device: ingest, image pyramid, depth pyramid, gradients.
+// Replaces Frame::computePyramid / computeDerivatives (core/src/Frame.cpp:215-275) for a batch of frames.
+#include "common.cuh"
+
+namespace vb
+{
+// ------------------------------------------------------------------------------------------------
+// ingest: staged host bytes -> level-0 planes (row-major u8 / f32).  Handles Eigen column-major input
+// (core/src/types.h:33-35) with a tiled transpose and f64 -> f32 depth narrowing.
+// ------------------------------------------------------------------------------------------------
+template <typename DepthT>
+__global__ void __launch_bounds__(256) ingest_kernel(
+  const uint8_t * __restrict__ gray, const DepthT * __restrict__ depth, int layout, int W, int H,
+  const FrameDev * __restrict__ frames, const int * __restrict__ slots)
+{
+  __shared__ uint8_t tg[32][33];
+  __shared__ float td[32][33];
+  const FrameDev & f = frames[slots[blockIdx.z]];
+  const size_t npx = (size_t)W * H;
+  const uint8_t * g = gray ? gray + blockIdx.z * npx : nullptr;
+  const DepthT * d = depth ? depth + blockIdx.z * npx : nullptr;
+  const int x0 = blockIdx.x * 32, y0 = blockIdx.y * 32;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // 32 x 8
+  if (layout == VSLAMB200_ROW_MAJOR) {
+    for (int j = ty; j < 32; j += 8) {
+      const int x = x0 + tx, y = y0 + j;
+      if (x < W && y < H) {
+        if (g) f.I[0][(size_t)y * W + x] = g[(size_t)y * W + x];
+        if (d) f.Z[0][(size_t)y * W + x] = (float)d[(size_t)y * W + x];
+      }
+    }
+  } else {
+    // column-major source: element (y, x) at x*H + y; read coalesced along y, write coalesced along x
+    for (int j = ty; j < 32; j += 8) {
+      const int x = x0 + j, y = y0 + tx;
+      if (x < W && y < H) {
+        if (g) tg[j][tx] = g[(size_t)x * H + y];
+        if (d) td[j][tx] = (float)d[(size_t)x * H + y];
+      }
+    }
+    __syncthreads();
+    for (int j = ty; j < 32; j += 8) {
+      const int x = x0 + tx, y = y0 + j;
+      if (x < W && y < H) {
+        if (g) f.I[0][(size_t)y * W + x] = tg[tx][j];
+        if (d) f.Z[0][(size_t)y * W + x] = td[tx][j];
+      }
+    }
+  }
+}
+
+void launch_ingest(const uint8_t * stagedGray, const void * stagedDepth, int depthType, int layout, int W, int H,
+                   const FrameDev * frames, const int * slots, int n, cudaStream_t s)
+{
+  dim3 grid((W + 31) / 32, (H + 31) / 32, n);
+  if (depthType == VSLAMB200_DEPTH_F64)
+    ingest_kernel<double><<<grid, 256, 0, s>>>(stagedGray, (const double *)stagedDepth, layout, W, H, frames, slots);
+  else
+    ingest_kernel<float><<<grid, 256, 0, s>>>(stagedGray, (const float *)stagedDepth, layout, W, H, frames, slots);
+}
+
+// ------------------------------------------------------------------------------------------------
+// K1a + K1b: one pyramid step for intensity (cv::pyrDown: 5x5 binomial, reflect-101, (s+128)>>8, even
+// rows/cols; Frame.cpp:264) and depth (3x3 masked median at (2i,2j) with zero border, even-count rule
+// (v[n/2-1]+v[n/2+1])/2, n==2 -> v[0]; Frame.cpp:269-274, algorithm.h:157-184, algorithm.cpp:109-120).
+// The intensity tile is staged through shared memory (each source pixel is read once per block).
+// ------------------------------------------------------------------------------------------------
+constexpr int PT = 32;  // output tile edge of the pyrDown kernel; source tile (2*PT+3)^2
+
+__global__ void __launch_bounds__(256) pyr_down_u8_kernel(
+  const FrameDev * __restrict__ frames, const int * __restrict__ slots, int level, int Wp, int Hp, int W, int H)
+{
+  __shared__ uint8_t src[2 * PT + 3][2 * PT + 4];
+  __shared__ uint16_t hrow[2 * PT + 3][PT];
+  const FrameDev & f = frames[slots[blockIdx.z]];
+  const uint8_t * __restrict__ in = f.I[level - 1];
+  uint8_t * __restrict__ out = f.I[level];
+  const int ox0 = blockIdx.x * PT, oy0 = blockIdx.y * PT;
+  const int sx0 = 2 * ox0 - 2, sy0 = 2 * oy0 - 2;
+  for (int i = threadIdx.x; i < (2 * PT + 3) * (2 * PT + 3); i += 256) {
+    const int r = i / (2 * PT + 3), c = i - r * (2 * PT + 3);
+    const int y = reflect101(sy0 + r, Hp), x = reflect101(sx0 + c, Wp);
+    src[r][c] = in[(size_t)y * Wp + x];
+  }
+  __syncthreads();
+  // horizontal pass at even columns
+  for (int i = threadIdx.x; i < (2 * PT + 3) * PT; i += 256) {
+    const int r = i / PT, c = i - r * PT;
+    const uint8_t * p = &src[r][2 * c];
+    hrow[r][c] = (uint16_t)(p[0] + 4 * p[1] + 6 * p[2] + 4 * p[3] + p[4]);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < PT * PT; i += 256) {
+    const int r = i / PT, c = i - r * PT;
+    const int ox = ox0 + c, oy = oy0 + r;
+    if (ox < W && oy < H) {
+      const int sacc = hrow[2 * r][c] + 4 * hrow[2 * r + 1][c] + 6 * hrow[2 * r + 2][c] + 4 * hrow[2 * r + 3][c] +
+                       hrow[2 * r + 4][c];
+      out[(size_t)oy * W + ox] = (uint8_t)((sacc + 128) >> 8);
+    }
+  }
+}
+
+__device__ __forceinline__ void cswap(float & a, float & b)
+{
+  const float lo = fminf(a, b), hi = fmaxf(a, b);
+  a = lo;
+  b = hi;
+}
+
+__global__ void __launch_bounds__(256) depth_down_kernel(
+  const FrameDev * __restrict__ frames, const int * __restrict__ slots, int level, int Wdp, int Hdp, int Wd, int Hd)
+{
+  const FrameDev & f = frames[slots[blockIdx.z]];
+  const float * __restrict__ in = f.Z[level - 1];
+  const int j = blockIdx.x * 32 + (threadIdx.x & 31);
+  const int i = blockIdx.y * 8 + (threadIdx.x >> 5);
+  if (i >= Hd || j >= Wd) return;
+  const int y = 2 * i, x = 2 * j;
+  float out = 0.f;
+  if (y >= 1 && y < Hdp - 1 && x >= 1 && x < Wdp - 1) {
+    const float INF = __int_as_float(0x7f800000);
+    float v[9];
+    int n = 0;
+#pragma unroll
+    for (int dy = -1; dy <= 1; dy++)
+#pragma unroll
+      for (int dx = -1; dx <= 1; dx++) {
+        const float z = in[(size_t)(y + dy) * Wdp + (x + dx)];
+        const bool keep = !(z <= 0.f);  // mask v <= 0 (NaN passes, as in the reference)
+        v[(dy + 1) * 3 + dx + 1] = keep ? z : INF;
+        n += keep;
+      }
+    // 9-input sorting network (25 compare-exchanges); masked samples sort to the end as +inf.
+    // NaN inputs are undefined here exactly as std::sort with NaN is in the reference.
+    cswap(v[0], v[1]); cswap(v[3], v[4]); cswap(v[6], v[7]);
+    cswap(v[1], v[2]); cswap(v[4], v[5]); cswap(v[7], v[8]);
+    cswap(v[0], v[1]); cswap(v[3], v[4]); cswap(v[6], v[7]);
+    cswap(v[0], v[3]); cswap(v[3], v[6]); cswap(v[0], v[3]);
+    cswap(v[1], v[4]); cswap(v[4], v[7]); cswap(v[1], v[4]);
+    cswap(v[2], v[5]); cswap(v[5], v[8]); cswap(v[2], v[5]);
+    cswap(v[1], v[3]); cswap(v[5], v[7]);
+    cswap(v[2], v[6]); cswap(v[4], v[6]); cswap(v[2], v[4]);
+    cswap(v[2], v[3]); cswap(v[5], v[6]);
+    float a = 0.f, b = 0.f;
+    bool even = false;
+    switch (n) {
+      case 0: a = 0.f; break;
+      case 1: a = v[0]; break;
+      case 2: a = v[0]; break;                       // reference reads out of bounds here; documented rule
+      case 3: a = v[1]; break;
+      case 4: a = v[1]; b = v[3]; even = true; break;
+      case 5: a = v[2]; break;
+      case 6: a = v[2]; b = v[4]; even = true; break;
+      case 7: a = v[3]; break;
+      case 8: a = v[3]; b = v[5]; even = true; break;
+      default: a = v[4]; break;
+    }
+    out = even ? (float)(((double)a + (double)b) / 2.0) : a;
+  }
+  f.Z[level][(size_t)i * Wd + j] = out;
+  // single-frame candidate mask folded into a second depth plane: depth(0)(int(v*2^l), int(u*2^l)) > 0
+  const int W0 = f.Wd[0];
+  const float z0 = f.Z[0][(size_t)(i << level) * W0 + (j << level)];
+  f.Zsf[level][(size_t)i * Wd + j] = (z0 > 0.f) ? out : 0.f;
+}
+
+void launch_pyramid_level(const FrameDev * frames, const int * slots, int n, int level, int W, int H, int Wd, int Hd,
+                          int Wp, int Hp, int Wdp, int Hdp, cudaStream_t s)
+{
+  dim3 g1((W + PT - 1) / PT, (H + PT - 1) / PT, n);
+  pyr_down_u8_kernel<<<g1, 256, 0, s>>>(frames, slots, level, Wp, Hp, W, H);
+  if (Wd > 0 && Hd > 0) {
+    dim3 g2((Wd + 31) / 32, (Hd + 7) / 8, n);
+    depth_down_kernel<<<g2, 256, 0, s>>>(frames, slots, level, Wdp, Hdp, Wd, Hd);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// K2: cv::GaussianBlur 3x3 ((s+8)>>4, reflect-101) fused with cv::Sobel CV_16S dx, dy (reflect-101 on the
+// blurred image) — Frame.cpp:225-228.  Blurred halo tile lives in shared memory only.
+// ------------------------------------------------------------------------------------------------
+constexpr int GT_X = 64, GT_Y = 16;
+
+__global__ void __launch_bounds__(256) blur_sobel_kernel(
+  const FrameDev * __restrict__ frames, const int * __restrict__ slots, int level, int W, int H)
+{
+  __shared__ uint8_t blur[GT_Y + 2][GT_X + 2];
+  const FrameDev & f = frames[slots[blockIdx.z]];
+  const uint8_t * __restrict__ in = f.I[level];
+  const int x0 = blockIdx.x * GT_X, y0 = blockIdx.y * GT_Y;
+  for (int i = threadIdx.x; i < (GT_Y + 2) * (GT_X + 2); i += 256) {
+    const int r = i / (GT_X + 2), c = i - r * (GT_X + 2);
+    // position in the blurred image, reflected into range (Sobel's border), then blur with its own reflect
+    const int by = reflect101(y0 + r - 1, H), bx = reflect101(x0 + c - 1, W);
+    const int ym = reflect101(by - 1, H), yp = reflect101(by + 1, H);
+    const int xm = reflect101(bx - 1, W), xp = reflect101(bx + 1, W);
+    const uint8_t * r0 = in + (size_t)ym * W;
+    const uint8_t * r1 = in + (size_t)by * W;
+    const uint8_t * r2 = in + (size_t)yp * W;
+    const int sacc = (r0[xm] + 2 * r0[bx] + r0[xp]) + 2 * (r1[xm] + 2 * r1[bx] + r1[xp]) + (r2[xm] + 2 * r2[bx] + r2[xp]);
+    blur[r][c] = (uint8_t)((sacc + 8) >> 4);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < GT_X * GT_Y; i += 256) {
+    const int r = i / GT_X, c = i - r * GT_X;
+    const int x = x0 + c, y = y0 + r;
+    if (x < W && y < H) {
+      const int a00 = blur[r][c], a01 = blur[r][c + 1], a02 = blur[r][c + 2];
+      const int a10 = blur[r + 1][c], a12 = blur[r + 1][c + 2];
+      const int a20 = blur[r + 2][c], a21 = blur[r + 2][c + 1], a22 = blur[r + 2][c + 2];
+      f.gx[level][(size_t)y * W + x] = (int16_t)((a02 - a00) + 2 * (a12 - a10) + (a22 - a20));
+      f.gy[level][(size_t)y * W + x] = (int16_t)((a20 + 2 * a21 + a22) - (a00 + 2 * a01 + a02));
+    }
+  }
+}
+
+void launch_gradients(const FrameDev * frames, const int * slots, int n, int level, int W, int H, cudaStream_t s)
+{
+  dim3 g((W + GT_X - 1) / GT_X, (H + GT_Y - 1) / GT_Y, n);
+  blur_sobel_kernel<<<g, 256, 0, s>>>(frames, slots, level, W, H);
+}
+}  // namespace vb
