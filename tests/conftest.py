@@ -1,0 +1,41 @@
+import os
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box)")
+
+
+@pytest.fixture(scope="session")
+def oracle():
+    from oracle import oracle as O
+    O.build()
+    return O
+
+
+@pytest.fixture(scope="session")
+def synth():
+    from vslam_b200 import synth as S
+    S.build()
+    return S
+
+
+@pytest.fixture(scope="session")
+def capi():
+    from vslam_b200 import build, capi as A
+    if not os.path.exists(A.LIB_PATH):
+        build.build_cuda()
+    return A
+
+
+@pytest.fixture()
+def ctx(capi):
+    c = capi.Context(capi.make_config())
+    yield c
+    c.close()

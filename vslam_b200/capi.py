@@ -1,0 +1,224 @@
+"""ctypes binding of include/vslam_b200.h.  Fails loudly when the CUDA library is missing: there is no
+CPU fallback."""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libvslam_b200.so")
+
+MAX_LEVELS = 8
+TRACE_STRIDE = 64
+LOSS_NONE, LOSS_QUADRATIC, LOSS_TUKEY, LOSS_HUBER, LOSS_TDIST = range(5)
+SCALER_IDENTITY, SCALER_MEDIAN, SCALER_MEAN, SCALER_TDIST = range(4)
+ROW_MAJOR, COL_MAJOR = 0, 1
+DEPTH_F32, DEPTH_F64 = 0, 1
+R_NOT_INTEREST, R_INVISIBLE = -32768, -32767
+STOP_NAMES = ["maxiter", "constraints", "hessian", "chi2", "converged", "nan"]
+
+
+class Config(C.Structure):
+    _fields_ = [("min_gradient", C.c_double), ("loss_kind", C.c_int), ("huber_c", C.c_double),
+                ("loss_v", C.c_double), ("scaler_kind", C.c_int), ("scaler_v", C.c_double),
+                ("min_step_size", C.c_double), ("max_iterations", C.c_int), ("include_prior", C.c_int)]
+
+
+class Job(C.Structure):
+    _fields_ = [("to", C.c_uint64), ("to_pose", C.c_double * 7), ("n_from", C.c_int), ("multi", C.c_int),
+                ("from_", C.POINTER(C.c_uint64)), ("from_poses", C.POINTER(C.c_double))]
+
+
+class Result(C.Structure):
+    _fields_ = [("pose", C.c_double * 7), ("cov", C.c_double * 36), ("status", C.c_int),
+                ("iters", C.c_int * MAX_LEVELS), ("stop", C.c_int * MAX_LEVELS)]
+
+
+class Stats(C.Structure):
+    _fields_ = [("kernel_launches", C.c_uint64), ("pixel_iterations", C.c_uint64),
+                ("point_iterations", C.c_uint64), ("gn_iterations", C.c_uint64), ("frames_uploaded", C.c_uint64),
+                ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64), ("ms_residual", C.c_double),
+                ("ms_accumulate", C.c_double), ("ms_preprocess", C.c_double), ("ms_lists", C.c_double)]
+
+
+EXPORTS = [
+    "vslamb200_last_error", "vslamb200_version", "vslamb200_create", "vslamb200_destroy", "vslamb200_set_config",
+    "vslamb200_set_stream", "vslamb200_frames_upload", "vslamb200_frames_upload_device", "vslamb200_frame_release",
+    "vslamb200_frame_release_all", "vslamb200_frame_dims", "vslamb200_frame_download", "vslamb200_align",
+    "vslamb200_set_trace", "vslamb200_get_trace", "vslamb200_evaluate", "vslamb200_get_stats",
+    "vslamb200_reset_stats", "vslamb200_set_timing", "vslamb200_synchronize",
+]
+
+_lib = None
+
+
+class VslamB200Error(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"vslam_b200 error {code}: {msg}")
+        self.code = code
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(f"{LIB_PATH} is missing: build it with `python -m vslam_b200.build` "
+                               "(vslam_b200 has no CPU fallback)")
+        L = C.CDLL(LIB_PATH)
+        vp, i, u64, sz = C.c_void_p, C.c_int, C.c_uint64, C.c_size_t
+        L.vslamb200_last_error.restype = C.c_char_p
+        L.vslamb200_create.argtypes = [vp, i, vp]
+        L.vslamb200_destroy.argtypes = [vp]
+        L.vslamb200_destroy.restype = None
+        L.vslamb200_set_config.argtypes = [vp, vp]
+        L.vslamb200_set_stream.argtypes = [vp, vp]
+        L.vslamb200_frames_upload.argtypes = [vp, i, vp, i, i, vp, sz, vp, i, sz, i, vp, i]
+        L.vslamb200_frames_upload_device.argtypes = [vp, i, vp, i, i, vp, vp, vp, i]
+        L.vslamb200_frame_release.argtypes = [vp, u64]
+        L.vslamb200_frame_release_all.argtypes = [vp]
+        L.vslamb200_frame_dims.argtypes = [vp, u64, i, vp]
+        L.vslamb200_frame_download.argtypes = [vp, u64, i, vp, vp, vp, vp, vp]
+        L.vslamb200_align.argtypes = [vp, vp, i, vp]
+        L.vslamb200_set_trace.argtypes = [vp, i]
+        L.vslamb200_get_trace.argtypes = [vp, i, vp]
+        L.vslamb200_evaluate.argtypes = [vp, u64, u64, i, vp, i, vp, vp]
+        L.vslamb200_get_stats.argtypes = [vp, vp]
+        L.vslamb200_reset_stats.argtypes = [vp]
+        L.vslamb200_set_timing.argtypes = [vp, i]
+        L.vslamb200_synchronize.argtypes = [vp]
+        _lib = L
+    return _lib
+
+
+def check(code):
+    if code != 0:
+        raise VslamB200Error(code, lib().vslamb200_last_error().decode())
+
+
+def ptr(a):
+    return a.ctypes.data_as(C.c_void_p) if a is not None else None
+
+
+def make_config(min_gradient=30.0, loss=LOSS_TDIST, scaler=SCALER_TDIST, huber_c=1.345, v=5.0,
+                min_step_size=1e-7, max_iterations=100, include_prior=False):
+    return Config(min_gradient, loss, huber_c, v, scaler, v, min_step_size, max_iterations, int(include_prior))
+
+
+class Context:
+    """Thin object wrapper over the C ABI (one context = one device + one stream)."""
+
+    def __init__(self, cfg=None, device=0):
+        self.cfg = cfg or make_config()
+        h = C.c_void_p()
+        check(lib().vslamb200_create(C.byref(self.cfg), device, C.byref(h)))
+        self.h = h
+
+    def close(self):
+        if getattr(self, "h", None):
+            lib().vslamb200_destroy(self.h)
+            self.h = None
+
+    __del__ = close
+
+    def set_config(self, cfg):
+        self.cfg = cfg
+        check(lib().vslamb200_set_config(self.h, C.byref(cfg)))
+
+    def upload(self, ids, gray, depth, cams, n_levels, layout=ROW_MAJOR):
+        """gray (n,H,W) u8, depth (n,H,W) f32|f64 (or (n,W,H) memory when layout == COL_MAJOR: pass W,H via shape
+        of the row-major interpretation), cams (n,4) or (4,)."""
+        gray = np.ascontiguousarray(gray)
+        depth = np.ascontiguousarray(depth)
+        if gray.ndim == 2:
+            gray, depth = gray[None], depth[None]
+        n = gray.shape[0]
+        if layout == ROW_MAJOR:
+            H, W = gray.shape[1:]
+        else:
+            W, H = gray.shape[1:]
+        ids = np.ascontiguousarray(np.atleast_1d(ids), np.uint64)
+        cams = np.ascontiguousarray(np.broadcast_to(np.asarray(cams, np.float64).reshape(-1, 4), (n, 4)))
+        assert gray.dtype == np.uint8 and depth.dtype in (np.float32, np.float64) and len(ids) == n
+        dt = DEPTH_F32 if depth.dtype == np.float32 else DEPTH_F64
+        check(lib().vslamb200_frames_upload(self.h, n, ptr(ids), W, H, ptr(gray), 0, ptr(depth), dt, 0, layout,
+                                            ptr(cams), n_levels))
+
+    def upload_device(self, ids, d_gray_ptr, d_depth_ptr, n, W, H, cams, n_levels):
+        ids = np.ascontiguousarray(np.atleast_1d(ids), np.uint64)
+        cams = np.ascontiguousarray(np.broadcast_to(np.asarray(cams, np.float64).reshape(-1, 4), (n, 4)))
+        check(lib().vslamb200_frames_upload_device(self.h, n, ptr(ids), W, H, C.c_void_p(d_gray_ptr),
+                                                   C.c_void_p(d_depth_ptr), ptr(cams), n_levels))
+
+    def release(self, fid):
+        check(lib().vslamb200_frame_release(self.h, int(fid)))
+
+    def release_all(self):
+        check(lib().vslamb200_frame_release_all(self.h))
+
+    def dims(self, fid, level):
+        d = np.zeros(4, np.int32)
+        check(lib().vslamb200_frame_dims(self.h, int(fid), level, ptr(d)))
+        return tuple(int(x) for x in d)
+
+    def download(self, fid, level):
+        W, H, Wd, Hd = self.dims(fid, level)
+        out = dict(I=np.empty((H, W), np.uint8), Z=np.empty((Hd, Wd), np.float32),
+                   Zsf=np.empty((Hd, Wd), np.float32), dIx=np.empty((H, W), np.int16),
+                   dIy=np.empty((H, W), np.int16))
+        check(lib().vslamb200_frame_download(self.h, int(fid), level, ptr(out["I"]), ptr(out["Z"]), ptr(out["Zsf"]),
+                                             ptr(out["dIx"]), ptr(out["dIy"])))
+        return out
+
+    def align(self, jobs):
+        """jobs: list of dict(to=id, to_pose=(7,), frm=[ids], from_poses=(k,7), multi=bool) -> list of dict"""
+        n = len(jobs)
+        arr = (Job * n)()
+        keep = []
+        for k, j in enumerate(jobs):
+            frm = np.ascontiguousarray(np.atleast_1d(j["frm"]), np.uint64)
+            fp = np.ascontiguousarray(np.asarray(j["from_poses"], np.float64).reshape(-1, 7))
+            keep += [frm, fp]
+            arr[k].to = int(j["to"])
+            arr[k].to_pose = (C.c_double * 7)(*np.asarray(j["to_pose"], np.float64))
+            arr[k].n_from = len(frm)
+            arr[k].multi = int(bool(j.get("multi", len(frm) > 1)))
+            arr[k].from_ = frm.ctypes.data_as(C.POINTER(C.c_uint64))
+            arr[k].from_poses = fp.ctypes.data_as(C.POINTER(C.c_double))
+        res = (Result * n)()
+        check(lib().vslamb200_align(self.h, arr, n, res))
+        out = []
+        for r in res:
+            out.append(dict(pose=np.array(r.pose), cov=np.array(r.cov).reshape(6, 6), status=r.status,
+                            iters=np.array(r.iters), stop=np.array(r.stop)))
+        return out
+
+    def align_raw(self, job_array, n, result_array):
+        check(lib().vslamb200_align(self.h, job_array, n, result_array))
+
+    def set_trace(self, on):
+        check(lib().vslamb200_set_trace(self.h, int(on)))
+
+    def get_trace(self, job, n_levels):
+        t = np.zeros((n_levels, self.cfg.max_iterations, TRACE_STRIDE))
+        check(lib().vslamb200_get_trace(self.h, job, ptr(t)))
+        return t
+
+    def evaluate(self, frm, to, level, se3, multi_mask=False):
+        W, H, _, _ = self.dims(frm, level)
+        rcode = np.empty((H, W), np.int16)
+        ne = np.zeros(64)
+        se3 = np.ascontiguousarray(se3, np.float64)
+        check(lib().vslamb200_evaluate(self.h, int(frm), int(to), level, ptr(se3), int(multi_mask), ptr(rcode), ptr(ne)))
+        return dict(n=int(ne[0]), chi2=ne[1], scale=ne[2], offset=ne[3], b=ne[4:10].copy(),
+                    A=ne[10:46].reshape(6, 6).copy(), rcode=rcode)
+
+    def stats(self):
+        s = Stats()
+        check(lib().vslamb200_get_stats(self.h, C.byref(s)))
+        return {f[0]: getattr(s, f[0]) for f in Stats._fields_}
+
+    def reset_stats(self):
+        check(lib().vslamb200_reset_stats(self.h))
+
+    def synchronize(self):
+        check(lib().vslamb200_synchronize(self.h))

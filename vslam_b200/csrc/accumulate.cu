@@ -7,7 +7,7 @@ namespace vb
 constexpr int THREADS = 256;
 
 template <int PPT>
-__global__ void __launch_bounds__(THREADS) accumulate_kernel(
+__global__ void __launch_bounds__(THREADS, 3) accumulate_kernel(
   JobState * __restrict__ jobs, ViewState * __restrict__ views, const int * __restrict__ activeViews,
   double * __restrict__ partials, int partialStride, SolverParams p, int level, double * __restrict__ trace,
   size_t traceJobStride)
@@ -26,7 +26,7 @@ __global__ void __launch_bounds__(THREADS) accumulate_kernel(
   }
   __syncthreads();
 
-  const float ifx = V.ifx32, ify = V.ify32, kx = V.kx32, ky = V.ky32, fxJ = V.fxJ, fyJ = V.fyJ;
+  const double ifx = V.ifx, ify = V.ify, kx = V.kx, ky = V.ky, fxJ = V.fxJd, fyJ = V.fyJd;
   const uint32_t * __restrict__ uvt = V.uvt;
   const float * __restrict__ dep = V.d;
   const uint32_t * __restrict__ grad = V.g;
@@ -47,22 +47,24 @@ __global__ void __launch_bounds__(THREADS) accumulate_kernel(
         const uint32_t pk = __ldg(uvt + idx);
         const float d = __ldg(dep + idx);
         const uint32_t gg = __ldg(grad + idx);
-        const float u = (float)(pk & 0xfff), v = (float)((pk >> 12) & 0xfff);
-        const float a = (float)(int16_t)(gg & 0xffff) * fxJ;   // dIx * fx
-        const float b = (float)(int16_t)(gg >> 16) * fyJ;      // dIy * fy
+        // WarpSE3::J rows (Warp.cpp:184-199) contracted with the template gradient
+        // (InverseCompositional.cpp:79-80), in normalised coordinates xn = x/z, yn = y/z.  The six
+        // entries are formed in fp64 and only then rounded to fp32: a coherent fp32 bias in xn / yn
+        // would be amplified by the cancellation in b = sum(w J r) near convergence.
+        const double u = (double)(pk & 0xfff), v = (double)((pk >> 12) & 0xfff);
+        const double a = (double)(int16_t)(gg & 0xffff) * fxJ;   // dIx * fx
+        const double b = (double)(int16_t)(gg >> 16) * fyJ;      // dIy * fy
         const float w = weighted ? lut[rr + 255] : 1.f;
         const float r = (float)rr;
-        // WarpSE3::J rows (Warp.cpp:184-199) contracted with the template gradient
-        // (InverseCompositional.cpp:79-80), in normalised coordinates xn = x/z, yn = y/z
-        const float zi = 1.f / d;
-        const float xn = fmaf(ifx, u, kx), yn = fmaf(ify, v, ky);
+        const double zi = 1.0 / (double)d;
+        const double xn = fma(ifx, u, kx), yn = fma(ify, v, ky);
         float J[6];
-        J[0] = a * zi;
-        J[1] = b * zi;
-        J[2] = -(a * xn + b * yn) * zi;
-        J[3] = -a * xn * yn - b * (1.f + yn * yn);
-        J[4] = a * (1.f + xn * xn) + b * xn * yn;
-        J[5] = b * xn - a * yn;
+        J[0] = (float)(a * zi);
+        J[1] = (float)(b * zi);
+        J[2] = (float)(-(a * xn + b * yn) * zi);
+        J[3] = (float)(-a * xn * yn - b * (1.0 + yn * yn));
+        J[4] = (float)(a * (1.0 + xn * xn) + b * xn * yn);
+        J[5] = (float)(b * xn - a * yn);
         int s = 0;
 #pragma unroll
         for (int i = 0; i < 6; i++) {
@@ -170,12 +172,8 @@ __global__ void level_setup_kernel(
   V.ify = 1.0 / V.fy;
   V.kx = -V.cx / V.fx;
   V.ky = -V.cy / V.fy;
-  V.ifx32 = (float)V.ifx;
-  V.ify32 = (float)V.ify;
-  V.kx32 = (float)V.kx;
-  V.ky32 = (float)V.ky;
-  V.fxJ = (float)ft.cam[level][0];
-  V.fyJ = (float)ft.cam[level][1];
+  V.fxJd = ft.cam[level][0];
+  V.fyJd = ft.cam[level][1];
   V.nIp = 0;
   V.nChunks = 0;
   V.ticketA = 0;

@@ -1,0 +1,807 @@
+// Host side of the C ABI (include/vslam_b200.h): context, device frame cache, batched alignment driver.
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <unordered_map>
+#include <vector>
+
+#include "common.cuh"
+
+namespace
+{
+thread_local std::string g_err;
+int fail(int code, const std::string & msg)
+{
+  g_err = msg;
+  return code;
+}
+#define CK(call)                                                                                          \
+  do {                                                                                                    \
+    cudaError_t e_ = (call);                                                                              \
+    if (e_ != cudaSuccess)                                                                                \
+      return fail(VSLAMB200_ECUDA, std::string(#call) + ": " + cudaGetErrorString(e_));                   \
+  } while (0)
+
+struct DevBuf
+{
+  void * p = nullptr;
+  size_t cap = 0;
+  cudaError_t ensure(size_t bytes, bool zero = false)
+  {
+    if (bytes <= cap) return cudaSuccess;
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+    size_t want = bytes + bytes / 8 + 256;
+    cudaError_t e = cudaMalloc(&p, want);
+    if (e != cudaSuccess) return e;
+    cap = want;
+    if (zero) e = cudaMemset(p, 0, want);
+    return e;
+  }
+  void release()
+  {
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+  }
+  template <typename T>
+  T * as()
+  {
+    return reinterpret_cast<T *>(p);
+  }
+};
+
+struct Arena
+{
+  void * ptr = nullptr;
+  size_t bytes = 0;
+  int refs = 0;
+};
+
+struct FrameHost
+{
+  bool used = false;
+  uint64_t id = 0;
+  int arena = -1;
+  vb::FrameDev dev;
+};
+
+size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+}  // namespace
+
+struct vslamb200_ctx
+{
+  int device = 0;
+  cudaStream_t own = nullptr, stream = nullptr;
+  vslamb200_config cfg;
+  std::unordered_map<uint64_t, int> idToSlot;
+  std::vector<FrameHost> frames;
+  std::vector<int> freeSlots;
+  std::vector<Arena> arenas;
+  DevBuf dFrames;  // FrameDev table
+  DevBuf stageGray, stageDepth, slotsBuf;
+  // alignment workspace
+  DevBuf jobs, views, active, counts, chunkCounts, partials, lists, hist, wlut, trace, plane;
+  int * hCounts = nullptr;  // pinned
+  int traceEnabled = 0, timing = 0;
+  int traceJobs = 0, traceLevels = 0, traceMaxIter = 0;
+  vslamb200_stats stats;
+  cudaEvent_t ev[3] = {nullptr, nullptr, nullptr};
+};
+
+namespace
+{
+void level_dims(int W, int H, int nLevels, vb::FrameDev & f)
+{
+  f.nLevels = nLevels;
+  f.W[0] = f.Wd[0] = W;
+  f.H[0] = f.Hd[0] = H;
+  for (int l = 1; l < nLevels; l++) {
+    f.W[l] = (f.W[l - 1] + 1) / 2;  // cv::pyrDown (Frame.cpp:264)
+    f.H[l] = (f.H[l - 1] + 1) / 2;
+    f.Wd[l] = (int)(f.Wd[l - 1] * 0.5);  // algorithm::resize (algorithm.h:93-94)
+    f.Hd[l] = (int)(f.Hd[l - 1] * 0.5);
+  }
+}
+
+// per-frame block layout; returns bytes.  base == nullptr only sizes.
+size_t layout_frame(vb::FrameDev & f, uint8_t * base)
+{
+  size_t off = 0;
+  auto take = [&](size_t bytes) {
+    uint8_t * p = base ? base + off : nullptr;
+    off += align_up(std::max<size_t>(bytes, 1), 256);
+    return p;
+  };
+  for (int l = 0; l < f.nLevels; l++) {
+    const size_t n = (size_t)f.W[l] * f.H[l], nd = (size_t)f.Wd[l] * f.Hd[l];
+    f.I[l] = take(n);
+    f.Z[l] = (float *)take(nd * 4);
+    f.Zsf[l] = l == 0 ? f.Z[0] : (float *)take(nd * 4);
+    f.gx[l] = (int16_t *)take(n * 2);
+    f.gy[l] = (int16_t *)take(n * 2);
+  }
+  return off;
+}
+
+int release_slot(vslamb200_ctx * c, int slot)
+{
+  FrameHost & f = c->frames[slot];
+  if (!f.used) return 0;
+  c->idToSlot.erase(f.id);
+  f.used = false;
+  Arena & a = c->arenas[f.arena];
+  if (--a.refs == 0) {
+    cudaFree(a.ptr);
+    a.ptr = nullptr;
+    a.bytes = 0;
+  }
+  c->freeSlots.push_back(slot);
+  return 0;
+}
+
+int upload_table(vslamb200_ctx * c, const std::vector<int> & slots)
+{
+  const size_t need = c->frames.size() * sizeof(vb::FrameDev);
+  if (need > c->dFrames.cap) {
+    // grow: re-upload every live entry
+    CK(cudaStreamSynchronize(c->stream));
+    CK(c->dFrames.ensure(std::max<size_t>(need * 2, 64 * sizeof(vb::FrameDev))));
+    std::vector<vb::FrameDev> all(c->frames.size());
+    for (size_t i = 0; i < c->frames.size(); i++) all[i] = c->frames[i].dev;
+    CK(cudaMemcpyAsync(c->dFrames.p, all.data(), need, cudaMemcpyHostToDevice, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    return 0;
+  }
+  // contiguous runs
+  size_t i = 0;
+  std::vector<int> s(slots);
+  std::sort(s.begin(), s.end());
+  std::vector<vb::FrameDev> tmp;
+  while (i < s.size()) {
+    size_t j = i;
+    while (j + 1 < s.size() && s[j + 1] == s[j] + 1) j++;
+    tmp.resize(j - i + 1);
+    for (size_t k = i; k <= j; k++) tmp[k - i] = c->frames[s[k]].dev;
+    CK(cudaMemcpyAsync(c->dFrames.as<vb::FrameDev>() + s[i], tmp.data(), tmp.size() * sizeof(vb::FrameDev),
+                       cudaMemcpyHostToDevice, c->stream));
+    CK(cudaStreamSynchronize(c->stream));  // tmp is reused
+    i = j + 1;
+  }
+  return 0;
+}
+
+// allocate slots + one arena for n frames of identical geometry
+int make_frames(vslamb200_ctx * c, int n, const uint64_t * ids, int W, int H, const double * cams, int nLevels,
+                std::vector<int> & slots)
+{
+  if (n <= 0 || !ids || !cams) return fail(VSLAMB200_EINVAL, "frames_upload: bad arguments");
+  if (nLevels < 1 || nLevels > vb::MAX_LEVELS) return fail(VSLAMB200_EINVAL, "frames_upload: n_levels out of range");
+  if (W < 1 || H < 1 || W > 4095 || H > 4095) return fail(VSLAMB200_EINVAL, "frames_upload: image size out of range");
+  for (int i = 0; i < n; i++)
+    if (std::abs(W / 2 - cams[4 * i + 2]) > 10)  // Frame.cpp:150-155
+      return fail(VSLAMB200_EDIMS, "Inconsistent camera parameters / image / depth dimensions detected.");
+  vb::FrameDev proto;
+  std::memset(&proto, 0, sizeof(proto));
+  level_dims(W, H, nLevels, proto);
+  const size_t frameBytes = layout_frame(proto, nullptr);
+  Arena a;
+  a.bytes = frameBytes * n;
+  CK(cudaMalloc(&a.ptr, a.bytes));
+  a.refs = n;
+  int arenaIdx = -1;
+  for (size_t i = 0; i < c->arenas.size(); i++)
+    if (!c->arenas[i].ptr) arenaIdx = (int)i;
+  if (arenaIdx < 0) {
+    c->arenas.push_back(a);
+    arenaIdx = (int)c->arenas.size() - 1;
+  } else {
+    c->arenas[arenaIdx] = a;
+  }
+  slots.resize(n);
+  for (int i = 0; i < n; i++) {
+    auto it = c->idToSlot.find(ids[i]);
+    if (it != c->idToSlot.end()) release_slot(c, it->second);
+    int slot;
+    if (!c->freeSlots.empty()) {
+      slot = c->freeSlots.back();
+      c->freeSlots.pop_back();
+    } else {
+      slot = (int)c->frames.size();
+      c->frames.emplace_back();
+    }
+    FrameHost & f = c->frames[slot];
+    f.used = true;
+    f.id = ids[i];
+    f.arena = arenaIdx;
+    f.dev = proto;
+    layout_frame(f.dev, (uint8_t *)a.ptr + frameBytes * i);
+    for (int l = 0; l < nLevels; l++) {
+      const double s = std::pow(0.5, l);  // Camera::resize (Camera.cpp:53-57, Frame.cpp:267)
+      for (int k = 0; k < 4; k++) f.dev.cam[l][k] = cams[4 * i + k] * s;
+    }
+    c->idToSlot[ids[i]] = slot;
+    slots[i] = slot;
+  }
+  return upload_table(c, slots);
+}
+
+// pyramid + gradients for uploaded level-0 planes
+int preprocess(vslamb200_ctx * c, const std::vector<int> & slots, int W, int H, int nLevels)
+{
+  const int n = (int)slots.size();
+  CK(c->slotsBuf.ensure(n * sizeof(int)));
+  CK(cudaMemcpyAsync(c->slotsBuf.p, slots.data(), n * sizeof(int), cudaMemcpyHostToDevice, c->stream));
+  const vb::FrameDev & f = c->frames[slots[0]].dev;
+  const vb::FrameDev * table = c->dFrames.as<vb::FrameDev>();
+  for (int l = 1; l < nLevels; l++) {
+    vb::launch_pyramid_level(table, c->slotsBuf.as<int>(), n, l, f.W[l], f.H[l], f.Wd[l], f.Hd[l], f.W[l - 1],
+                             f.H[l - 1], f.Wd[l - 1], f.Hd[l - 1], c->stream);
+    c->stats.kernel_launches += 2;
+  }
+  for (int l = 0; l < nLevels; l++) {
+    vb::launch_gradients(table, c->slotsBuf.as<int>(), n, l, f.W[l], f.H[l], c->stream);
+    c->stats.kernel_launches += 1;
+  }
+  CK(cudaGetLastError());
+  CK(cudaStreamSynchronize(c->stream));  // slots vector / staging lifetimes
+  c->stats.frames_uploaded += n;
+  (void)W;
+  (void)H;
+  return 0;
+}
+}  // namespace
+
+// ------------------------------------------------------------------------------------------------
+// C ABI: context and frames
+// ------------------------------------------------------------------------------------------------
+extern "C" {
+
+const char * vslamb200_last_error(void) { return g_err.c_str(); }
+int vslamb200_version(void) { return 100; }
+
+static int check_cfg(const vslamb200_config * cfg)
+{
+  if (!cfg) return fail(VSLAMB200_EINVAL, "config is null");
+  if (cfg->loss_kind < 0 || cfg->loss_kind > VSLAMB200_LOSS_TDIST) return fail(VSLAMB200_EINVAL, "bad loss_kind");
+  if (cfg->scaler_kind < 0 || cfg->scaler_kind > VSLAMB200_SCALER_TDIST) return fail(VSLAMB200_EINVAL, "bad scaler_kind");
+  if (cfg->max_iterations < 1 || cfg->max_iterations > 100000) return fail(VSLAMB200_EINVAL, "bad max_iterations");
+  return 0;
+}
+
+int vslamb200_create(const vslamb200_config * cfg, int device, vslamb200_ctx ** out)
+{
+  if (!out) return fail(VSLAMB200_EINVAL, "out is null");
+  if (int e = check_cfg(cfg)) return e;
+  int nDev = 0;
+  cudaError_t ce = cudaGetDeviceCount(&nDev);
+  if (ce != cudaSuccess || nDev == 0)
+    return fail(VSLAMB200_ECUDA, std::string("no CUDA device available (") + cudaGetErrorString(ce) +
+                                   "); vslam_b200 has no CPU fallback");
+  if (device < 0 || device >= nDev) return fail(VSLAMB200_EINVAL, "device index out of range");
+  CK(cudaSetDevice(device));
+  auto c = new vslamb200_ctx();
+  c->device = device;
+  c->cfg = *cfg;
+  std::memset(&c->stats, 0, sizeof(c->stats));
+  cudaError_t e1 = cudaStreamCreateWithFlags(&c->own, cudaStreamNonBlocking);
+  cudaError_t e2 = cudaMallocHost((void **)&c->hCounts, 16 * sizeof(int));
+  cudaError_t e3 = cudaEventCreate(&c->ev[0]);
+  cudaError_t e4 = cudaEventCreate(&c->ev[1]);
+  if (e4 == cudaSuccess) e4 = cudaEventCreate(&c->ev[2]);
+  if (e1 != cudaSuccess || e2 != cudaSuccess || e3 != cudaSuccess || e4 != cudaSuccess) {
+    delete c;
+    return fail(VSLAMB200_ECUDA, "context resources could not be created");
+  }
+  c->stream = c->own;
+  *out = c;
+  return 0;
+}
+
+void vslamb200_destroy(vslamb200_ctx * c)
+{
+  if (!c) return;
+  cudaSetDevice(c->device);
+  cudaStreamSynchronize(c->stream);
+  for (auto & a : c->arenas)
+    if (a.ptr) cudaFree(a.ptr);
+  DevBuf * bufs[] = {&c->dFrames, &c->stageGray, &c->stageDepth, &c->slotsBuf, &c->jobs, &c->views, &c->active,
+                     &c->counts, &c->chunkCounts, &c->partials, &c->lists, &c->hist, &c->wlut, &c->trace, &c->plane};
+  for (auto b : bufs) b->release();
+  if (c->hCounts) cudaFreeHost(c->hCounts);
+  if (c->ev[0]) cudaEventDestroy(c->ev[0]);
+  if (c->ev[1]) cudaEventDestroy(c->ev[1]);
+  if (c->ev[2]) cudaEventDestroy(c->ev[2]);
+  if (c->own) cudaStreamDestroy(c->own);
+  delete c;
+}
+
+int vslamb200_set_config(vslamb200_ctx * c, const vslamb200_config * cfg)
+{
+  if (!c) return fail(VSLAMB200_EINVAL, "ctx is null");
+  if (int e = check_cfg(cfg)) return e;
+  c->cfg = *cfg;
+  return 0;
+}
+
+int vslamb200_set_stream(vslamb200_ctx * c, void * s)
+{
+  if (!c) return fail(VSLAMB200_EINVAL, "ctx is null");
+  CK(cudaStreamSynchronize(c->stream));
+  c->stream = s ? (cudaStream_t)s : c->own;
+  return 0;
+}
+
+int vslamb200_synchronize(vslamb200_ctx * c)
+{
+  if (!c) return fail(VSLAMB200_EINVAL, "ctx is null");
+  CK(cudaSetDevice(c->device));
+  CK(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+int vslamb200_frames_upload(
+  vslamb200_ctx * c, int n, const uint64_t * ids, int W, int H, const uint8_t * gray, size_t grayStride,
+  const void * depth, int depthType, size_t depthStride, int layout, const double * cams, int nLevels)
+{
+  if (!c || !gray || !depth) return fail(VSLAMB200_EINVAL, "frames_upload: null argument");
+  if (depthType != VSLAMB200_DEPTH_F32 && depthType != VSLAMB200_DEPTH_F64)
+    return fail(VSLAMB200_EINVAL, "frames_upload: bad depth_type");
+  if (layout != VSLAMB200_ROW_MAJOR && layout != VSLAMB200_COL_MAJOR)
+    return fail(VSLAMB200_EINVAL, "frames_upload: bad layout");
+  CK(cudaSetDevice(c->device));
+  std::vector<int> slots;
+  if (int e = make_frames(c, n, ids, W, H, cams, nLevels, slots)) return e;
+  const size_t npx = (size_t)W * H;
+  const size_t dsz = depthType == VSLAMB200_DEPTH_F64 ? 8 : 4;
+  if (!grayStride) grayStride = npx;
+  if (!depthStride) depthStride = npx * dsz;
+  // frames of one call live in one arena with a constant stride
+  const vb::FrameDev & f0 = c->frames[slots[0]].dev;
+  const size_t frameStride = n > 1 ? (size_t)((uint8_t *)c->frames[slots[1]].dev.I[0] - (uint8_t *)f0.I[0]) : npx;
+  const bool direct = layout == VSLAMB200_ROW_MAJOR && depthType == VSLAMB200_DEPTH_F32;
+  if (direct) {
+    CK(cudaMemcpy2DAsync(f0.I[0], frameStride, gray, grayStride, npx, n, cudaMemcpyHostToDevice, c->stream));
+    CK(cudaMemcpy2DAsync(f0.Z[0], frameStride, depth, depthStride, npx * 4, n, cudaMemcpyHostToDevice, c->stream));
+  } else {
+    const int sub = 32;  // frames per staging round
+    CK(c->stageGray.ensure(npx * sub));
+    CK(c->stageDepth.ensure(npx * dsz * sub));
+    CK(c->slotsBuf.ensure((size_t)n * sizeof(int)));
+    for (int b = 0; b < n; b += sub) {
+      const int m = std::min(sub, n - b);
+      CK(cudaMemcpy2DAsync(c->stageGray.p, npx, gray + grayStride * b, grayStride, npx, m, cudaMemcpyHostToDevice, c->stream));
+      CK(cudaMemcpy2DAsync(c->stageDepth.p, npx * dsz, (const uint8_t *)depth + depthStride * b, depthStride, npx * dsz,
+                           m, cudaMemcpyHostToDevice, c->stream));
+      CK(cudaMemcpyAsync(c->slotsBuf.p, slots.data() + b, m * sizeof(int), cudaMemcpyHostToDevice, c->stream));
+      vb::launch_ingest(c->stageGray.as<uint8_t>(), c->stageDepth.p, depthType, layout, W, H,
+                        c->dFrames.as<vb::FrameDev>(), c->slotsBuf.as<int>(), m, c->stream);
+      c->stats.kernel_launches++;
+      CK(cudaStreamSynchronize(c->stream));
+    }
+  }
+  c->stats.h2d_bytes += (uint64_t)n * npx * (1 + dsz);
+  return preprocess(c, slots, W, H, nLevels);
+}
+
+int vslamb200_frames_upload_device(
+  vslamb200_ctx * c, int n, const uint64_t * ids, int W, int H, const uint8_t * dGray, const float * dDepth,
+  const double * cams, int nLevels)
+{
+  if (!c || !dGray || !dDepth) return fail(VSLAMB200_EINVAL, "frames_upload_device: null argument");
+  CK(cudaSetDevice(c->device));
+  std::vector<int> slots;
+  if (int e = make_frames(c, n, ids, W, H, cams, nLevels, slots)) return e;
+  const size_t npx = (size_t)W * H;
+  const vb::FrameDev & f0 = c->frames[slots[0]].dev;
+  const size_t frameStride = n > 1 ? (size_t)((uint8_t *)c->frames[slots[1]].dev.I[0] - (uint8_t *)f0.I[0]) : npx;
+  CK(cudaMemcpy2DAsync(f0.I[0], frameStride, dGray, npx, npx, n, cudaMemcpyDeviceToDevice, c->stream));
+  CK(cudaMemcpy2DAsync(f0.Z[0], frameStride, dDepth, npx * 4, npx * 4, n, cudaMemcpyDeviceToDevice, c->stream));
+  return preprocess(c, slots, W, H, nLevels);
+}
+
+int vslamb200_frame_release(vslamb200_ctx * c, uint64_t id)
+{
+  if (!c) return fail(VSLAMB200_EINVAL, "ctx is null");
+  auto it = c->idToSlot.find(id);
+  if (it == c->idToSlot.end()) return fail(VSLAMB200_ENOFRAME, "frame_release: unknown frame id");
+  CK(cudaSetDevice(c->device));
+  CK(cudaStreamSynchronize(c->stream));
+  return release_slot(c, it->second);
+}
+
+int vslamb200_frame_release_all(vslamb200_ctx * c)
+{
+  if (!c) return fail(VSLAMB200_EINVAL, "ctx is null");
+  CK(cudaSetDevice(c->device));
+  CK(cudaStreamSynchronize(c->stream));
+  for (size_t i = 0; i < c->frames.size(); i++) release_slot(c, (int)i);
+  return 0;
+}
+
+int vslamb200_frame_dims(vslamb200_ctx * c, uint64_t id, int level, int * d)
+{
+  if (!c || !d) return fail(VSLAMB200_EINVAL, "frame_dims: null argument");
+  auto it = c->idToSlot.find(id);
+  if (it == c->idToSlot.end()) return fail(VSLAMB200_ENOFRAME, "frame_dims: unknown frame id");
+  const vb::FrameDev & f = c->frames[it->second].dev;
+  if (level < 0 || level >= f.nLevels) return fail(VSLAMB200_EINVAL, "frame_dims: no such level");
+  d[0] = f.W[level];
+  d[1] = f.H[level];
+  d[2] = f.Wd[level];
+  d[3] = f.Hd[level];
+  return 0;
+}
+
+int vslamb200_frame_download(
+  vslamb200_ctx * c, uint64_t id, int level, uint8_t * I, float * Z, float * Zsf, int16_t * gx, int16_t * gy)
+{
+  if (!c) return fail(VSLAMB200_EINVAL, "ctx is null");
+  auto it = c->idToSlot.find(id);
+  if (it == c->idToSlot.end()) return fail(VSLAMB200_ENOFRAME, "frame_download: unknown frame id");
+  const vb::FrameDev & f = c->frames[it->second].dev;
+  if (level < 0 || level >= f.nLevels) return fail(VSLAMB200_EINVAL, "frame_download: no such level");
+  CK(cudaSetDevice(c->device));
+  const size_t n = (size_t)f.W[level] * f.H[level], nd = (size_t)f.Wd[level] * f.Hd[level];
+  if (I) CK(cudaMemcpyAsync(I, f.I[level], n, cudaMemcpyDeviceToHost, c->stream));
+  if (Z) CK(cudaMemcpyAsync(Z, f.Z[level], nd * 4, cudaMemcpyDeviceToHost, c->stream));
+  if (Zsf) CK(cudaMemcpyAsync(Zsf, f.Zsf[level], nd * 4, cudaMemcpyDeviceToHost, c->stream));
+  if (gx) CK(cudaMemcpyAsync(gx, f.gx[level], n * 2, cudaMemcpyDeviceToHost, c->stream));
+  if (gy) CK(cudaMemcpyAsync(gy, f.gy[level], n * 2, cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+}  // extern "C"
+
+// ------------------------------------------------------------------------------------------------
+// batched alignment driver
+// ------------------------------------------------------------------------------------------------
+namespace
+{
+vb::Pose to_pose(const double * p)
+{
+  vb::Pose o;
+  for (int i = 0; i < 4; i++) o.q[i] = p[i];
+  for (int i = 0; i < 3; i++) o.t[i] = p[4 + i];
+  return o;
+}
+
+vb::SolverParams solver_params(const vslamb200_config & cfg)
+{
+  vb::SolverParams p;
+  p.minGradient2 = cfg.min_gradient * cfg.min_gradient;  // SE3Alignment.cpp:54
+  p.lossKind = cfg.loss_kind;
+  p.huberC = cfg.huber_c;
+  p.lossV = cfg.loss_v;
+  p.scalerKind = cfg.loss_kind == VSLAMB200_LOSS_NONE ? VSLAMB200_SCALER_IDENTITY : cfg.scaler_kind;
+  p.scalerV = cfg.scaler_v;
+  p.minStepSize = cfg.min_step_size;
+  p.maxIterations = cfg.max_iterations;
+  p.includePrior = cfg.include_prior;
+  return p;
+}
+
+struct Problem
+{
+  std::vector<vb::JobState> jobs;
+  std::vector<vb::ViewState> views;
+  int W = 0, H = 0, nLevels = 0;
+  vb::FrameDev geo;
+};
+
+// validate the jobs, build host-side job / view tables
+int build_problem(vslamb200_ctx * c, const vslamb200_job * jobs, int nJobs, Problem & P)
+{
+  if (!jobs || nJobs <= 0) return fail(VSLAMB200_EINVAL, "align: no jobs");
+  P.jobs.resize(nJobs);
+  bool first = true;
+  for (int j = 0; j < nJobs; j++) {
+    const vslamb200_job & in = jobs[j];
+    if (in.n_from < 1 || in.n_from > vb::MAX_VIEWS || !in.from || !in.from_poses)
+      return fail(VSLAMB200_EINVAL, "align: n_from out of range or null keyframe list");
+    if (!in.multi && in.n_from != 1) return fail(VSLAMB200_EINVAL, "align: single-frame overload takes one keyframe");
+    auto itTo = c->idToSlot.find(in.to);
+    if (itTo == c->idToSlot.end()) return fail(VSLAMB200_ENOFRAME, "align: unknown target frame id");
+    vb::JobState J;
+    std::memset(&J, 0, sizeof(J));
+    J.nViews = in.n_from;
+    J.view0 = (int)P.views.size();
+    J.multi = in.multi ? 1 : 0;
+    J.toPose = to_pose(in.to_pose);
+    J.pose = J.toPose;
+    for (int i = 0; i < 36; i++) J.cov[i] = (i % 7 == 0) ? 1.0 : 0.0;
+    const vb::FrameDev & ft = c->frames[itTo->second].dev;
+    for (int k = 0; k < in.n_from; k++) {
+      auto itF = c->idToSlot.find(in.from[k]);
+      if (itF == c->idToSlot.end()) return fail(VSLAMB200_ENOFRAME, "align: unknown keyframe id");
+      const vb::FrameDev & ff = c->frames[itF->second].dev;
+      if (first) {
+        P.geo = ff;
+        P.W = ff.W[0];
+        P.H = ff.H[0];
+        P.nLevels = ff.nLevels;
+        first = false;
+      }
+      for (const vb::FrameDev * f : {&ff, &ft}) {
+        if (f->nLevels != P.nLevels || f->W[0] != P.W || f->H[0] != P.H)
+          return fail(VSLAMB200_EINVAL, "align: all frames of one call must share size and pyramid depth");
+      }
+      vb::ViewState V;
+      std::memset(&V, 0, sizeof(V));
+      V.job = j;
+      V.fromSlot = itF->second;
+      V.toSlot = itTo->second;
+      V.poseRef = to_pose(in.from_poses + 7 * k);
+      P.views.push_back(V);
+    }
+    J.nLevels = P.nLevels;
+    P.jobs[j] = J;
+  }
+  // the reference indexes the point cloud (depth dims) with the intensity width; at odd sizes the
+  // two pyramids disagree and the reference is ill-defined
+  for (int l = 0; l < P.nLevels; l++)
+    if (P.geo.W[l] != P.geo.Wd[l] || P.geo.H[l] != P.geo.Hd[l])
+      return fail(VSLAMB200_EDIMS, "align: intensity and depth pyramid sizes disagree (image size not divisible by 2^(levels-1))");
+  return 0;
+}
+
+int pick_chunk(long points)
+{
+  // enough blocks to fill 148 SMs several times over, as few partial sums as possible
+  const long target = 148L * 16;
+  for (int chunk : {4096, 2048, 1024}) {
+    if (points / chunk >= target) return chunk;
+  }
+  return 512;
+}
+
+int run_level(vslamb200_ctx * c, Problem & P, int level, const vb::SolverParams & sp, int maxIterOverride = -1)
+{
+  const int nJobs = (int)P.jobs.size(), nViews = (int)P.views.size();
+  const int npx = P.geo.W[level] * P.geo.H[level];
+  const int listChunks = vb::list_chunks_for(npx);
+  const int chunk = pick_chunk((long)npx * nViews / 2);
+  const int partialStride = (P.geo.W[0] * P.geo.H[0] + 511) / 512;
+  vb::JobState * dJobs = c->jobs.as<vb::JobState>();
+  vb::ViewState * dViews = c->views.as<vb::ViewState>();
+  const vb::FrameDev * table = c->dFrames.as<vb::FrameDev>();
+  int * dActive = c->active.as<int>();
+  int * dCounts = c->counts.as<int>();
+  double * dTrace = c->traceEnabled ? c->trace.as<double>() : nullptr;
+  const size_t traceJobStride = (size_t)P.nLevels * sp.maxIterations * vb::TRACE_STRIDE;
+
+  vb::launch_level_setup(table, dJobs, dViews, nViews, level, c->stream);
+  vb::launch_build_lists(table, dViews, dJobs, nViews, level, npx, sp.minGradient2, chunk, c->chunkCounts.as<int>(),
+                         listChunks, c->stream);
+  vb::launch_level_begin(dJobs, dViews, nJobs, level, c->stream);
+  vb::launch_compact_active(dJobs, dViews, nViews, dActive, dCounts, c->stream);
+  c->stats.kernel_launches += 6;
+  CK(cudaMemcpyAsync(c->hCounts, dCounts, 8 * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  const int maxIter = maxIterOverride > 0 ? maxIterOverride : sp.maxIterations;
+  for (int it = 0; it < maxIter && c->hCounts[0] > 0; it++) {
+    const int nActive = c->hCounts[0], maxChunks = c->hCounts[2];
+    const uint64_t pts = (uint64_t)(uint32_t)c->hCounts[3] | ((uint64_t)(uint32_t)c->hCounts[4] << 32);
+    if (c->timing) CK(cudaEventRecord(c->ev[0], c->stream));
+    vb::launch_residual(dViews, dActive, nActive, maxChunks, chunk, sp, c->stream);
+    if (c->timing) CK(cudaEventRecord(c->ev[1], c->stream));
+    vb::launch_accumulate(dJobs, dViews, dActive, nActive, maxChunks, chunk, c->partials.as<double>(), partialStride,
+                          sp, level, dTrace, traceJobStride, c->stream);
+    if (c->timing) CK(cudaEventRecord(c->ev[2], c->stream));
+    vb::launch_compact_active(dJobs, dViews, nViews, dActive, dCounts, c->stream);
+    c->stats.kernel_launches += 3;
+    c->stats.pixel_iterations += (uint64_t)nActive * npx;
+    c->stats.point_iterations += pts;
+    c->stats.gn_iterations += c->hCounts[1];
+    CK(cudaMemcpyAsync(c->hCounts, dCounts, 8 * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    if (c->timing) {
+      float a = 0, b = 0;
+      CK(cudaEventElapsedTime(&a, c->ev[0], c->ev[1]));
+      CK(cudaEventElapsedTime(&b, c->ev[1], c->ev[2]));
+      c->stats.ms_residual += a;
+      c->stats.ms_accumulate += b;
+    }
+  }
+  CK(cudaGetLastError());
+  return 0;
+}
+
+int prepare_workspace(vslamb200_ctx * c, Problem & P, const vb::SolverParams & sp)
+{
+  const int nJobs = (int)P.jobs.size(), nViews = (int)P.views.size();
+  const size_t npx0 = (size_t)P.W * P.H;
+  const size_t listStride = align_up(npx0, 64);
+  CK(c->lists.ensure(listStride * 14 * nViews));
+  CK(c->hist.ensure((size_t)nViews * vb::HIST_BINS * sizeof(int), true));
+  CK(cudaMemsetAsync(c->hist.p, 0, (size_t)nViews * vb::HIST_BINS * sizeof(int), c->stream));
+  CK(c->wlut.ensure((size_t)nViews * vb::HIST_BINS * sizeof(float)));
+  CK(c->active.ensure((size_t)nViews * sizeof(int)));
+  CK(c->counts.ensure(64));
+  CK(c->chunkCounts.ensure((size_t)nViews * vb::list_chunks_for((int)npx0) * sizeof(int)));
+  const size_t partialStride = (npx0 + 511) / 512;
+  CK(c->partials.ensure((size_t)nViews * partialStride * vb::NE_TERMS * sizeof(double)));
+  uint8_t * base = c->lists.as<uint8_t>();
+  for (int v = 0; v < nViews; v++) {
+    vb::ViewState & V = P.views[v];
+    uint8_t * b = base + (size_t)v * listStride * 14;
+    V.uvt = (uint32_t *)b;
+    V.d = (float *)(b + listStride * 4);
+    V.g = (uint32_t *)(b + listStride * 8);
+    V.r = (int16_t *)(b + listStride * 12);
+    V.hist = c->hist.as<int>() + (size_t)v * vb::HIST_BINS;
+    V.wlut = c->wlut.as<float>() + (size_t)v * vb::HIST_BINS;
+  }
+  CK(c->jobs.ensure(nJobs * sizeof(vb::JobState)));
+  CK(c->views.ensure(nViews * sizeof(vb::ViewState)));
+  CK(cudaMemcpyAsync(c->jobs.p, P.jobs.data(), nJobs * sizeof(vb::JobState), cudaMemcpyHostToDevice, c->stream));
+  CK(cudaMemcpyAsync(c->views.p, P.views.data(), nViews * sizeof(vb::ViewState), cudaMemcpyHostToDevice, c->stream));
+  if (c->traceEnabled) {
+    const size_t bytes = (size_t)nJobs * P.nLevels * sp.maxIterations * vb::TRACE_STRIDE * sizeof(double);
+    CK(c->trace.ensure(bytes));
+    CK(cudaMemsetAsync(c->trace.p, 0, bytes, c->stream));
+    c->traceJobs = nJobs;
+    c->traceLevels = P.nLevels;
+    c->traceMaxIter = sp.maxIterations;
+  }
+  return 0;
+}
+}  // namespace
+
+extern "C" {
+
+int vslamb200_align(vslamb200_ctx * c, const vslamb200_job * jobs, int nJobs, vslamb200_result * out)
+{
+  if (!c || !out) return fail(VSLAMB200_EINVAL, "align: null argument");
+  CK(cudaSetDevice(c->device));
+  Problem P;
+  if (int e = build_problem(c, jobs, nJobs, P)) return e;
+  const vb::SolverParams sp = solver_params(c->cfg);
+  if (int e = prepare_workspace(c, P, sp)) return e;
+  for (int level = P.nLevels - 1; level >= 0; level--)
+    if (int e = run_level(c, P, level, sp)) return e;
+  CK(cudaMemcpyAsync(P.jobs.data(), c->jobs.p, nJobs * sizeof(vb::JobState), cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  c->stats.d2h_bytes += (uint64_t)nJobs * sizeof(vb::JobState);
+  for (int j = 0; j < nJobs; j++) {
+    const vb::JobState & J = P.jobs[j];
+    vslamb200_result & r = out[j];
+    for (int i = 0; i < 4; i++) r.pose[i] = J.pose.q[i];
+    for (int i = 0; i < 3; i++) r.pose[4 + i] = J.pose.t[i];
+    std::memcpy(r.cov, J.cov, sizeof(r.cov));
+    r.status = J.status;
+    for (int l = 0; l < VSLAMB200_MAX_LEVELS; l++) {
+      r.iters[l] = l < P.nLevels ? J.iters[l] : 0;
+      r.stop[l] = l < P.nLevels ? J.stop[l] : 0;
+    }
+  }
+  return 0;
+}
+
+int vslamb200_set_trace(vslamb200_ctx * c, int enable)
+{
+  if (!c) return fail(VSLAMB200_EINVAL, "ctx is null");
+  c->traceEnabled = enable ? 1 : 0;
+  return 0;
+}
+
+int vslamb200_get_trace(vslamb200_ctx * c, int job, double * out)
+{
+  if (!c || !out) return fail(VSLAMB200_EINVAL, "get_trace: null argument");
+  if (!c->trace.p || job < 0 || job >= c->traceJobs) return fail(VSLAMB200_EINVAL, "get_trace: no trace for that job");
+  CK(cudaSetDevice(c->device));
+  const size_t n = (size_t)c->traceLevels * c->traceMaxIter * vb::TRACE_STRIDE;
+  CK(cudaMemcpy(out, c->trace.as<double>() + n * job, n * sizeof(double), cudaMemcpyDeviceToHost));
+  return 0;
+}
+
+int vslamb200_evaluate(
+  vslamb200_ctx * c, uint64_t from, uint64_t to, int level, const double * se3, int multiMask, int16_t * rcode,
+  double * ne64)
+{
+  if (!c || !se3) return fail(VSLAMB200_EINVAL, "evaluate: null argument");
+  CK(cudaSetDevice(c->device));
+  const double ident[7] = {0, 0, 0, 1, 0, 0, 0};
+  vslamb200_job job;
+  job.to = to;
+  std::memcpy(job.to_pose, se3, sizeof(job.to_pose));
+  job.n_from = 1;
+  job.multi = multiMask ? 1 : 0;
+  job.from = &from;
+  job.from_poses = ident;
+  Problem P;
+  if (int e = build_problem(c, &job, 1, P)) return e;
+  if (level < 0 || level >= P.nLevels) return fail(VSLAMB200_EINVAL, "evaluate: no such level");
+  vb::SolverParams sp = solver_params(c->cfg);
+  sp.includePrior = 0;
+  const int savedTrace = c->traceEnabled;
+  c->traceEnabled = 0;
+  int e = prepare_workspace(c, P, sp);
+  c->traceEnabled = savedTrace;
+  if (e) return e;
+  // one iteration with the warp forced to exactly the caller's transform
+  const int nViews = 1, nJobs = 1;
+  const int npx = P.geo.W[level] * P.geo.H[level];
+  const int chunk = 512;
+  const int partialStride = (P.W * P.H + 511) / 512;
+  vb::JobState * dJobs = c->jobs.as<vb::JobState>();
+  vb::ViewState * dViews = c->views.as<vb::ViewState>();
+  const vb::FrameDev * table = c->dFrames.as<vb::FrameDev>();
+  vb::launch_level_setup(table, dJobs, dViews, nViews, level, c->stream);
+  vb::launch_build_lists(table, dViews, dJobs, nViews, level, npx, sp.minGradient2, chunk, c->chunkCounts.as<int>(),
+                         vb::list_chunks_for(npx), c->stream);
+  vb::launch_level_begin(dJobs, dViews, nJobs, level, c->stream);
+  vb::ViewState V;
+  CK(cudaMemcpyAsync(&V, dViews, sizeof(V), cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  V.se3 = to_pose(se3);
+  vb::quat_to_R(V.se3.q, V.R);
+  for (int i = 0; i < 3; i++) V.t[i] = V.se3.t[i];
+  CK(cudaMemcpyAsync(dViews, &V, sizeof(V), cudaMemcpyHostToDevice, c->stream));
+  const int zero = 0;
+  CK(c->active.ensure(sizeof(int)));
+  CK(cudaMemcpyAsync(c->active.p, &zero, sizeof(int), cudaMemcpyHostToDevice, c->stream));
+  vb::launch_residual(dViews, c->active.as<int>(), 1, V.nChunks, chunk, sp, c->stream);
+  vb::launch_accumulate(dJobs, dViews, c->active.as<int>(), 1, V.nChunks, chunk, c->partials.as<double>(), partialStride,
+                        sp, level, nullptr, 0, c->stream);
+  c->stats.kernel_launches += 7;
+  if (rcode) {
+    CK(c->plane.ensure((size_t)npx * 2));
+    vb::launch_scatter_rcode(dViews, 0, c->plane.as<int16_t>(), c->stream);
+    CK(cudaMemcpyAsync(rcode, c->plane.p, (size_t)npx * 2, cudaMemcpyDeviceToHost, c->stream));
+  }
+  std::vector<double> part((size_t)std::max(V.nChunks, 1) * vb::NE_TERMS, 0.0);
+  if (V.nChunks > 0)
+    CK(cudaMemcpyAsync(part.data(), c->partials.p, (size_t)V.nChunks * vb::NE_TERMS * sizeof(double),
+                       cudaMemcpyDeviceToHost, c->stream));
+  vb::ViewState V2;
+  CK(cudaMemcpyAsync(&V2, dViews, sizeof(V2), cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  CK(cudaGetLastError());
+  if (ne64) {
+    double s[vb::NE_TERMS] = {0};
+    for (int ch = 0; ch < V.nChunks; ch++)
+      for (int k = 0; k < vb::NE_TERMS; k++) s[k] += part[(size_t)ch * vb::NE_TERMS + k];
+    const double n = (double)V.nIp;
+    if (V.nIp > 1)
+      for (double & x : s) x /= n;
+    std::memset(ne64, 0, 64 * sizeof(double));
+    ne64[0] = n;
+    ne64[1] = s[27];
+    ne64[2] = V2.scale;
+    ne64[3] = V2.offset;
+    for (int i = 0; i < 6; i++) ne64[4 + i] = s[21 + i];
+    int idx = 0;
+    for (int i = 0; i < 6; i++)
+      for (int j = i; j < 6; j++) {
+        ne64[10 + i * 6 + j] = s[idx];
+        ne64[10 + j * 6 + i] = s[idx++];
+      }
+  }
+  return 0;
+}
+
+int vslamb200_get_stats(vslamb200_ctx * c, vslamb200_stats * out)
+{
+  if (!c || !out) return fail(VSLAMB200_EINVAL, "get_stats: null argument");
+  *out = c->stats;
+  return 0;
+}
+int vslamb200_reset_stats(vslamb200_ctx * c)
+{
+  if (!c) return fail(VSLAMB200_EINVAL, "ctx is null");
+  std::memset(&c->stats, 0, sizeof(c->stats));
+  return 0;
+}
+int vslamb200_set_timing(vslamb200_ctx * c, int enable)
+{
+  if (!c) return fail(VSLAMB200_EINVAL, "ctx is null");
+  c->timing = enable ? 1 : 0;
+  return 0;
+}
+
+}  // extern "C"

@@ -46,8 +46,7 @@ struct ViewState
   const uint8_t * I;        // target intensity(level)
   double fx, fy, cx, cy;    // projection intrinsics (_camCur = from->camera(level), Warp.cpp:136-137)
   double ifx, ify, kx, ky;  // analytic K^-1 of the keyframe camera (Camera.cpp:32-35)
-  float fxJ, fyJ;           // Jacobian scale (_camRef = to->camera(level), Warp.cpp:198-199)
-  float ifx32, ify32, kx32, ky32;
+  double fxJd, fyJd;        // Jacobian scale (_camRef = to->camera(level), Warp.cpp:198-199)
   // interest list (SoA)
   uint32_t * uvt;           // u | v<<12 | T<<24
   float * d;                // depth of the point
