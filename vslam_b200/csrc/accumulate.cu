@@ -148,6 +148,12 @@ void launch_accumulate(JobState * jobs, ViewState * views, const int * activeVie
 // ------------------------------------------------------------------------------------------------
 // per-level bookkeeping
 // ------------------------------------------------------------------------------------------------
+__device__ inline void split_hi_lo(double v, float & hi, float & lo)
+{
+  hi = (float)v;
+  lo = (float)(v - (double)hi);
+}
+
 // one thread per view: static fields of the level, warp = pose * poseRef^-1 (Warp.cpp:135-147), prior
 __global__ void level_setup_kernel(
   const FrameDev * __restrict__ frames, JobState * __restrict__ jobs, ViewState * __restrict__ views, int nViews,
@@ -174,6 +180,14 @@ __global__ void level_setup_kernel(
   V.ky = -V.cy / V.fy;
   V.fxJd = ft.cam[level][0];
   V.fyJd = ft.cam[level][1];
+  split_hi_lo(V.ifx, V.ifxH, V.ifxL);
+  split_hi_lo(V.ify, V.ifyH, V.ifyL);
+  split_hi_lo(V.kx, V.kxH, V.kxL);
+  split_hi_lo(V.ky, V.kyH, V.kyL);
+  split_hi_lo(V.fxJd, V.fxJH, V.fxJL);
+  split_hi_lo(V.fyJd, V.fyJH, V.fyJL);
+  V.fx32 = (float)V.fx;
+  V.fy32 = (float)V.fy;
   V.nIp = 0;
   V.nChunks = 0;
   V.ticketA = 0;

@@ -134,8 +134,33 @@ __device__ void scale_and_weights(ViewState & V, const SolverParams & p, int * h
   if (tid < 255) V.wlut[tid + 256] = (float)loss_weight(p, (r1 - offset) / scale);
 }
 
+// Exact warp of one interest point, operation for operation the oracle's (fp64, explicit fma):
+// Camera::image2camera (Camera.cpp:32-35), se3 * p (Warp.cpp:160-161), Camera::camera2image
+// (Camera.cpp:23-30), visibility (InverseCompositional.cpp:115-116), std::round.
+__device__ __noinline__ int warp_exact(const ViewState & V, int u, int v, float df)
+{
+  const double d = (double)df;
+  const double X = __fma_rn(V.kx, d, __dmul_rn(V.ifx, __dmul_rn((double)u, d)));
+  const double Y = __fma_rn(V.ky, d, __dmul_rn(V.ify, __dmul_rn((double)v, d)));
+  const double qx = __fma_rn(V.R[2], d, __fma_rn(V.R[1], Y, __fma_rn(V.R[0], X, V.t[0])));
+  const double qy = __fma_rn(V.R[5], d, __fma_rn(V.R[4], Y, __fma_rn(V.R[3], X, V.t[1])));
+  const double qz = __fma_rn(V.R[8], d, __fma_rn(V.R[7], Y, __fma_rn(V.R[6], X, V.t[2])));
+  if (!(qz > 0.0)) return -1;
+  const double up = __ddiv_rn(__fma_rn(V.fx, qx, __dmul_rn(V.cx, qz)), qz);
+  const double vp = __ddiv_rn(__fma_rn(V.fy, qy, __dmul_rn(V.cy, qz)), qz);
+  if (!(1.0 < up && up < (double)(V.Wt - 1) && 1.0 < vp && vp < (double)(V.Ht - 1) && isfinite(up))) return -1;
+  // std::round (half away from zero) of a positive value == floor(x + 0.5)
+  return __double2int_rd(vp + 0.5) * V.Wt + __double2int_rd(up + 0.5);
+}
+
+// Residual kernel.  The sampled pixel index and the visibility flag are integer decisions, and they must
+// be the fp64 oracle's.  A filtered evaluation gets them without fp64 in the common case: in exact
+// arithmetic u' = u + fx*(Dx - xn*Dz)/(z + Dz) with D = (R - I) p + t, because p was back-projected from
+// the integer pixel (u, v).  The displacement is small, so fp32 carries it with an absolute error far
+// below a pixel; only when it lands within the error bound eps of a rounding (k + 0.5) or visibility
+// (integer) boundary is the point re-evaluated by warp_exact().
 template <int PPT>
-__global__ void __launch_bounds__(THREADS) residual_kernel(
+__global__ void __launch_bounds__(THREADS, 4) residual_kernel(
   ViewState * __restrict__ views, const int * __restrict__ activeViews, SolverParams p)
 {
   ViewState & V = views[activeViews[blockIdx.y]];
@@ -148,13 +173,12 @@ __global__ void __launch_bounds__(THREADS) residual_kernel(
   hist[tid + 256] = 0;
   __syncthreads();
 
-  const double R0 = V.R[0], R1 = V.R[1], R2 = V.R[2], R3 = V.R[3], R4 = V.R[4], R5 = V.R[5], R6 = V.R[6],
-               R7 = V.R[7], R8 = V.R[8];
-  const double t0 = V.t[0], t1 = V.t[1], t2 = V.t[2];
-  const double fx = V.fx, fy = V.fy, cx = V.cx, cy = V.cy;
-  const double ifx = V.ifx, ify = V.ify, kx = V.kx, ky = V.ky;
-  const double umax = (double)(V.Wt - 1), vmax = (double)(V.Ht - 1);
-  const int Wt = V.Wt;
+  const float r00 = V.rI[0], r01 = V.rI[1], r02 = V.rI[2], r10 = V.rI[3], r11 = V.rI[4], r12 = V.rI[5],
+              r20 = V.rI[6], r21 = V.rI[7], r22 = V.rI[8];
+  const float t0 = V.t32[0], t1 = V.t32[1], t2 = V.t32[2];
+  const float fx = V.fx32, fy = V.fy32, ifx = V.ifxH, ify = V.ifyH, kx = V.kxH, ky = V.kyH;
+  const float epsA = V.epsA, epsB = V.epsB;
+  const int Wt = V.Wt, Ht = V.Ht;
   const uint8_t * __restrict__ I = V.I;
   const uint32_t * __restrict__ uvt = V.uvt;
   const float * __restrict__ dep = V.d;
@@ -163,33 +187,40 @@ __global__ void __launch_bounds__(THREADS) residual_kernel(
   const int base = blockIdx.x * (THREADS * PPT);
   const bool needHist = p.lossKind != VSLAMB200_LOSS_NONE;
 
-#pragma unroll
+#pragma unroll 4
   for (int k = 0; k < PPT; k++) {
     const int idx = base + k * THREADS + tid;
     if (idx < nIp) {
       const uint32_t pk = __ldg(uvt + idx);
-      const double d = (double)__ldg(dep + idx);
+      const float d = __ldg(dep + idx);
       const int u = pk & 0xfff, v = (pk >> 12) & 0xfff, T = pk >> 24;
-      // Camera::image2camera (Camera.cpp:32-35), same operation order as the oracle
-      const double X = __fma_rn(kx, d, __dmul_rn(ifx, __dmul_rn((double)u, d)));
-      const double Y = __fma_rn(ky, d, __dmul_rn(ify, __dmul_rn((double)v, d)));
-      // se3 * p (Warp.cpp:160-161)
-      const double qx = __fma_rn(R2, d, __fma_rn(R1, Y, __fma_rn(R0, X, t0)));
-      const double qy = __fma_rn(R5, d, __fma_rn(R4, Y, __fma_rn(R3, X, t1)));
-      const double qz = __fma_rn(R8, d, __fma_rn(R7, Y, __fma_rn(R6, X, t2)));
+      const float xn = fmaf((float)u, ifx, kx), yn = fmaf((float)v, ify, ky);
+      const float px = xn * d, py = yn * d;
+      const float Dx = fmaf(r02, d, fmaf(r01, py, fmaf(r00, px, t0)));
+      const float Dy = fmaf(r12, d, fmaf(r11, py, fmaf(r10, px, t1)));
+      const float Dz = fmaf(r22, d, fmaf(r21, py, fmaf(r20, px, t2)));
+      const float qz = d + Dz;
+      const float iz = __frcp_rn(qz);
+      const float du = fx * fmaf(-xn, Dz, Dx) * iz;
+      const float dv = fy * fmaf(-yn, Dz, Dy) * iz;
+      // distance of the displacement to the nearest multiple of 0.5 (rounding and visibility boundaries)
+      const float fu = du + du, fv = dv + dv;
+      const float distu = 0.5f * fabsf(fu - rintf(fu)), distv = 0.5f * fabsf(fv - rintf(fv));
+      const float eps = fmaf(epsA, d, epsB) * fabsf(iz) + 3.8e-6f * (fabsf(du) + fabsf(dv)) + 6.1e-5f;
+      int pix;
+      if (!(qz > 0.25f * d) || !(fminf(distu, distv) > eps) || !(fabsf(du) + fabsf(dv) < 4096.f)) {
+        pix = warp_exact(V, u, v, d);
+      } else {
+        // boundaries are integers: compare the displacement with exact integer offsets
+        const bool vis = du > (float)(1 - u) && du < (float)(Wt - 1 - u) && dv > (float)(1 - v) && dv < (float)(Ht - 1 - v);
+        const int iu = u + __float2int_rd(du + 0.5f), iv = v + __float2int_rd(dv + 0.5f);
+        pix = vis ? iv * Wt + iu : -1;
+      }
       int16_t rr = R_INVISIBLE;
-      if (qz > 0.0) {
-        // Camera::camera2image (Camera.cpp:23-30)
-        const double up = __ddiv_rn(__fma_rn(fx, qx, __dmul_rn(cx, qz)), qz);
-        const double vp = __ddiv_rn(__fma_rn(fy, qy, __dmul_rn(cy, qz)), qz);
-        // InverseCompositional.cpp:115-116
-        if (1.0 < up && up < umax && 1.0 < vp && vp < vmax && isfinite(up)) {
-          // std::round (half away from zero) of a positive value == floor(x + 0.5)
-          const int iu = __double2int_rd(up + 0.5), iv = __double2int_rd(vp + 0.5);
-          const int r = (int)__ldg(I + (size_t)iv * Wt + iu) - T;
-          rr = (int16_t)r;
-          if (needHist) atomicAdd(&hist[r + 255], 1);
-        }
+      if (pix >= 0) {
+        const int r = (int)__ldg(I + pix) - T;
+        rr = (int16_t)r;
+        if (needHist) atomicAdd(&hist[r + 255], 1);
       }
       rout[idx] = rr;
     }

@@ -7,7 +7,7 @@
 #include <unordered_map>
 #include <vector>
 
-#include "common.cuh"
+#include "solve.cuh"
 
 namespace
 {
@@ -739,8 +739,7 @@ int vslamb200_evaluate(
   CK(cudaMemcpyAsync(&V, dViews, sizeof(V), cudaMemcpyDeviceToHost, c->stream));
   CK(cudaStreamSynchronize(c->stream));
   V.se3 = to_pose(se3);
-  vb::quat_to_R(V.se3.q, V.R);
-  for (int i = 0; i < 3; i++) V.t[i] = V.se3.t[i];
+  vb::view_set_warp(V);
   CK(cudaMemcpyAsync(dViews, &V, sizeof(V), cudaMemcpyHostToDevice, c->stream));
   const int zero = 0;
   CK(c->active.ensure(sizeof(int)));

@@ -47,6 +47,9 @@ struct ViewState
   double fx, fy, cx, cy;    // projection intrinsics (_camCur = from->camera(level), Warp.cpp:136-137)
   double ifx, ify, kx, ky;  // analytic K^-1 of the keyframe camera (Camera.cpp:32-35)
   double fxJd, fyJd;        // Jacobian scale (_camRef = to->camera(level), Warp.cpp:198-199)
+  // fp32 hi/lo splits of the fp64 constants: keeps the fp32 Jacobian free of coherent rounding bias
+  float ifxH, ifxL, ifyH, ifyL, kxH, kxL, kyH, kyL, fxJH, fxJL, fyJH, fyJL;
+  float fx32, fy32;
   // interest list (SoA)
   uint32_t * uvt;           // u | v<<12 | T<<24
   float * d;                // depth of the point
@@ -58,6 +61,9 @@ struct ViewState
   Pose poseRef;             // keyframe pose
   Pose se3;                 // poseCur * poseRef^-1
   double R[9], t[3];        // rotation matrix / translation of se3 for the residual kernel
+  // fp32 fast path of the residual kernel (displacement form, see align_kernels.cu)
+  float rI[9], t32[3];      // R - I and t rounded to fp32
+  float epsA, epsB;         // per-view terms of the fast-path error bound
   double xPred[6];          // MotionPrior::_xPred (SE3Alignment.cpp:32)
   // robust weights of the current iteration
   int * hist;               // HIST_BINS global bins

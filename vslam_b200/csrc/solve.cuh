@@ -92,12 +92,26 @@ __device__ inline void inverse6(const double * A, double * out)
     for (int j = 0; j < 6; j++) out[i * 6 + j] = m[i][6 + j];
 }
 
-__device__ inline void view_set_warp(ViewState & V)
+__host__ __device__ inline void view_set_warp(ViewState & V)
 {
   quat_to_R(V.se3.q, V.R);
   V.t[0] = V.se3.t[0];
   V.t[1] = V.se3.t[1];
   V.t[2] = V.se3.t[2];
+  double rImax = 0.0, tmax = 0.0;
+  for (int i = 0; i < 9; i++) {
+    const double d = V.R[i] - ((i % 4 == 0) ? 1.0 : 0.0);
+    V.rI[i] = (float)d;
+    rImax = fmax(rImax, fabs(d));
+  }
+  for (int i = 0; i < 3; i++) {
+    V.t32[i] = (float)V.t[i];
+    tmax = fmax(tmax, fabs(V.t[i]));
+  }
+  // fast-path error bound: eps = epsA*d/qz + epsB/qz + ... (derivation in DESIGN.md, "filtered warp")
+  const double u128 = 128.0 / 16777216.0, fmx = fmax(V.fx, V.fy);
+  V.epsA = (float)(u128 * fmx * rImax * 4.25);
+  V.epsB = (float)(u128 * fmx * tmax * 1.7);
 }
 
 // End of a level's solve: covariance and pose hand-off (SE3Alignment.cpp:100-102)
@@ -121,7 +135,7 @@ __device__ inline void finish_level(JobState & J, ViewState * views, int level, 
 
 // One GaussNewton::solve iteration (GaussNewton.cpp:44-99) on the stacked, normalised, prior-augmented
 // normal equations.  sums: per view 28 raw terms (21 upper A, 6 b, chi2), view-major.
-__device__ __noinline__ void gn_step(
+static __device__ __noinline__ void gn_step(
   JobState & J, ViewState * views, const double * sums, const SolverParams & p, int level, double * trace)
 {
   double A[36], b[6], chi2 = 0.0;
