@@ -90,7 +90,9 @@ typedef struct vslamb200_stats
   uint64_t gn_iterations;        /* Gauss-Newton iterations over all jobs and levels */
   uint64_t frames_uploaded;
   uint64_t h2d_bytes, d2h_bytes;
-  double ms_residual, ms_accumulate, ms_preprocess, ms_lists;  /* filled only when timing is enabled */
+  /* filled only when timing is enabled: interest-list construction and the Gauss-Newton level kernel per level */
+  double ms_lists, ms_preprocess, ms_gn_level[VSLAMB200_MAX_LEVELS];
+  uint64_t pixel_iterations_level[VSLAMB200_MAX_LEVELS];  /* pixel_iterations split by pyramid level */
 } vslamb200_stats;
 
 const char * vslamb200_last_error(void);

@@ -37,8 +37,9 @@ class Result(C.Structure):
 class Stats(C.Structure):
     _fields_ = [("kernel_launches", C.c_uint64), ("pixel_iterations", C.c_uint64),
                 ("point_iterations", C.c_uint64), ("gn_iterations", C.c_uint64), ("frames_uploaded", C.c_uint64),
-                ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64), ("ms_residual", C.c_double),
-                ("ms_accumulate", C.c_double), ("ms_preprocess", C.c_double), ("ms_lists", C.c_double)]
+                ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64), ("ms_lists", C.c_double),
+                ("ms_preprocess", C.c_double), ("ms_gn_level", C.c_double * MAX_LEVELS),
+                ("pixel_iterations_level", C.c_uint64 * MAX_LEVELS)]
 
 
 EXPORTS = [
@@ -215,7 +216,10 @@ class Context:
     def stats(self):
         s = Stats()
         check(lib().vslamb200_get_stats(self.h, C.byref(s)))
-        return {f[0]: getattr(s, f[0]) for f in Stats._fields_}
+        out = {f[0]: getattr(s, f[0]) for f in Stats._fields_}
+        out["ms_gn_level"] = list(out["ms_gn_level"])
+        out["pixel_iterations_level"] = list(out["pixel_iterations_level"])
+        return out
 
     def reset_stats(self):
         check(lib().vslamb200_reset_stats(self.h))

@@ -84,8 +84,7 @@ struct vslamb200_ctx
   DevBuf dFrames;  // FrameDev table
   DevBuf stageGray, stageDepth, slotsBuf;
   // alignment workspace
-  DevBuf jobs, views, active, counts, chunkCounts, partials, lists, hist, wlut, trace, plane;
-  int * hCounts = nullptr;  // pinned
+  DevBuf jobs, views, chunkCounts, partials, lists, trace, plane;
   int traceEnabled = 0, timing = 0;
   int traceJobs = 0, traceLevels = 0, traceMaxIter = 0;
   vslamb200_stats stats;
@@ -288,7 +287,7 @@ int vslamb200_create(const vslamb200_config * cfg, int device, vslamb200_ctx ** 
   c->cfg = *cfg;
   std::memset(&c->stats, 0, sizeof(c->stats));
   cudaError_t e1 = cudaStreamCreateWithFlags(&c->own, cudaStreamNonBlocking);
-  cudaError_t e2 = cudaMallocHost((void **)&c->hCounts, 16 * sizeof(int));
+  cudaError_t e2 = cudaSuccess;
   cudaError_t e3 = cudaEventCreate(&c->ev[0]);
   cudaError_t e4 = cudaEventCreate(&c->ev[1]);
   if (e4 == cudaSuccess) e4 = cudaEventCreate(&c->ev[2]);
@@ -308,10 +307,9 @@ void vslamb200_destroy(vslamb200_ctx * c)
   cudaStreamSynchronize(c->stream);
   for (auto & a : c->arenas)
     if (a.ptr) cudaFree(a.ptr);
-  DevBuf * bufs[] = {&c->dFrames, &c->stageGray, &c->stageDepth, &c->slotsBuf, &c->jobs, &c->views, &c->active,
-                     &c->counts, &c->chunkCounts, &c->partials, &c->lists, &c->hist, &c->wlut, &c->trace, &c->plane};
+  DevBuf * bufs[] = {&c->dFrames, &c->stageGray, &c->stageDepth, &c->slotsBuf, &c->jobs, &c->views,
+                     &c->chunkCounts, &c->partials, &c->lists, &c->trace, &c->plane};
   for (auto b : bufs) b->release();
-  if (c->hCounts) cudaFreeHost(c->hCounts);
   if (c->ev[0]) cudaEventDestroy(c->ev[0]);
   if (c->ev[1]) cudaEventDestroy(c->ev[1]);
   if (c->ev[2]) cudaEventDestroy(c->ev[2]);
@@ -549,65 +547,49 @@ int build_problem(vslamb200_ctx * c, const vslamb200_job * jobs, int nJobs, Prob
   return 0;
 }
 
-int pick_chunk(long points)
+// cluster size of a level's Gauss-Newton kernel: enough CTAs per job that a slice of the interest list is a few
+// ten thousand points (its residuals then stay in shared memory), never more than the portable maximum of 8
+int pick_cluster(int npx, int maxViewsPerJob)
 {
-  // enough blocks to fill 148 SMs several times over, as few partial sums as possible
-  const long target = 148L * 16;
-  for (int chunk : {4096, 2048, 1024}) {
-    if (points / chunk >= target) return chunk;
-  }
-  return 512;
+  (void)maxViewsPerJob;
+  if (npx > 160000) return 8;
+  if (npx > 40000) return 4;
+  if (npx > 12000) return 2;
+  return 1;
 }
 
-int run_level(vslamb200_ctx * c, Problem & P, int level, const vb::SolverParams & sp, int maxIterOverride = -1)
+int run_level(vslamb200_ctx * c, Problem & P, int level, const vb::SolverParams & sp, int maxEvals, bool residualsInHbm)
 {
   const int nJobs = (int)P.jobs.size(), nViews = (int)P.views.size();
   const int npx = P.geo.W[level] * P.geo.H[level];
   const int listChunks = vb::list_chunks_for(npx);
-  const int chunk = pick_chunk((long)npx * nViews / 2);
-  const int partialStride = (P.geo.W[0] * P.geo.H[0] + 511) / 512;
   vb::JobState * dJobs = c->jobs.as<vb::JobState>();
   vb::ViewState * dViews = c->views.as<vb::ViewState>();
   const vb::FrameDev * table = c->dFrames.as<vb::FrameDev>();
-  int * dActive = c->active.as<int>();
-  int * dCounts = c->counts.as<int>();
   double * dTrace = c->traceEnabled ? c->trace.as<double>() : nullptr;
   const size_t traceJobStride = (size_t)P.nLevels * sp.maxIterations * vb::TRACE_STRIDE;
+  const int cluster = pick_cluster(npx, 1);
+  const int maxPointsPerCta = (((npx + cluster - 1) / cluster) + 3) & ~3;
 
+  if (c->timing) CK(cudaEventRecord(c->ev[0], c->stream));
   vb::launch_level_setup(table, dJobs, dViews, nViews, level, c->stream);
-  vb::launch_build_lists(table, dViews, dJobs, nViews, level, npx, sp.minGradient2, chunk, c->chunkCounts.as<int>(),
-                         listChunks, c->stream);
+  vb::launch_build_lists(table, dViews, dJobs, nViews, level, npx, sp.minGradient2, c->chunkCounts.as<int>(), listChunks,
+                         c->stream);
   vb::launch_level_begin(dJobs, dViews, nJobs, level, c->stream);
-  vb::launch_compact_active(dJobs, dViews, nViews, dActive, dCounts, c->stream);
+  if (c->timing) CK(cudaEventRecord(c->ev[1], c->stream));
+  CK(vb::launch_gn_level(dJobs, dViews, nJobs, cluster, maxPointsPerCta, residualsInHbm, sp, level, maxEvals, dTrace,
+                         traceJobStride, c->partials.as<double>(), c->stream));
+  if (c->timing) CK(cudaEventRecord(c->ev[2], c->stream));
   c->stats.kernel_launches += 6;
-  CK(cudaMemcpyAsync(c->hCounts, dCounts, 8 * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
-  CK(cudaStreamSynchronize(c->stream));
-  const int maxIter = maxIterOverride > 0 ? maxIterOverride : sp.maxIterations;
-  for (int it = 0; it < maxIter && c->hCounts[0] > 0; it++) {
-    const int nActive = c->hCounts[0], maxChunks = c->hCounts[2];
-    const uint64_t pts = (uint64_t)(uint32_t)c->hCounts[3] | ((uint64_t)(uint32_t)c->hCounts[4] << 32);
-    if (c->timing) CK(cudaEventRecord(c->ev[0], c->stream));
-    vb::launch_residual(dViews, dActive, nActive, maxChunks, chunk, sp, c->stream);
-    if (c->timing) CK(cudaEventRecord(c->ev[1], c->stream));
-    vb::launch_accumulate(dJobs, dViews, dActive, nActive, maxChunks, chunk, c->partials.as<double>(), partialStride,
-                          sp, level, dTrace, traceJobStride, c->stream);
-    if (c->timing) CK(cudaEventRecord(c->ev[2], c->stream));
-    vb::launch_compact_active(dJobs, dViews, nViews, dActive, dCounts, c->stream);
-    c->stats.kernel_launches += 3;
-    c->stats.pixel_iterations += (uint64_t)nActive * npx;
-    c->stats.point_iterations += pts;
-    c->stats.gn_iterations += c->hCounts[1];
-    CK(cudaMemcpyAsync(c->hCounts, dCounts, 8 * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
-    CK(cudaStreamSynchronize(c->stream));
-    if (c->timing) {
-      float a = 0, b = 0;
-      CK(cudaEventElapsedTime(&a, c->ev[0], c->ev[1]));
-      CK(cudaEventElapsedTime(&b, c->ev[1], c->ev[2]));
-      c->stats.ms_residual += a;
-      c->stats.ms_accumulate += b;
-    }
-  }
   CK(cudaGetLastError());
+  if (c->timing) {
+    CK(cudaStreamSynchronize(c->stream));
+    float a = 0, b = 0;
+    CK(cudaEventElapsedTime(&a, c->ev[0], c->ev[1]));
+    CK(cudaEventElapsedTime(&b, c->ev[1], c->ev[2]));
+    c->stats.ms_lists += a;
+    c->stats.ms_gn_level[level] += b;
+  }
   return 0;
 }
 
@@ -616,25 +598,19 @@ int prepare_workspace(vslamb200_ctx * c, Problem & P, const vb::SolverParams & s
   const int nJobs = (int)P.jobs.size(), nViews = (int)P.views.size();
   const size_t npx0 = (size_t)P.W * P.H;
   const size_t listStride = align_up(npx0, 64);
-  CK(c->lists.ensure(listStride * 14 * nViews));
-  CK(c->hist.ensure((size_t)nViews * vb::HIST_BINS * sizeof(int), true));
-  CK(cudaMemsetAsync(c->hist.p, 0, (size_t)nViews * vb::HIST_BINS * sizeof(int), c->stream));
-  CK(c->wlut.ensure((size_t)nViews * vb::HIST_BINS * sizeof(float)));
-  CK(c->active.ensure((size_t)nViews * sizeof(int)));
-  CK(c->counts.ensure(64));
+  // per view: zi f64 | uvt u32 | d f32 | g u32 | r s16   (22 bytes per candidate pixel)
+  CK(c->lists.ensure(listStride * 22 * nViews));
   CK(c->chunkCounts.ensure((size_t)nViews * vb::list_chunks_for((int)npx0) * sizeof(int)));
-  const size_t partialStride = (npx0 + 511) / 512;
-  CK(c->partials.ensure((size_t)nViews * partialStride * vb::NE_TERMS * sizeof(double)));
+  CK(c->partials.ensure((size_t)nViews * vb::NE_TERMS * sizeof(double)));
   uint8_t * base = c->lists.as<uint8_t>();
   for (int v = 0; v < nViews; v++) {
     vb::ViewState & V = P.views[v];
-    uint8_t * b = base + (size_t)v * listStride * 14;
-    V.uvt = (uint32_t *)b;
-    V.d = (float *)(b + listStride * 4);
-    V.g = (uint32_t *)(b + listStride * 8);
-    V.r = (int16_t *)(b + listStride * 12);
-    V.hist = c->hist.as<int>() + (size_t)v * vb::HIST_BINS;
-    V.wlut = c->wlut.as<float>() + (size_t)v * vb::HIST_BINS;
+    uint8_t * b = base + (size_t)v * listStride * 22;
+    V.zi = (double *)b;
+    V.uvt = (uint32_t *)(b + listStride * 8);
+    V.d = (float *)(b + listStride * 12);
+    V.g = (uint32_t *)(b + listStride * 16);
+    V.r = (int16_t *)(b + listStride * 20);
   }
   CK(c->jobs.ensure(nJobs * sizeof(vb::JobState)));
   CK(c->views.ensure(nViews * sizeof(vb::ViewState)));
@@ -663,7 +639,7 @@ int vslamb200_align(vslamb200_ctx * c, const vslamb200_job * jobs, int nJobs, vs
   const vb::SolverParams sp = solver_params(c->cfg);
   if (int e = prepare_workspace(c, P, sp)) return e;
   for (int level = P.nLevels - 1; level >= 0; level--)
-    if (int e = run_level(c, P, level, sp)) return e;
+    if (int e = run_level(c, P, level, sp, sp.maxIterations + 1, false)) return e;
   CK(cudaMemcpyAsync(P.jobs.data(), c->jobs.p, nJobs * sizeof(vb::JobState), cudaMemcpyDeviceToHost, c->stream));
   CK(cudaStreamSynchronize(c->stream));
   c->stats.d2h_bytes += (uint64_t)nJobs * sizeof(vb::JobState);
@@ -677,7 +653,14 @@ int vslamb200_align(vslamb200_ctx * c, const vslamb200_job * jobs, int nJobs, vs
     for (int l = 0; l < VSLAMB200_MAX_LEVELS; l++) {
       r.iters[l] = l < P.nLevels ? J.iters[l] : 0;
       r.stop[l] = l < P.nLevels ? J.stop[l] : 0;
+      if (l < P.nLevels) {
+        const uint64_t px = (uint64_t)J.evals[l] * J.nViews * P.geo.W[l] * P.geo.H[l];
+        c->stats.pixel_iterations += px;
+        c->stats.pixel_iterations_level[l] += px;
+        c->stats.gn_iterations += J.evals[l];
+      }
     }
+    c->stats.point_iterations += J.pointIters;
   }
   return 0;
 }
@@ -723,16 +706,14 @@ int vslamb200_evaluate(
   int e = prepare_workspace(c, P, sp);
   c->traceEnabled = savedTrace;
   if (e) return e;
-  // one iteration with the warp forced to exactly the caller's transform
+  // one computeNormalEquations with the warp forced to exactly the caller's transform
   const int nViews = 1, nJobs = 1;
   const int npx = P.geo.W[level] * P.geo.H[level];
-  const int chunk = 512;
-  const int partialStride = (P.W * P.H + 511) / 512;
   vb::JobState * dJobs = c->jobs.as<vb::JobState>();
   vb::ViewState * dViews = c->views.as<vb::ViewState>();
   const vb::FrameDev * table = c->dFrames.as<vb::FrameDev>();
   vb::launch_level_setup(table, dJobs, dViews, nViews, level, c->stream);
-  vb::launch_build_lists(table, dViews, dJobs, nViews, level, npx, sp.minGradient2, chunk, c->chunkCounts.as<int>(),
+  vb::launch_build_lists(table, dViews, dJobs, nViews, level, npx, sp.minGradient2, c->chunkCounts.as<int>(),
                          vb::list_chunks_for(npx), c->stream);
   vb::launch_level_begin(dJobs, dViews, nJobs, level, c->stream);
   vb::ViewState V;
@@ -741,30 +722,26 @@ int vslamb200_evaluate(
   V.se3 = to_pose(se3);
   vb::view_set_warp(V);
   CK(cudaMemcpyAsync(dViews, &V, sizeof(V), cudaMemcpyHostToDevice, c->stream));
-  const int zero = 0;
-  CK(c->active.ensure(sizeof(int)));
-  CK(cudaMemcpyAsync(c->active.p, &zero, sizeof(int), cudaMemcpyHostToDevice, c->stream));
-  vb::launch_residual(dViews, c->active.as<int>(), 1, V.nChunks, chunk, sp, c->stream);
-  vb::launch_accumulate(dJobs, dViews, c->active.as<int>(), 1, V.nChunks, chunk, c->partials.as<double>(), partialStride,
-                        sp, level, nullptr, 0, c->stream);
-  c->stats.kernel_launches += 7;
+  CK(cudaMemsetAsync(c->partials.p, 0, vb::NE_TERMS * sizeof(double), c->stream));
+  const int cluster = pick_cluster(npx, 1);
+  CK(vb::launch_gn_level(dJobs, dViews, nJobs, cluster, (((npx + cluster - 1) / cluster) + 3) & ~3, true, sp, level, 1,
+                         nullptr, 0, c->partials.as<double>(), c->stream));
+  c->stats.kernel_launches += 6;
   if (rcode) {
     CK(c->plane.ensure((size_t)npx * 2));
     vb::launch_scatter_rcode(dViews, 0, c->plane.as<int16_t>(), c->stream);
     CK(cudaMemcpyAsync(rcode, c->plane.p, (size_t)npx * 2, cudaMemcpyDeviceToHost, c->stream));
+    c->stats.kernel_launches += 2;
   }
-  std::vector<double> part((size_t)std::max(V.nChunks, 1) * vb::NE_TERMS, 0.0);
-  if (V.nChunks > 0)
-    CK(cudaMemcpyAsync(part.data(), c->partials.p, (size_t)V.nChunks * vb::NE_TERMS * sizeof(double),
-                       cudaMemcpyDeviceToHost, c->stream));
+  double sums[vb::NE_TERMS];
+  CK(cudaMemcpyAsync(sums, c->partials.p, sizeof(sums), cudaMemcpyDeviceToHost, c->stream));
   vb::ViewState V2;
   CK(cudaMemcpyAsync(&V2, dViews, sizeof(V2), cudaMemcpyDeviceToHost, c->stream));
   CK(cudaStreamSynchronize(c->stream));
   CK(cudaGetLastError());
   if (ne64) {
-    double s[vb::NE_TERMS] = {0};
-    for (int ch = 0; ch < V.nChunks; ch++)
-      for (int k = 0; k < vb::NE_TERMS; k++) s[k] += part[(size_t)ch * vb::NE_TERMS + k];
+    double s[vb::NE_TERMS];
+    std::memcpy(s, sums, sizeof(s));
     const double n = (double)V.nIp;
     if (V.nIp > 1)
       for (double & x : s) x /= n;

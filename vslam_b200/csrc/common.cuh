@@ -53,10 +53,10 @@ struct ViewState
   // interest list (SoA)
   uint32_t * uvt;           // u | v<<12 | T<<24
   float * d;                // depth of the point
+  double * zi;              // 1 / depth in fp64 (Warp.cpp:170 zi), computed once per level
   uint32_t * g;             // dIx (low 16) | dIy (high 16)
   int16_t * r;              // residual of the current iteration (R_INVISIBLE if not visible)
   int nIp;                  // retained interest points (nConstraints of this view)
-  int nChunks;              // ceil(nIp / chunk)
   // warp
   Pose poseRef;             // keyframe pose
   Pose se3;                 // poseCur * poseRef^-1
@@ -69,7 +69,6 @@ struct ViewState
   int * hist;               // HIST_BINS global bins
   float * wlut;             // HIST_BINS weights
   double scale, offset;
-  unsigned int ticketA;     // last-block counter of the residual kernel
 };
 
 struct JobState
@@ -91,8 +90,9 @@ struct JobState
   int status;
   int iters[MAX_LEVELS];
   int stop[MAX_LEVELS];
-  unsigned int ticketB;     // last-block counter of the accumulate kernel
-  int totalChunks;          // sum of nChunks over the job's views
+  int totalPoints;          // sum of nIp over the job's views at the current level
+  int evals[MAX_LEVELS];    // computeNormalEquations calls per level (completed steps + a final rejected one)
+  unsigned long long pointIters;  // sum over evaluations of the interest points visited
 };
 
 struct SolverParams
@@ -245,19 +245,16 @@ void launch_pyramid_level(const FrameDev * frames, const int * slots, int n, int
 void launch_gradients(const FrameDev * frames, const int * slots, int n, int level, int W, int H, cudaStream_t s);
 // lists.cu
 void launch_build_lists(const FrameDev * frames, ViewState * views, const JobState * jobs, int nViews, int level,
-                        int maxPixels, double minGradient2, int chunk, int * chunkCounts, int maxChunksPerView,
-                        cudaStream_t s);
+                        int maxPixels, double minGradient2, int * chunkCounts, int maxChunksPerView, cudaStream_t s);
 int list_chunks_for(int pixels);
-// align_kernels.cu / accumulate.cu
+// level_misc.cu
 void launch_level_setup(const FrameDev * frames, JobState * jobs, ViewState * views, int nViews, int level,
                         cudaStream_t s);
 void launch_level_begin(JobState * jobs, ViewState * views, int nJobs, int level, cudaStream_t s);
-void launch_residual(ViewState * views, const int * activeViews, int nActiveViews, int maxChunks, int chunk,
-                     SolverParams p, cudaStream_t s);
-void launch_accumulate(JobState * jobs, ViewState * views, const int * activeViews, int nActiveViews, int maxChunks,
-                       int chunk, double * partials, int partialStride, SolverParams p, int level, double * trace,
-                       size_t traceJobStride, cudaStream_t s);
-void launch_compact_active(const JobState * jobs, const ViewState * views, int nViews, int * activeViews, int * counts,
-                           cudaStream_t s);
 void launch_scatter_rcode(const ViewState * views, int view, int16_t * plane, cudaStream_t s);
+// gn_level.cu
+size_t gn_level_static_smem();
+cudaError_t launch_gn_level(JobState * jobs, ViewState * views, int nJobs, int clusterSize, int maxPointsPerCta,
+                            bool residualsInHbm, SolverParams p, int level, int maxEvals, double * trace,
+                            size_t traceJobStride, double * viewSums, cudaStream_t s);
 }  // namespace vb

@@ -1,0 +1,466 @@
+// One launch per pyramid level: a thread-block CLUSTER per alignment job runs the whole
+// GaussNewton::solve loop of that level on device (GaussNewton.cpp:33-102 over
+// InverseCompositional::computeNormalEquations, InverseCompositional.cpp:105-154, stacked over the job's
+// keyframes, InverseCompositionalStacked.cpp:39-48).  No host round trip inside the loop.
+//
+// Per Gauss-Newton iteration and per keyframe ("view") every CTA of the cluster owns a contiguous slice
+// of the view's interest list:
+//   phase A  SE3 warp + nearest sample + integer residual r (kept in shared memory, or in HBM when the
+//            slice does not fit) + shared-memory residual histogram
+//   barrier  cluster barrier; every CTA sums the cluster's histograms through distributed shared memory and
+//            derives the robust scale and the 511-entry weight table from it (Scaler.cpp:21-67,
+//            Loss.cpp:51-92) - residuals are u8 - u8 integers, so every scaler is a function of the histogram
+//   phase C  1x6 Jacobian (fp64), weight lookup, 21 + 6 + 1 products (fp64), fixed-order block reduction
+//   barrier  cluster barrier; every CTA sums the cluster's block partials in rank order (deterministic) and
+//            runs the 6x6 solve / pose update / termination logic redundantly (bitwise identical), so no
+//            broadcast of the new pose is needed.
+// Everything that feeds A, b and chi2 is fp64: the nearest-neighbour sampling makes the iteration chaotic
+// (one pixel switching its rounded target changes b by ~1 % near convergence), so matching the CPU
+// aligner's iterates and stopping decisions needs ~1e-13 relative accuracy, not fp32's 1e-7.
+#include <cooperative_groups.h>
+
+#include "solve.cuh"
+
+namespace cg = cooperative_groups;
+
+namespace vb
+{
+constexpr int GT = 256;  // threads per CTA
+
+__device__ __forceinline__ double block_sum256(double v, double * sm /* >= 8 doubles */)
+{
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  __syncthreads();
+  if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = v;
+  __syncthreads();
+  double s = 0;
+#pragma unroll
+  for (int w = 0; w < GT / 32; w++) s += sm[w];
+  return s;
+}
+
+__device__ __forceinline__ double loss_weight(const SolverParams & p, double r)
+{
+  switch (p.lossKind) {
+    case VSLAMB200_LOSS_TUKEY: {
+      const double C = 4.6851;
+      if (fabs(r) < C) {
+        const double rc = r / C;
+        const double q = 1.0 - rc * rc;
+        return q * q;
+      }
+      return 0.0;
+    }
+    case VSLAMB200_LOSS_HUBER:
+      if (fabs(r) < p.huberC) return 1.0;
+      return (p.huberC * r > 0.0 ? 1.0 : -1.0) / r;
+    case VSLAMB200_LOSS_TDIST:
+      return (p.lossV + 1.0) / (p.lossV + r * r);
+    default:
+      return 1.0;
+  }
+}
+
+// Scale / offset from the residual histogram (h[b] = #visible points with r = b-255; invisible points
+// count as r = 0, InverseCompositional.cpp:111,130) and the weight table.  Whole block.
+__device__ void scale_and_weights(
+  ViewState & V, const SolverParams & p, int * h /* smem 512 */, double * lut /* smem 512 */, double * red)
+{
+  const int tid = threadIdx.x;
+  __shared__ double s_scale, s_offset;
+  const int c0 = h[tid] + h[tid + 256];
+  const double vis = block_sum256((double)c0, red);
+  const long n = V.nIp;
+  __syncthreads();
+  if (tid == 0) h[255] += (int)(n - (long)vis);  // zeros of the invisible points
+  __syncthreads();
+  double scale = 1.0, offset = 0.0;
+  const double r0 = (double)(tid - 255), r1 = (double)(tid + 1);
+  const double n0 = (double)h[tid], n1 = (double)h[tid + 256];
+  if (p.scalerKind == VSLAMB200_SCALER_TDIST) {
+    // sigma^2 <- mean(r^2 (nu+1) / (nu + (r/sigma)^2)), from sigma = 1, <= 30 steps, until |step| <= 1e-5
+    const double a0 = n0 * (r0 * r0 * (p.scalerV + 1)), a1 = n1 * (r1 * r1 * (p.scalerV + 1));
+    double step = 1.79769313486231570e308, sigma = 1.0;
+    __syncthreads();
+    for (int it = 0; it < 30 && step > 1e-5; it++) {
+      double term = 0.0;
+      if (n0 > 0) {
+        const double q = r0 / sigma;
+        term += a0 / (p.scalerV + q * q);
+      }
+      if (n1 > 0) {
+        const double q = r1 / sigma;
+        term += a1 / (p.scalerV + q * q);
+      }
+      // one barrier per step: warp partials alternate between two shared buffers
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) term += __shfl_xor_sync(0xffffffffu, term, o);
+      double * buf = red + (it & 1) * (GT / 32);
+      if ((tid & 31) == 0) buf[tid >> 5] = term;
+      __syncthreads();
+      double sum = 0.0;
+#pragma unroll
+      for (int w = 0; w < GT / 32; w++) sum += buf[w];
+      const double s = sqrt(sum / (double)n);
+      step = fabs(sigma - s);
+      sigma = s;
+    }
+    __syncthreads();
+    scale = sigma;
+  } else if (p.scalerKind == VSLAMB200_SCALER_MEAN || p.scalerKind == VSLAMB200_SCALER_MEDIAN) {
+    if (n > 0) {
+      if (p.scalerKind == VSLAMB200_SCALER_MEAN) {
+        const double sum = block_sum256(n0 * r0 + n1 * r1, red);  // exact: integers < 2^53
+        offset = sum / (double)n;
+      } else {
+        if (tid == 0) {
+          // order statistics of the sorted residual vector (algorithm.cpp:109-120)
+          long ka, kb;
+          if (n % 2 == 0) {
+            ka = n / 2 - 1;
+            kb = n / 2 + 1;
+            if (n == 2) ka = kb = 0;
+          } else {
+            ka = kb = n / 2;
+          }
+          long cum = 0;
+          double va = 0, vb2 = 0;
+          bool fa = false, fb = false;
+          for (int b = 0; b < 511 && !(fa && fb); b++) {
+            cum += h[b];
+            if (!fa && cum > ka) {
+              va = b - 255;
+              fa = true;
+            }
+            if (!fb && cum > kb) {
+              vb2 = b - 255;
+              fb = true;
+            }
+          }
+          s_offset = (n % 2 == 0 && n != 2) ? (va + vb2) / 2 : va;
+        }
+        __syncthreads();
+        offset = s_offset;
+      }
+      const double a = block_sum256(n0 * fabs(r0 - offset) + n1 * fabs(r1 - offset), red);
+      scale = sqrt(a / (double)(n - 1));
+    }
+  }
+  if (tid == 0) {
+    s_scale = scale;
+    V.scale = scale;
+    V.offset = offset;
+  }
+  __syncthreads();
+  scale = s_scale;
+  lut[tid] = loss_weight(p, (r0 - offset) / scale);
+  if (tid < 255) lut[tid + 256] = loss_weight(p, (r1 - offset) / scale);
+}
+
+// Exact warp of one interest point, operation for operation the oracle's (fp64, explicit fma):
+// Camera::image2camera (Camera.cpp:32-35), se3 * p (Warp.cpp:160-161), Camera::camera2image
+// (Camera.cpp:23-30), visibility (InverseCompositional.cpp:115-116), std::round.
+__device__ __noinline__ int warp_exact(const ViewState & V, int u, int v, float df)
+{
+  const double d = (double)df;
+  const double X = __fma_rn(V.kx, d, __dmul_rn(V.ifx, __dmul_rn((double)u, d)));
+  const double Y = __fma_rn(V.ky, d, __dmul_rn(V.ify, __dmul_rn((double)v, d)));
+  const double qx = __fma_rn(V.R[2], d, __fma_rn(V.R[1], Y, __fma_rn(V.R[0], X, V.t[0])));
+  const double qy = __fma_rn(V.R[5], d, __fma_rn(V.R[4], Y, __fma_rn(V.R[3], X, V.t[1])));
+  const double qz = __fma_rn(V.R[8], d, __fma_rn(V.R[7], Y, __fma_rn(V.R[6], X, V.t[2])));
+  if (!(qz > 0.0)) return -1;
+  const double up = __ddiv_rn(__fma_rn(V.fx, qx, __dmul_rn(V.cx, qz)), qz);
+  const double vp = __ddiv_rn(__fma_rn(V.fy, qy, __dmul_rn(V.cy, qz)), qz);
+  if (!(1.0 < up && up < (double)(V.Wt - 1) && 1.0 < vp && vp < (double)(V.Ht - 1) && isfinite(up))) return -1;
+  // std::round (half away from zero) of a positive value == floor(x + 0.5)
+  return __double2int_rd(vp + 0.5) * V.Wt + __double2int_rd(up + 0.5);
+}
+
+struct WarpConsts
+{
+  float r00, r01, r02, r10, r11, r12, r20, r21, r22, t0, t1, t2, fx, fy, ifx, ify, kx, ky, epsA, epsB;
+  int Wt, Ht;
+};
+
+// Sampled target pixel index of one interest point, or -1 when it is not visible.  The index and the
+// visibility flag are integer decisions and must be the fp64 oracle's.  A filtered evaluation gets them
+// without fp64 in the common case: in exact arithmetic u' = u + fx*(Dx - xn*Dz)/(z + Dz) with
+// D = (R - I) p + t, because p was back-projected from the integer pixel (u, v).  The displacement is
+// small, so fp32 carries it with an absolute error far below a pixel; only when it lands within the
+// error bound eps of a rounding (k + 0.5) or visibility (integer) boundary is the point re-evaluated by
+// warp_exact().
+__device__ __forceinline__ int warp_filtered(const ViewState & V, const WarpConsts & c, int u, int v, float d)
+{
+  const float xn = fmaf((float)u, c.ifx, c.kx), yn = fmaf((float)v, c.ify, c.ky);
+  const float px = xn * d, py = yn * d;
+  const float Dx = fmaf(c.r02, d, fmaf(c.r01, py, fmaf(c.r00, px, c.t0)));
+  const float Dy = fmaf(c.r12, d, fmaf(c.r11, py, fmaf(c.r10, px, c.t1)));
+  const float Dz = fmaf(c.r22, d, fmaf(c.r21, py, fmaf(c.r20, px, c.t2)));
+  const float qz = d + Dz;
+  const float iz = __frcp_rn(qz);
+  const float du = c.fx * fmaf(-xn, Dz, Dx) * iz;
+  const float dv = c.fy * fmaf(-yn, Dz, Dy) * iz;
+  // distance of the displacement to the nearest multiple of 0.5 (rounding and visibility boundaries)
+  const float fu = du + du, fv = dv + dv;
+  const float distu = 0.5f * fabsf(fu - rintf(fu)), distv = 0.5f * fabsf(fv - rintf(fv));
+  const float eps = fmaf(c.epsA, d, c.epsB) * fabsf(iz) + 3.8e-6f * (fabsf(du) + fabsf(dv)) + 6.1e-5f;
+  if (!(qz > 0.25f * d) || !(fminf(distu, distv) > eps) || !(fabsf(du) + fabsf(dv) < 4096.f)) return warp_exact(V, u, v, d);
+  // boundaries are integers: compare the displacement with exact integer offsets
+  const bool vis = du > (float)(1 - u) && du < (float)(c.Wt - 1 - u) && dv > (float)(1 - v) && dv < (float)(c.Ht - 1 - v);
+  const int iu = u + __float2int_rd(du + 0.5f), iv = v + __float2int_rd(dv + 0.5f);
+  return vis ? iv * c.Wt + iu : -1;
+}
+
+struct LevelShared
+{
+  JobState J;
+  ViewState Vs[MAX_VIEWS];
+  int hist[2][HIST_BINS];
+  int tot[HIST_BINS];
+  double lut[HIST_BINS];
+  double partial[2][MAX_VIEWS][NE_TERMS];
+  double sums[MAX_VIEWS * NE_TERMS];
+  double red[GT / 32 * NE_TERMS];
+};
+
+template <typename T>
+__device__ __forceinline__ void block_copy(T * dst, const T * src)
+{
+  static_assert(sizeof(T) % 4 == 0, "word copy");
+  const uint32_t * s = reinterpret_cast<const uint32_t *>(src);
+  uint32_t * d = reinterpret_cast<uint32_t *>(dst);
+  for (int i = threadIdx.x; i < (int)(sizeof(T) / 4); i += GT) d[i] = s[i];
+}
+
+// RSMEM: residuals of the CTA's slice stay in dynamic shared memory (4 x int16 per slot);
+// otherwise they go through the view's r array in HBM (large images, and the parity path that reads r back).
+template <bool RSMEM>
+__global__ void __launch_bounds__(GT, 2) gn_level_kernel(
+  JobState * __restrict__ jobs, ViewState * __restrict__ views, SolverParams p, int level, int maxEvals,
+  double * __restrict__ trace, size_t traceJobStride, double * __restrict__ viewSums)
+{
+  cg::cluster_group cluster = cg::this_cluster();
+  const unsigned C = cluster.num_blocks(), rank = cluster.block_rank();
+  const int job = blockIdx.x / C;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  __shared__ LevelShared S;
+  extern __shared__ uint2 rs[];
+
+  block_copy(&S.J, jobs + job);
+  __syncthreads();
+  if (!S.J.active) return;  // uniform over the cluster: nobody writes jobs[job] before the final barrier
+  const int K = S.J.nViews;
+  for (int k = 0; k < K; k++) block_copy(&S.Vs[k], views + S.J.view0 + k);
+  __syncthreads();
+  const bool weighted = p.lossKind != VSLAMB200_LOSS_NONE;
+  int hb = 0, evals = 0;
+
+  for (;;) {
+    const int pb = evals & 1;
+    for (int k = 0; k < K; k++) {
+      ViewState & V = S.Vs[k];
+      const int n = V.nIp;
+      const int per = (((n + (int)C - 1) / (int)C) + 3) & ~3;
+      const int p0 = min(n, (int)rank * per), p1 = min(n, p0 + per);
+      int * hist = S.hist[hb];
+      if (weighted) {
+        hist[tid] = 0;
+        hist[tid + 256] = 0;
+        __syncthreads();
+      }
+      // ---------------------------------------------------------------- phase A
+      {
+        WarpConsts c;
+        c.r00 = V.rI[0]; c.r01 = V.rI[1]; c.r02 = V.rI[2]; c.r10 = V.rI[3]; c.r11 = V.rI[4]; c.r12 = V.rI[5];
+        c.r20 = V.rI[6]; c.r21 = V.rI[7]; c.r22 = V.rI[8];
+        c.t0 = V.t32[0]; c.t1 = V.t32[1]; c.t2 = V.t32[2];
+        c.fx = V.fx32; c.fy = V.fy32; c.ifx = V.ifxH; c.ify = V.ifyH; c.kx = V.kxH; c.ky = V.kyH;
+        c.epsA = V.epsA; c.epsB = V.epsB; c.Wt = V.Wt; c.Ht = V.Ht;
+        const uint8_t * __restrict__ I = V.I;
+        const uint4 * __restrict__ uvt4 = reinterpret_cast<const uint4 *>(V.uvt);
+        const float4 * __restrict__ d4 = reinterpret_cast<const float4 *>(V.d);
+        uint2 * __restrict__ r4 = reinterpret_cast<uint2 *>(V.r);
+        int slot = tid;
+#pragma unroll 2
+        for (int g = p0 + 4 * tid; g < p1; g += 4 * GT, slot += GT) {
+          const uint4 pk4 = __ldg(uvt4 + (g >> 2));
+          const float4 dd4 = __ldg(d4 + (g >> 2));
+          const uint32_t pk[4] = {pk4.x, pk4.y, pk4.z, pk4.w};
+          const float dd[4] = {dd4.x, dd4.y, dd4.z, dd4.w};
+          int pix[4];
+#pragma unroll
+          for (int q = 0; q < 4; q++) {
+            pix[q] = -1;
+            if (g + q < p1) pix[q] = warp_filtered(V, c, pk[q] & 0xfff, (pk[q] >> 12) & 0xfff, dd[q]);
+          }
+          int val[4];
+#pragma unroll
+          for (int q = 0; q < 4; q++) val[q] = pix[q] >= 0 ? (int)__ldg(I + pix[q]) : 0;
+          uint32_t rr[4];
+#pragma unroll
+          for (int q = 0; q < 4; q++) {
+            const int r = val[q] - (int)(pk[q] >> 24);
+            rr[q] = pix[q] >= 0 ? (uint32_t)(uint16_t)(int16_t)r : (uint32_t)(uint16_t)R_INVISIBLE;
+            if (weighted && pix[q] >= 0) atomicAdd(&hist[r + 255], 1);
+          }
+          const uint2 packed = make_uint2(rr[0] | (rr[1] << 16), rr[2] | (rr[3] << 16));
+          if (RSMEM)
+            rs[slot] = packed;
+          else
+            r4[g >> 2] = packed;
+        }
+      }
+      // ---------------------------------------------------------------- scale + weight table
+      if (weighted) {
+        cluster.sync();
+        int a = 0, b = 0;
+        for (unsigned rk = 0; rk < C; rk++) {
+          const int * h = cluster.map_shared_rank(hist, rk);
+          a += h[tid];
+          b += h[tid + 256];
+        }
+        S.tot[tid] = a;
+        S.tot[tid + 256] = b;
+        __syncthreads();
+        scale_and_weights(V, p, S.tot, S.lut, S.red);
+        __syncthreads();
+        hb ^= 1;
+      }
+      // ---------------------------------------------------------------- phase C
+      double acc[NE_TERMS];
+#pragma unroll
+      for (int s = 0; s < NE_TERMS; s++) acc[s] = 0.0;
+      {
+        const double ifx = V.ifx, ify = V.ify, kx = V.kx, ky = V.ky, fxJ = V.fxJd, fyJ = V.fyJd;
+        const uint4 * __restrict__ uvt4 = reinterpret_cast<const uint4 *>(V.uvt);
+        const uint4 * __restrict__ g4 = reinterpret_cast<const uint4 *>(V.g);
+        const double2 * __restrict__ zi2 = reinterpret_cast<const double2 *>(V.zi);
+        const uint2 * __restrict__ r4 = reinterpret_cast<const uint2 *>(V.r);
+        const double * __restrict__ lut = S.lut;
+        int slot = tid;
+#pragma unroll 1
+        for (int g = p0 + 4 * tid; g < p1; g += 4 * GT, slot += GT) {
+          const uint4 pk4 = __ldg(uvt4 + (g >> 2));
+          const uint4 gg4 = __ldg(g4 + (g >> 2));
+          const double2 za = __ldg(zi2 + (g >> 1)), zb = __ldg(zi2 + (g >> 1) + 1);
+          const uint2 packed = RSMEM ? rs[slot] : r4[g >> 2];
+          const uint32_t pk[4] = {pk4.x, pk4.y, pk4.z, pk4.w};
+          const uint32_t gg[4] = {gg4.x, gg4.y, gg4.z, gg4.w};
+          const double zz[4] = {za.x, za.y, zb.x, zb.y};
+          const int rq[4] = {(int)(int16_t)(packed.x & 0xffff), (int)(int16_t)(packed.x >> 16),
+                             (int)(int16_t)(packed.y & 0xffff), (int)(int16_t)(packed.y >> 16)};
+#pragma unroll
+          for (int q = 0; q < 4; q++) {
+            // branch-free: a point outside the slice or not visible gets weight 0 (and a zero Jacobian when its
+            // list entry is padding), which adds exact zeros - the oracle skips w == 0 points the same way
+            const bool inside = g + q < p1;
+            const bool use = inside && rq[q] != R_INVISIBLE;
+            // WarpSE3::J rows (Warp.cpp:184-199) contracted with the template gradient
+            // (InverseCompositional.cpp:79-80), in normalised coordinates xn = x/z, yn = y/z
+            const double u = (double)(int)(pk[q] & 0xfff), v = (double)(int)((pk[q] >> 12) & 0xfff);
+            const double a = inside ? (double)(int)(int16_t)(gg[q] & 0xffff) * fxJ : 0.0;  // dIx * fx
+            const double b = inside ? (double)(int)(int16_t)(gg[q] >> 16) * fyJ : 0.0;     // dIy * fy
+            const int ri = use ? rq[q] : 0;
+            const double w = use ? (weighted ? lut[ri + 255] : 1.0) : 0.0;
+            const double r = (double)ri;
+            const double zi = inside ? zz[q] : 0.0;
+            const double xn = fma(ifx, u, kx), yn = fma(ify, v, ky);
+            const double cc = fma(a, xn, b * yn);
+            double J[6];
+            J[0] = a * zi;
+            J[1] = b * zi;
+            J[2] = -cc * zi;
+            J[3] = -fma(cc, yn, b);
+            J[4] = fma(cc, xn, a);
+            J[5] = fma(b, xn, -a * yn);
+            int s = 0;
+#pragma unroll
+            for (int i = 0; i < 6; i++) {
+              const double wj = w * J[i];
+#pragma unroll
+              for (int j = i; j < 6; j++) {
+                acc[s] = fma(wj, J[j], acc[s]);
+                s++;
+              }
+              acc[21 + i] = fma(wj, r, acc[21 + i]);
+            }
+            acc[27] = fma(w * r, r, acc[27]);
+          }
+        }
+      }
+      // fixed-order block reduction: lanes (xor tree), then warps 0..7
+#pragma unroll
+      for (int s = 0; s < NE_TERMS; s++) {
+        double v = acc[s];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        if (lane == 0) S.red[warp * NE_TERMS + s] = v;
+      }
+      __syncthreads();
+      if (tid < NE_TERMS) {
+        double v = 0.0;
+#pragma unroll
+        for (int w = 0; w < GT / 32; w++) v += S.red[w * NE_TERMS + tid];
+        S.partial[pb][k][tid] = v;
+      }
+      __syncthreads();
+    }
+    // ------------------------------------------------------------------ cluster reduction + solve
+    cluster.sync();
+    for (int i = tid; i < K * NE_TERMS; i += GT) {
+      const int k = i / NE_TERMS, t = i - k * NE_TERMS;
+      double v = 0.0;
+      for (unsigned rk = 0; rk < C; rk++) v += cluster.map_shared_rank(&S.partial[pb][k][t], rk)[0];
+      S.sums[i] = v;
+      if (viewSums && rank == 0) viewSums[(size_t)(S.J.view0 + k) * NE_TERMS + t] = v;
+    }
+    __syncthreads();
+    evals++;
+    if (tid == 0) {
+      S.J.evals[level]++;
+      S.J.pointIters += (unsigned long long)S.J.totalPoints;
+      gn_step(S.J, S.Vs, S.sums, p, level, (trace && rank == 0) ? trace + (size_t)job * traceJobStride : nullptr);
+      if (S.J.active && evals >= maxEvals) finish_level(S.J, S.Vs, level, VSLAMB200_STOP_MAXITER);
+    }
+    __syncthreads();
+    if (!S.J.active) break;
+  }
+  cluster.sync();  // nobody leaves while its shared memory may still be read remotely
+  if (rank == 0) {
+    block_copy(jobs + job, &S.J);
+    for (int k = 0; k < K; k++) block_copy(views + S.J.view0 + k, &S.Vs[k]);
+  }
+}
+
+size_t gn_level_static_smem() { return sizeof(LevelShared); }
+
+cudaError_t launch_gn_level(
+  JobState * jobs, ViewState * views, int nJobs, int clusterSize, int maxPointsPerCta, bool residualsInHbm,
+  SolverParams p, int level, int maxEvals, double * trace, size_t traceJobStride, double * viewSums, cudaStream_t s)
+{
+  if (nJobs <= 0) return cudaSuccess;
+  size_t dyn = (size_t)((maxPointsPerCta + 3) / 4 + GT) * sizeof(uint2);
+  const bool rsmem = !residualsInHbm && dyn + sizeof(LevelShared) <= 110 * 1024;
+  if (!rsmem) dyn = 0;
+  if (rsmem) {
+    cudaError_t e = cudaFuncSetAttribute(gn_level_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
+    if (e != cudaSuccess) return e;
+  }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)nJobs * clusterSize, 1, 1);
+  cfg.blockDim = dim3(GT, 1, 1);
+  cfg.dynamicSmemBytes = dyn;
+  cfg.stream = s;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = clusterSize;
+  at[0].val.clusterDim.y = 1;
+  at[0].val.clusterDim.z = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = 1;
+  if (rsmem)
+    return cudaLaunchKernelEx(&cfg, gn_level_kernel<true>, jobs, views, p, level, maxEvals, trace, traceJobStride, viewSums);
+  return cudaLaunchKernelEx(&cfg, gn_level_kernel<false>, jobs, views, p, level, maxEvals, trace, traceJobStride, viewSums);
+}
+}  // namespace vb

@@ -52,7 +52,7 @@ __global__ void __launch_bounds__(LTHREADS) list_count_kernel(
 
 // one block per view: exclusive scan of the chunk counts (in place), nIp and nChunks of the view
 __global__ void __launch_bounds__(256) list_scan_kernel(
-  ViewState * __restrict__ views, int * __restrict__ chunkCounts, int maxChunks, int chunk)
+  ViewState * __restrict__ views, int * __restrict__ chunkCounts, int maxChunks)
 {
   ViewState & V = views[blockIdx.x];
   const int npx = V.W * V.H;
@@ -81,10 +81,7 @@ __global__ void __launch_bounds__(256) list_scan_kernel(
     if (threadIdx.x == 255) carry = excl + v;
     __syncthreads();
   }
-  if (threadIdx.x == 0) {
-    V.nIp = carry;
-    V.nChunks = (carry + chunk - 1) / chunk;
-  }
+  if (threadIdx.x == 0) V.nIp = carry;
 }
 
 __global__ void __launch_bounds__(LTHREADS) list_write_kernel(
@@ -121,6 +118,7 @@ __global__ void __launch_bounds__(LTHREADS) list_write_kernel(
       const int v = i / W, u = i - v * W;
       V.uvt[o] = (uint32_t)u | ((uint32_t)v << 12) | ((uint32_t)f.I[level][i] << 24);
       V.d[o] = d;
+      V.zi[o] = 1.0 / (double)d;   // Warp.cpp:170
       V.g[o] = g;
     }
     running += tot;
@@ -129,12 +127,11 @@ __global__ void __launch_bounds__(LTHREADS) list_write_kernel(
 }
 
 void launch_build_lists(const FrameDev * frames, ViewState * views, const JobState * jobs, int nViews, int level,
-                        int maxPixels, double minGradient2, int chunk, int * chunkCounts, int maxChunksPerView,
-                        cudaStream_t s)
+                        int maxPixels, double minGradient2, int * chunkCounts, int maxChunksPerView, cudaStream_t s)
 {
   dim3 grid((maxPixels + LCHUNK - 1) / LCHUNK, nViews);
   list_count_kernel<<<grid, LTHREADS, 0, s>>>(frames, views, jobs, level, minGradient2, chunkCounts, maxChunksPerView);
-  list_scan_kernel<<<nViews, 256, 0, s>>>(views, chunkCounts, maxChunksPerView, chunk);
+  list_scan_kernel<<<nViews, 256, 0, s>>>(views, chunkCounts, maxChunksPerView);
   list_write_kernel<<<grid, LTHREADS, 0, s>>>(frames, views, jobs, level, minGradient2, chunkCounts, maxChunksPerView);
 }
 

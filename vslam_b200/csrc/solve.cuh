@@ -4,91 +4,118 @@
 
 namespace vb
 {
+// The 6x6 routines keep their matrices in registers: every loop is fully unrolled and every index is a
+// compile-time constant.  Partial pivoting is done with predicated row exchanges (a sequence of compare-and-
+// swap steps that brings the largest remaining |entry| of the column to the pivot row); in exact arithmetic
+// this is the same elimination as picking the arg-max row, only the order of the not-yet-eliminated rows differs.
+
 // determinant by LU with partial pivoting (GaussNewton.cpp:52)
-__device__ inline double det6(const double * A)
+__device__ __forceinline__ double det6(const double * A)
 {
-  double m[36];
-  for (int i = 0; i < 36; i++) m[i] = A[i];
+  double m[6][6];
+#pragma unroll
+  for (int i = 0; i < 6; i++)
+#pragma unroll
+    for (int j = 0; j < 6; j++) m[i][j] = A[i * 6 + j];
   double det = 1.0;
+#pragma unroll
   for (int c = 0; c < 6; c++) {
-    int p = c;
-    for (int r = c + 1; r < 6; r++)
-      if (fabs(m[r * 6 + c]) > fabs(m[p * 6 + c])) p = r;
-    if (m[p * 6 + c] == 0.0) return 0.0;
-    if (p != c) {
-      for (int k = 0; k < 6; k++) {
-        const double t = m[p * 6 + k];
-        m[p * 6 + k] = m[c * 6 + k];
-        m[c * 6 + k] = t;
-      }
-      det = -det;
-    }
-    det *= m[c * 6 + c];
+#pragma unroll
     for (int r = c + 1; r < 6; r++) {
-      const double f = m[r * 6 + c] / m[c * 6 + c];
-      for (int k = c; k < 6; k++) m[r * 6 + k] -= f * m[c * 6 + k];
+      const bool sw = fabs(m[r][c]) > fabs(m[c][c]);
+#pragma unroll
+      for (int k = c; k < 6; k++) {
+        const double x = m[c][k], y = m[r][k];
+        m[c][k] = sw ? y : x;
+        m[r][k] = sw ? x : y;
+      }
+      det = sw ? -det : det;
+    }
+    if (m[c][c] == 0.0) return 0.0;
+    det *= m[c][c];
+    const double inv = 1.0 / m[c][c];
+#pragma unroll
+    for (int r = c + 1; r < 6; r++) {
+      const double f = m[r][c] * inv;
+#pragma unroll
+      for (int k = c + 1; k < 6; k++) m[r][k] = fma(-f, m[c][k], m[r][k]);
     }
   }
   return det;
 }
 
 // LDL^T solve (GaussNewton.cpp:76)
-__device__ inline void ldlt_solve(const double * A, const double * b, double * x)
+__device__ __forceinline__ void ldlt_solve(const double * A, const double * b, double * x)
 {
-  double L[36], D[6], y[6];
-  for (int i = 0; i < 36; i++) L[i] = 0.0;
+  double L[6][6], D[6], y[6];
+#pragma unroll
   for (int j = 0; j < 6; j++) {
     double d = A[j * 6 + j];
-    for (int k = 0; k < j; k++) d -= L[j * 6 + k] * L[j * 6 + k] * D[k];
+#pragma unroll
+    for (int k = 0; k < j; k++) d = fma(-L[j][k] * L[j][k], D[k], d);
     D[j] = d;
-    L[j * 6 + j] = 1.0;
+    const double inv = 1.0 / d;
+#pragma unroll
     for (int i = j + 1; i < 6; i++) {
       double s = A[i * 6 + j];
-      for (int k = 0; k < j; k++) s -= L[i * 6 + k] * L[j * 6 + k] * D[k];
-      L[i * 6 + j] = s / d;
+#pragma unroll
+      for (int k = 0; k < j; k++) s = fma(-L[i][k] * L[j][k], D[k], s);
+      L[i][j] = s * inv;
     }
   }
+#pragma unroll
   for (int i = 0; i < 6; i++) {
     double s = b[i];
-    for (int k = 0; k < i; k++) s -= L[i * 6 + k] * y[k];
+#pragma unroll
+    for (int k = 0; k < i; k++) s = fma(-L[i][k], y[k], s);
     y[i] = s;
   }
+#pragma unroll
   for (int i = 5; i >= 0; i--) {
     double s = y[i] / D[i];
-    for (int k = i + 1; k < 6; k++) s -= L[k * 6 + i] * x[k];
+#pragma unroll
+    for (int k = i + 1; k < 6; k++) s = fma(-L[k][i], x[k], s);
     x[i] = s;
   }
 }
 
 // inverse by Gauss-Jordan with partial pivoting (SE3Alignment.cpp:101)
-__device__ inline void inverse6(const double * A, double * out)
+static __device__ __noinline__ void inverse6(const double * A, double * out)
 {
   double m[6][12];
+#pragma unroll
   for (int i = 0; i < 6; i++)
+#pragma unroll
     for (int j = 0; j < 6; j++) {
       m[i][j] = A[i * 6 + j];
       m[i][6 + j] = i == j ? 1.0 : 0.0;
     }
+#pragma unroll
   for (int c = 0; c < 6; c++) {
-    int p = c;
-    for (int r = c + 1; r < 6; r++)
-      if (fabs(m[r][c]) > fabs(m[p][c])) p = r;
-    if (p != c)
+#pragma unroll
+    for (int r = c + 1; r < 6; r++) {
+      const bool sw = fabs(m[r][c]) > fabs(m[c][c]);
+#pragma unroll
       for (int k = 0; k < 12; k++) {
-        const double t = m[p][k];
-        m[p][k] = m[c][k];
-        m[c][k] = t;
+        const double x = m[c][k], y = m[r][k];
+        m[c][k] = sw ? y : x;
+        m[r][k] = sw ? x : y;
       }
+    }
     const double inv = 1.0 / m[c][c];
+#pragma unroll
     for (int k = 0; k < 12; k++) m[c][k] *= inv;
+#pragma unroll
     for (int r = 0; r < 6; r++) {
       if (r == c) continue;
       const double f = m[r][c];
-      if (f == 0.0) continue;
-      for (int k = 0; k < 12; k++) m[r][k] -= f * m[c][k];
+#pragma unroll
+      for (int k = 0; k < 12; k++) m[r][k] = fma(-f, m[c][k], m[r][k]);
     }
   }
+#pragma unroll
   for (int i = 0; i < 6; i++)
+#pragma unroll
     for (int j = 0; j < 6; j++) out[i * 6 + j] = m[i][6 + j];
 }
 
@@ -115,7 +142,8 @@ __host__ __device__ inline void view_set_warp(ViewState & V)
 }
 
 // End of a level's solve: covariance and pose hand-off (SE3Alignment.cpp:100-102)
-__device__ inline void finish_level(JobState & J, ViewState * views, int level, int stop)
+// jv: the job's views (jv[0] is the job's first keyframe)
+static __device__ __noinline__ void finish_level(JobState & J, ViewState * jv, int level, int stop)
 {
   J.stop[level] = stop;
   J.iters[level] = J.nPushed;
@@ -129,21 +157,21 @@ __device__ inline void finish_level(JobState & J, ViewState * views, int level, 
     return;
   }
   inverse6(J.lastA, J.cov);
-  const ViewState & V0 = views[J.view0];
+  const ViewState & V0 = jv[0];
   J.pose = se3_mul(V0.se3, V0.poseRef);  // WarpSE3::poseCur (Warp.cpp:239)
 }
 
 // One GaussNewton::solve iteration (GaussNewton.cpp:44-99) on the stacked, normalised, prior-augmented
 // normal equations.  sums: per view 28 raw terms (21 upper A, 6 b, chi2), view-major.
 static __device__ __noinline__ void gn_step(
-  JobState & J, ViewState * views, const double * sums, const SolverParams & p, int level, double * trace)
+  JobState & J, ViewState * jv, const double * sums, const SolverParams & p, int level, double * trace)
 {
   double A[36], b[6], chi2 = 0.0;
   for (int i = 0; i < 36; i++) A[i] = 0.0;
   for (int i = 0; i < 6; i++) b[i] = 0.0;
   long nTotal = 0;
   for (int k = 0; k < J.nViews; k++) {
-    ViewState & V = views[J.view0 + k];
+    ViewState & V = jv[k];
     const double * s = sums + k * NE_TERMS;
     double Av[36], bv[6], c2 = s[27];
     int idx = 0;
@@ -178,24 +206,24 @@ static __device__ __noinline__ void gn_step(
   }
   const int i = J.iter;
   const double det = det6(A);
-  if (nTotal < 6) return finish_level(J, views, level, VSLAMB200_STOP_CONSTRAINTS);
-  if (!isfinite(det) || fabs(det) < 1e-6) return finish_level(J, views, level, VSLAMB200_STOP_HESSIAN);
+  if (nTotal < 6) return finish_level(J, jv, level, VSLAMB200_STOP_CONSTRAINTS);
+  if (!isfinite(det) || fabs(det) < 1e-6) return finish_level(J, jv, level, VSLAMB200_STOP_HESSIAN);
   const double dChi2 = i > 0 ? chi2 - J.chi2Prev : 0.0;
   if (i > 0 && dChi2 > 0) {
     // problem->setX(x.row(i-1)) (GaussNewton.cpp:73): se3 = exp(x) for every stacked frame
-    for (int k = 0; k < J.nViews; k++) views[J.view0 + k].se3 = se3_exp(J.xPrev);
-    return finish_level(J, views, level, VSLAMB200_STOP_CHI2);
+    for (int k = 0; k < J.nViews; k++) jv[k].se3 = se3_exp(J.xPrev);
+    return finish_level(J, jv, level, VSLAMB200_STOP_CHI2);
   }
   double dx[6], mdx[6];
   ldlt_solve(A, b, dx);
   for (int k = 0; k < 6; k++) mdx[k] = -dx[k];
   const Pose inc = se3_exp(mdx);  // updateCompositional(-dx) (InverseCompositional.cpp:104, Warp.cpp:153-157)
   for (int k = 0; k < J.nViews; k++) {
-    ViewState & V = views[J.view0 + k];
+    ViewState & V = jv[k];
     V.se3 = se3_mul(V.se3, inc);
   }
   double x[6];
-  se3_log(views[J.view0].se3, x);
+  se3_log(jv[0].se3, x);
   double nrm = 0;
   for (int k = 0; k < 6; k++) nrm += dx[k] * dx[k];
   const double step = sqrt(nrm);
@@ -207,8 +235,8 @@ static __device__ __noinline__ void gn_step(
     t[1] = (double)nTotal;
     t[2] = chi2;
     t[3] = step;
-    t[4] = views[J.view0].scale;
-    t[5] = views[J.view0].offset;
+    t[4] = jv[0].scale;
+    t[5] = jv[0].offset;
     for (int k = 0; k < 6; k++) t[6 + k] = x[k];
     for (int k = 0; k < 6; k++) t[12 + k] = b[k];
     for (int k = 0; k < 36; k++) t[18 + k] = A[k];
@@ -217,16 +245,16 @@ static __device__ __noinline__ void gn_step(
   double bmax = b[0];
   for (int k = 1; k < 6; k++) bmax = fmax(bmax, b[k]);
   if (i > 0 && (step < p.minStepSize || fabs(bmax) < p.minStepSize || fabs(dChi2) < p.minStepSize))
-    return finish_level(J, views, level, VSLAMB200_STOP_CONVERGED);
+    return finish_level(J, jv, level, VSLAMB200_STOP_CONVERGED);
   if (!isfinite(step)) {
     if (i > 0)
-      for (int k = 0; k < J.nViews; k++) views[J.view0 + k].se3 = se3_exp(J.xPrev);
-    return finish_level(J, views, level, VSLAMB200_STOP_NAN);
+      for (int k = 0; k < J.nViews; k++) jv[k].se3 = se3_exp(J.xPrev);
+    return finish_level(J, jv, level, VSLAMB200_STOP_NAN);
   }
   for (int k = 0; k < 6; k++) J.xPrev[k] = x[k];
   J.chi2Prev = chi2;
   J.iter = i + 1;
-  if (J.iter >= p.maxIterations) return finish_level(J, views, level, VSLAMB200_STOP_MAXITER);
-  for (int k = 0; k < J.nViews; k++) view_set_warp(views[J.view0 + k]);
+  if (J.iter >= p.maxIterations) return finish_level(J, jv, level, VSLAMB200_STOP_MAXITER);
+  for (int k = 0; k < J.nViews; k++) view_set_warp(jv[k]);
 }
 }  // namespace vb
