@@ -558,7 +558,7 @@ int pick_cluster(int npx, int maxViewsPerJob)
   return 1;
 }
 
-int run_level(vslamb200_ctx * c, Problem & P, int level, const vb::SolverParams & sp, int maxEvals, bool residualsInHbm)
+int run_level(vslamb200_ctx * c, Problem & P, int level, const vb::SolverParams & sp, int maxEvals)
 {
   const int nJobs = (int)P.jobs.size(), nViews = (int)P.views.size();
   const int npx = P.geo.W[level] * P.geo.H[level];
@@ -569,7 +569,6 @@ int run_level(vslamb200_ctx * c, Problem & P, int level, const vb::SolverParams 
   double * dTrace = c->traceEnabled ? c->trace.as<double>() : nullptr;
   const size_t traceJobStride = (size_t)P.nLevels * sp.maxIterations * vb::TRACE_STRIDE;
   const int cluster = pick_cluster(npx, 1);
-  const int maxPointsPerCta = (((npx + cluster - 1) / cluster) + 3) & ~3;
 
   if (c->timing) CK(cudaEventRecord(c->ev[0], c->stream));
   vb::launch_level_setup(table, dJobs, dViews, nViews, level, c->stream);
@@ -577,7 +576,7 @@ int run_level(vslamb200_ctx * c, Problem & P, int level, const vb::SolverParams 
                          c->stream);
   vb::launch_level_begin(dJobs, dViews, nJobs, level, c->stream);
   if (c->timing) CK(cudaEventRecord(c->ev[1], c->stream));
-  CK(vb::launch_gn_level(dJobs, dViews, nJobs, cluster, maxPointsPerCta, residualsInHbm, sp, level, maxEvals, dTrace,
+  CK(vb::launch_gn_level(dJobs, dViews, nJobs, cluster, sp, level, maxEvals, dTrace,
                          traceJobStride, c->partials.as<double>(), c->stream));
   if (c->timing) CK(cudaEventRecord(c->ev[2], c->stream));
   c->stats.kernel_launches += 6;
@@ -639,7 +638,7 @@ int vslamb200_align(vslamb200_ctx * c, const vslamb200_job * jobs, int nJobs, vs
   const vb::SolverParams sp = solver_params(c->cfg);
   if (int e = prepare_workspace(c, P, sp)) return e;
   for (int level = P.nLevels - 1; level >= 0; level--)
-    if (int e = run_level(c, P, level, sp, sp.maxIterations + 1, false)) return e;
+    if (int e = run_level(c, P, level, sp, sp.maxIterations + 1)) return e;
   CK(cudaMemcpyAsync(P.jobs.data(), c->jobs.p, nJobs * sizeof(vb::JobState), cudaMemcpyDeviceToHost, c->stream));
   CK(cudaStreamSynchronize(c->stream));
   c->stats.d2h_bytes += (uint64_t)nJobs * sizeof(vb::JobState);
@@ -724,8 +723,7 @@ int vslamb200_evaluate(
   CK(cudaMemcpyAsync(dViews, &V, sizeof(V), cudaMemcpyHostToDevice, c->stream));
   CK(cudaMemsetAsync(c->partials.p, 0, vb::NE_TERMS * sizeof(double), c->stream));
   const int cluster = pick_cluster(npx, 1);
-  CK(vb::launch_gn_level(dJobs, dViews, nJobs, cluster, (((npx + cluster - 1) / cluster) + 3) & ~3, true, sp, level, 1,
-                         nullptr, 0, c->partials.as<double>(), c->stream));
+  CK(vb::launch_gn_level(dJobs, dViews, nJobs, cluster, sp, level, 1, nullptr, 0, c->partials.as<double>(), c->stream));
   c->stats.kernel_launches += 6;
   if (rcode) {
     CK(c->plane.ensure((size_t)npx * 2));

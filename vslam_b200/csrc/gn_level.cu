@@ -5,8 +5,8 @@
 //
 // Per Gauss-Newton iteration and per keyframe ("view") every CTA of the cluster owns a contiguous slice
 // of the view's interest list:
-//   phase A  SE3 warp + nearest sample + integer residual r (kept in shared memory, or in HBM when the
-//            slice does not fit) + shared-memory residual histogram
+//   phase A  SE3 warp + nearest sample + integer residual r (2 B per point, written to the view's r array)
+//            + shared-memory residual histogram
 //   barrier  cluster barrier; every CTA sums the cluster's histograms through distributed shared memory and
 //            derives the robust scale and the 511-entry weight table from it (Scaler.cpp:21-67,
 //            Loss.cpp:51-92) - residuals are u8 - u8 integers, so every scaler is a function of the histogram
@@ -14,6 +14,9 @@
 //   barrier  cluster barrier; every CTA sums the cluster's block partials in rank order (deterministic) and
 //            runs the 6x6 solve / pose update / termination logic redundantly (bitwise identical), so no
 //            broadcast of the new pose is needed.
+// The interest list is static for the level, so both phases stream it through a 4-stage shared-memory ring
+// filled by TMA bulk copies (cp.async.bulk + mbarrier complete_tx): the first chunks of the next phase are
+// issued before the barrier / scale / solve sections, which hides the HBM latency behind them.
 // Everything that feeds A, b and chi2 is fp64: the nearest-neighbour sampling makes the iteration chaotic
 // (one pixel switching its rounded target changes b by ~1 % near convergence), so matching the CPU
 // aligner's iterates and stopping decisions needs ~1e-13 relative accuracy, not fp32's 1e-7.
@@ -188,8 +191,8 @@ struct WarpConsts
 // without fp64 in the common case: in exact arithmetic u' = u + fx*(Dx - xn*Dz)/(z + Dz) with
 // D = (R - I) p + t, because p was back-projected from the integer pixel (u, v).  The displacement is
 // small, so fp32 carries it with an absolute error far below a pixel; only when it lands within the
-// error bound eps of a rounding (k + 0.5) or visibility (integer) boundary is the point re-evaluated by
-// warp_exact().
+// error bound eps of a rounding boundary (u' = k + 0.5) or of a visibility boundary (u' = 1, W-1; v' = 1,
+// H-1) is the point re-evaluated by warp_exact().
 __device__ __forceinline__ int warp_filtered(const ViewState & V, const WarpConsts & c, int u, int v, float d)
 {
   const float xn = fmaf((float)u, c.ifx, c.kx), yn = fmaf((float)v, c.ify, c.ky);
@@ -201,15 +204,59 @@ __device__ __forceinline__ int warp_filtered(const ViewState & V, const WarpCons
   const float iz = __frcp_rn(qz);
   const float du = c.fx * fmaf(-xn, Dz, Dx) * iz;
   const float dv = c.fy * fmaf(-yn, Dz, Dy) * iz;
-  // distance of the displacement to the nearest multiple of 0.5 (rounding and visibility boundaries)
-  const float fu = du + du, fv = dv + dv;
-  const float distu = 0.5f * fabsf(fu - rintf(fu)), distv = 0.5f * fabsf(fv - rintf(fv));
+  // distance of the displacement to the nearest half-integer (u, v are integers: rounding boundaries of u')
+  const float hu = du - 0.5f, hv = dv - 0.5f;
+  const float distu = fabsf(hu - rintf(hu)), distv = fabsf(hv - rintf(hv));
+  // distance to the four visibility boundaries, as exact integer offsets of the displacement
+  const float lu = du - (float)(1 - u), ru = (float)(c.Wt - 1 - u) - du;
+  const float lv = dv - (float)(1 - v), rv = (float)(c.Ht - 1 - v) - dv;
+  const float dist = fminf(fminf(distu, distv), fminf(fminf(fabsf(lu), fabsf(ru)), fminf(fabsf(lv), fabsf(rv))));
   const float eps = fmaf(c.epsA, d, c.epsB) * fabsf(iz) + 3.8e-6f * (fabsf(du) + fabsf(dv)) + 6.1e-5f;
-  if (!(qz > 0.25f * d) || !(fminf(distu, distv) > eps) || !(fabsf(du) + fabsf(dv) < 4096.f)) return warp_exact(V, u, v, d);
-  // boundaries are integers: compare the displacement with exact integer offsets
-  const bool vis = du > (float)(1 - u) && du < (float)(c.Wt - 1 - u) && dv > (float)(1 - v) && dv < (float)(c.Ht - 1 - v);
+  if (!(qz > 0.25f * d) || !(dist > eps) || !(fabsf(du) + fabsf(dv) < 4096.f)) return warp_exact(V, u, v, d);
+  const bool vis = lu > 0.f && ru > 0.f && lv > 0.f && rv > 0.f;
   const int iu = u + __float2int_rd(du + 0.5f), iv = v + __float2int_rd(dv + 0.5f);
   return vis ? iv * c.Wt + iu : -1;
+}
+
+// ------------------------------------------------------------------------------------------------
+// shared-memory ring fed by TMA bulk copies
+// ------------------------------------------------------------------------------------------------
+constexpr int CH = 1024;                 // interest points per chunk (4 per thread)
+constexpr int NS = 4;                    // ring stages
+constexpr int OFF_UVT = 0;               // u | v<<12 | T<<24   (CH x 4 B)
+constexpr int OFF_DG = CH * 4;           // phase A: depth f32; phase C: packed gradients (CH x 4 B)
+constexpr int OFF_ZI = CH * 8;           // phase C: 1/z f64 (CH x 8 B)
+constexpr int OFF_R = CH * 16;           // phase C: residuals s16 (CH x 2 B)
+constexpr int STAGE_BYTES = CH * 18;
+
+__device__ __forceinline__ uint32_t smem_u32(const void * p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t * bar, uint32_t count)
+{
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t * bar, uint32_t bytes)
+{
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t * bar, uint32_t parity)
+{
+  const uint32_t a = smem_u32(bar);
+  uint32_t done;
+  do {
+    asm volatile(
+      "{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(done)
+      : "r"(a), "r"(parity)
+      : "memory");
+  } while (!done);
+}
+// global -> own shared memory, completion counted in bytes on an mbarrier of this CTA
+__device__ __forceinline__ void bulk_g2s(void * dst, const void * src, uint32_t bytes, uint64_t * bar)
+{
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                 smem_u32(dst)),
+               "l"(src), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
 }
 
 struct LevelShared
@@ -222,6 +269,7 @@ struct LevelShared
   double partial[2][MAX_VIEWS][NE_TERMS];
   double sums[MAX_VIEWS * NE_TERMS];
   double red[GT / 32 * NE_TERMS];
+  alignas(8) uint64_t full[NS];
 };
 
 template <typename T>
@@ -233,9 +281,34 @@ __device__ __forceinline__ void block_copy(T * dst, const T * src)
   for (int i = threadIdx.x; i < (int)(sizeof(T) / 4); i += GT) d[i] = s[i];
 }
 
-// RSMEM: residuals of the CTA's slice stay in dynamic shared memory (4 x int16 per slot);
-// otherwise they go through the view's r array in HBM (large images, and the parity path that reads r back).
-template <bool RSMEM>
+// slice of a view's interest list owned by one CTA of the cluster (multiples of 8 points: 16-byte TMA alignment
+// of the 2-byte residual array)
+__device__ __forceinline__ void slice_of(int n, unsigned C, unsigned rank, int & p0, int & p1)
+{
+  const int per = (((n + (int)C - 1) / (int)C) + 7) & ~7;
+  p0 = min(n, (int)rank * per);
+  p1 = min(n, p0 + per);
+}
+
+// one elected thread: bulk copies of chunk c of the slice [p0, p1) into ring stage (item % NS)
+__device__ __forceinline__ void issue_chunk(
+  LevelShared & S, unsigned char * ring, const ViewState & V, bool phaseC, int p0, int p1, int c, uint32_t item)
+{
+  const int start = p0 + c * CH;
+  const int cnt = (min(CH, p1 - start) + 7) & ~7;
+  unsigned char * st = ring + (size_t)(item % NS) * STAGE_BYTES;
+  uint64_t * bar = &S.full[item % NS];
+  mbar_expect_tx(bar, (uint32_t)cnt * (phaseC ? 18u : 8u));
+  bulk_g2s(st + OFF_UVT, V.uvt + start, cnt * 4, bar);
+  if (phaseC) {
+    bulk_g2s(st + OFF_DG, V.g + start, cnt * 4, bar);
+    bulk_g2s(st + OFF_ZI, V.zi + start, cnt * 8, bar);
+    bulk_g2s(st + OFF_R, V.r + start, cnt * 2, bar);
+  } else {
+    bulk_g2s(st + OFF_DG, V.d + start, cnt * 4, bar);
+  }
+}
+
 __global__ void __launch_bounds__(GT, 2) gn_level_kernel(
   JobState * __restrict__ jobs, ViewState * __restrict__ views, SolverParams p, int level, int maxEvals,
   double * __restrict__ trace, size_t traceJobStride, double * __restrict__ viewSums)
@@ -245,24 +318,38 @@ __global__ void __launch_bounds__(GT, 2) gn_level_kernel(
   const int job = blockIdx.x / C;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   __shared__ LevelShared S;
-  extern __shared__ uint2 rs[];
+  extern __shared__ __align__(128) unsigned char ring[];
 
   block_copy(&S.J, jobs + job);
   __syncthreads();
   if (!S.J.active) return;  // uniform over the cluster: nobody writes jobs[job] before the final barrier
   const int K = S.J.nViews;
   for (int k = 0; k < K; k++) block_copy(&S.Vs[k], views + S.J.view0 + k);
+  if (tid == 0) {
+    for (int s = 0; s < NS; s++) mbar_init(&S.full[s], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
   __syncthreads();
   const bool weighted = p.lossKind != VSLAMB200_LOSS_NONE;
   int hb = 0, evals = 0;
+  uint32_t item = 0;  // chunks consumed so far == ring position of the next chunk (uniform over the CTA)
+
+  // prologue of the very first phase A
+  {
+    int p0, p1;
+    slice_of(S.Vs[0].nIp, C, rank, p0, p1);
+    const int nCh = (p1 - p0 + CH - 1) / CH;
+    if (tid == 0)
+      for (int c = 0; c < min(NS, nCh); c++) issue_chunk(S, ring, S.Vs[0], false, p0, p1, c, item + c);
+  }
 
   for (;;) {
     const int pb = evals & 1;
     for (int k = 0; k < K; k++) {
       ViewState & V = S.Vs[k];
-      const int n = V.nIp;
-      const int per = (((n + (int)C - 1) / (int)C) + 3) & ~3;
-      const int p0 = min(n, (int)rank * per), p1 = min(n, p0 + per);
+      int p0, p1;
+      slice_of(V.nIp, C, rank, p0, p1);
+      const int nCh = (p1 - p0 + CH - 1) / CH;
       int * hist = S.hist[hb];
       if (weighted) {
         hist[tid] = 0;
@@ -278,14 +365,13 @@ __global__ void __launch_bounds__(GT, 2) gn_level_kernel(
         c.fx = V.fx32; c.fy = V.fy32; c.ifx = V.ifxH; c.ify = V.ifyH; c.kx = V.kxH; c.ky = V.kyH;
         c.epsA = V.epsA; c.epsB = V.epsB; c.Wt = V.Wt; c.Ht = V.Ht;
         const uint8_t * __restrict__ I = V.I;
-        const uint4 * __restrict__ uvt4 = reinterpret_cast<const uint4 *>(V.uvt);
-        const float4 * __restrict__ d4 = reinterpret_cast<const float4 *>(V.d);
         uint2 * __restrict__ r4 = reinterpret_cast<uint2 *>(V.r);
-        int slot = tid;
-#pragma unroll 2
-        for (int g = p0 + 4 * tid; g < p1; g += 4 * GT, slot += GT) {
-          const uint4 pk4 = __ldg(uvt4 + (g >> 2));
-          const float4 dd4 = __ldg(d4 + (g >> 2));
+        for (int ch = 0; ch < nCh; ch++, item++) {
+          const unsigned char * st = ring + (size_t)(item % NS) * STAGE_BYTES;
+          mbar_wait(&S.full[item % NS], (item / NS) & 1);
+          const int g = p0 + ch * CH + 4 * tid;
+          const uint4 pk4 = *reinterpret_cast<const uint4 *>(st + OFF_UVT + tid * 16);
+          const float4 dd4 = *reinterpret_cast<const float4 *>(st + OFF_DG + tid * 16);
           const uint32_t pk[4] = {pk4.x, pk4.y, pk4.z, pk4.w};
           const float dd[4] = {dd4.x, dd4.y, dd4.z, dd4.w};
           int pix[4];
@@ -304,13 +390,16 @@ __global__ void __launch_bounds__(GT, 2) gn_level_kernel(
             rr[q] = pix[q] >= 0 ? (uint32_t)(uint16_t)(int16_t)r : (uint32_t)(uint16_t)R_INVISIBLE;
             if (weighted && pix[q] >= 0) atomicAdd(&hist[r + 255], 1);
           }
-          const uint2 packed = make_uint2(rr[0] | (rr[1] << 16), rr[2] | (rr[3] << 16));
-          if (RSMEM)
-            rs[slot] = packed;
-          else
-            r4[g >> 2] = packed;
+          if (g < p1) r4[g >> 2] = make_uint2(rr[0] | (rr[1] << 16), rr[2] | (rr[3] << 16));
+          __syncthreads();  // stage consumed by everybody: refill it
+          if (tid == 0 && ch + NS < nCh) issue_chunk(S, ring, V, false, p0, p1, ch + NS, item + NS);
         }
       }
+      // the residuals were written through the generic proxy and are read back by TMA (async proxy)
+      asm volatile("fence.proxy.async;" ::: "memory");
+      __syncthreads();
+      if (tid == 0)
+        for (int c = 0; c < min(NS, nCh); c++) issue_chunk(S, ring, V, true, p0, p1, c, item + c);
       // ---------------------------------------------------------------- scale + weight table
       if (weighted) {
         cluster.sync();
@@ -333,18 +422,17 @@ __global__ void __launch_bounds__(GT, 2) gn_level_kernel(
       for (int s = 0; s < NE_TERMS; s++) acc[s] = 0.0;
       {
         const double ifx = V.ifx, ify = V.ify, kx = V.kx, ky = V.ky, fxJ = V.fxJd, fyJ = V.fyJd;
-        const uint4 * __restrict__ uvt4 = reinterpret_cast<const uint4 *>(V.uvt);
-        const uint4 * __restrict__ g4 = reinterpret_cast<const uint4 *>(V.g);
-        const double2 * __restrict__ zi2 = reinterpret_cast<const double2 *>(V.zi);
-        const uint2 * __restrict__ r4 = reinterpret_cast<const uint2 *>(V.r);
         const double * __restrict__ lut = S.lut;
-        int slot = tid;
 #pragma unroll 1
-        for (int g = p0 + 4 * tid; g < p1; g += 4 * GT, slot += GT) {
-          const uint4 pk4 = __ldg(uvt4 + (g >> 2));
-          const uint4 gg4 = __ldg(g4 + (g >> 2));
-          const double2 za = __ldg(zi2 + (g >> 1)), zb = __ldg(zi2 + (g >> 1) + 1);
-          const uint2 packed = RSMEM ? rs[slot] : r4[g >> 2];
+        for (int ch = 0; ch < nCh; ch++, item++) {
+          const unsigned char * st = ring + (size_t)(item % NS) * STAGE_BYTES;
+          mbar_wait(&S.full[item % NS], (item / NS) & 1);
+          const int g = p0 + ch * CH + 4 * tid;
+          const uint4 pk4 = *reinterpret_cast<const uint4 *>(st + OFF_UVT + tid * 16);
+          const uint4 gg4 = *reinterpret_cast<const uint4 *>(st + OFF_DG + tid * 16);
+          const double2 za = *reinterpret_cast<const double2 *>(st + OFF_ZI + tid * 32);
+          const double2 zb = *reinterpret_cast<const double2 *>(st + OFF_ZI + tid * 32 + 16);
+          const uint2 packed = *reinterpret_cast<const uint2 *>(st + OFF_R + tid * 8);
           const uint32_t pk[4] = {pk4.x, pk4.y, pk4.z, pk4.w};
           const uint32_t gg[4] = {gg4.x, gg4.y, gg4.z, gg4.w};
           const double zz[4] = {za.x, za.y, zb.x, zb.y};
@@ -387,7 +475,19 @@ __global__ void __launch_bounds__(GT, 2) gn_level_kernel(
             }
             acc[27] = fma(w * r, r, acc[27]);
           }
+          __syncthreads();
+          if (tid == 0 && ch + NS < nCh) issue_chunk(S, ring, V, true, p0, p1, ch + NS, item + NS);
         }
+      }
+      // prologue of the next phase A (next keyframe, or keyframe 0 of the next iteration): the list does not
+      // depend on the pose, so it streams in behind the reduction and the solve
+      {
+        const ViewState & Vn = S.Vs[k + 1 < K ? k + 1 : 0];
+        int q0, q1;
+        slice_of(Vn.nIp, C, rank, q0, q1);
+        const int nChN = (q1 - q0 + CH - 1) / CH;
+        if (tid == 0)
+          for (int c = 0; c < min(NS, nChN); c++) issue_chunk(S, ring, Vn, false, q0, q1, c, item + c);
       }
       // fixed-order block reduction: lanes (xor tree), then warps 0..7
 #pragma unroll
@@ -426,6 +526,13 @@ __global__ void __launch_bounds__(GT, 2) gn_level_kernel(
     __syncthreads();
     if (!S.J.active) break;
   }
+  // drain the speculative prologue of the phase A that will not run: no bulk copy may be in flight at exit
+  {
+    int p0, p1;
+    slice_of(S.Vs[0].nIp, C, rank, p0, p1);
+    const int nCh = (p1 - p0 + CH - 1) / CH;
+    for (int c = 0; c < min(NS, nCh); c++) mbar_wait(&S.full[(item + c) % NS], ((item + c) / NS) & 1);
+  }
   cluster.sync();  // nobody leaves while its shared memory may still be read remotely
   if (rank == 0) {
     block_copy(jobs + job, &S.J);
@@ -436,17 +543,13 @@ __global__ void __launch_bounds__(GT, 2) gn_level_kernel(
 size_t gn_level_static_smem() { return sizeof(LevelShared); }
 
 cudaError_t launch_gn_level(
-  JobState * jobs, ViewState * views, int nJobs, int clusterSize, int maxPointsPerCta, bool residualsInHbm,
-  SolverParams p, int level, int maxEvals, double * trace, size_t traceJobStride, double * viewSums, cudaStream_t s)
+  JobState * jobs, ViewState * views, int nJobs, int clusterSize, SolverParams p, int level, int maxEvals,
+  double * trace, size_t traceJobStride, double * viewSums, cudaStream_t s)
 {
   if (nJobs <= 0) return cudaSuccess;
-  size_t dyn = (size_t)((maxPointsPerCta + 3) / 4 + GT) * sizeof(uint2);
-  const bool rsmem = !residualsInHbm && dyn + sizeof(LevelShared) <= 110 * 1024;
-  if (!rsmem) dyn = 0;
-  if (rsmem) {
-    cudaError_t e = cudaFuncSetAttribute(gn_level_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
-    if (e != cudaSuccess) return e;
-  }
+  const size_t dyn = (size_t)NS * STAGE_BYTES;
+  cudaError_t e = cudaFuncSetAttribute(gn_level_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
+  if (e != cudaSuccess) return e;
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3((unsigned)nJobs * clusterSize, 1, 1);
   cfg.blockDim = dim3(GT, 1, 1);
@@ -459,8 +562,6 @@ cudaError_t launch_gn_level(
   at[0].val.clusterDim.z = 1;
   cfg.attrs = at;
   cfg.numAttrs = 1;
-  if (rsmem)
-    return cudaLaunchKernelEx(&cfg, gn_level_kernel<true>, jobs, views, p, level, maxEvals, trace, traceJobStride, viewSums);
-  return cudaLaunchKernelEx(&cfg, gn_level_kernel<false>, jobs, views, p, level, maxEvals, trace, traceJobStride, viewSums);
+  return cudaLaunchKernelEx(&cfg, gn_level_kernel, jobs, views, p, level, maxEvals, trace, traceJobStride, viewSums);
 }
 }  // namespace vb
