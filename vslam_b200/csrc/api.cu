@@ -487,7 +487,7 @@ struct Problem
 {
   std::vector<vb::JobState> jobs;
   std::vector<vb::ViewState> views;
-  int W = 0, H = 0, nLevels = 0;
+  int W = 0, H = 0, nLevels = 0, maxViews = 1;
   vb::FrameDev geo;
 };
 
@@ -537,6 +537,7 @@ int build_problem(vslamb200_ctx * c, const vslamb200_job * jobs, int nJobs, Prob
       P.views.push_back(V);
     }
     J.nLevels = P.nLevels;
+    P.maxViews = std::max(P.maxViews, in.n_from);
     P.jobs[j] = J;
   }
   // the reference indexes the point cloud (depth dims) with the intensity width; at odd sizes the
@@ -576,7 +577,7 @@ int run_level(vslamb200_ctx * c, Problem & P, int level, const vb::SolverParams 
                          c->stream);
   vb::launch_level_begin(dJobs, dViews, nJobs, level, c->stream);
   if (c->timing) CK(cudaEventRecord(c->ev[1], c->stream));
-  CK(vb::launch_gn_level(dJobs, dViews, nJobs, cluster, sp, level, maxEvals, dTrace,
+  CK(vb::launch_gn_level(dJobs, dViews, nJobs, P.maxViews, cluster, sp, level, maxEvals, dTrace,
                          traceJobStride, c->partials.as<double>(), c->stream));
   if (c->timing) CK(cudaEventRecord(c->ev[2], c->stream));
   c->stats.kernel_launches += 6;
@@ -723,7 +724,7 @@ int vslamb200_evaluate(
   CK(cudaMemcpyAsync(dViews, &V, sizeof(V), cudaMemcpyHostToDevice, c->stream));
   CK(cudaMemsetAsync(c->partials.p, 0, vb::NE_TERMS * sizeof(double), c->stream));
   const int cluster = pick_cluster(npx, 1);
-  CK(vb::launch_gn_level(dJobs, dViews, nJobs, cluster, sp, level, 1, nullptr, 0, c->partials.as<double>(), c->stream));
+  CK(vb::launch_gn_level(dJobs, dViews, nJobs, 1, cluster, sp, level, 1, nullptr, 0, c->partials.as<double>(), c->stream));
   c->stats.kernel_launches += 6;
   if (rcode) {
     CK(c->plane.ensure((size_t)npx * 2));

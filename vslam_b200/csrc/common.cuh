@@ -254,6 +254,6 @@ void launch_level_begin(JobState * jobs, ViewState * views, int nJobs, int level
 void launch_scatter_rcode(const ViewState * views, int view, int16_t * plane, cudaStream_t s);
 // gn_level.cu
 size_t gn_level_static_smem();
-cudaError_t launch_gn_level(JobState * jobs, ViewState * views, int nJobs, int clusterSize, SolverParams p, int level,
-                            int maxEvals, double * trace, size_t traceJobStride, double * viewSums, cudaStream_t s);
+cudaError_t launch_gn_level(JobState * jobs, ViewState * views, int nJobs, int maxViewsPerJob, int clusterSize,
+                            SolverParams p, int level, int maxEvals, double * trace, size_t traceJobStride, double * viewSums, cudaStream_t s);
 }  // namespace vb

@@ -28,9 +28,11 @@ namespace cg = cooperative_groups;
 
 namespace vb
 {
-constexpr int GT = 256;  // threads per CTA
+constexpr int GT = 128;              // threads per CTA
+constexpr int BPT = HIST_BINS / GT;  // histogram bins per thread
+constexpr int CTAS_PER_SM = 4;
 
-__device__ __forceinline__ double block_sum256(double v, double * sm /* >= 8 doubles */)
+__device__ __forceinline__ double block_sum(double v, double * sm /* >= GT/32 doubles */)
 {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
@@ -72,30 +74,37 @@ __device__ void scale_and_weights(
 {
   const int tid = threadIdx.x;
   __shared__ double s_scale, s_offset;
-  const int c0 = h[tid] + h[tid + 256];
-  const double vis = block_sum256((double)c0, red);
+  // thread t owns bins t, t + GT, ... (bin b holds the residual value b - 255; bin 511 is unused)
+  int c0 = 0;
+#pragma unroll
+  for (int j = 0; j < BPT; j++) c0 += h[tid + j * GT];
+  const double vis = block_sum((double)c0, red);
   const long n = V.nIp;
   __syncthreads();
   if (tid == 0) h[255] += (int)(n - (long)vis);  // zeros of the invisible points
   __syncthreads();
   double scale = 1.0, offset = 0.0;
-  const double r0 = (double)(tid - 255), r1 = (double)(tid + 1);
-  const double n0 = (double)h[tid], n1 = (double)h[tid + 256];
+  double rv[BPT], nv[BPT];
+#pragma unroll
+  for (int j = 0; j < BPT; j++) {
+    rv[j] = (double)(tid + j * GT - 255);
+    nv[j] = (double)h[tid + j * GT];
+  }
   if (p.scalerKind == VSLAMB200_SCALER_TDIST) {
     // sigma^2 <- mean(r^2 (nu+1) / (nu + (r/sigma)^2)), from sigma = 1, <= 30 steps, until |step| <= 1e-5
-    const double a0 = n0 * (r0 * r0 * (p.scalerV + 1)), a1 = n1 * (r1 * r1 * (p.scalerV + 1));
+    double av[BPT];
+#pragma unroll
+    for (int j = 0; j < BPT; j++) av[j] = nv[j] * (rv[j] * rv[j] * (p.scalerV + 1));
     double step = 1.79769313486231570e308, sigma = 1.0;
     __syncthreads();
     for (int it = 0; it < 30 && step > 1e-5; it++) {
       double term = 0.0;
-      if (n0 > 0) {
-        const double q = r0 / sigma;
-        term += a0 / (p.scalerV + q * q);
-      }
-      if (n1 > 0) {
-        const double q = r1 / sigma;
-        term += a1 / (p.scalerV + q * q);
-      }
+#pragma unroll
+      for (int j = 0; j < BPT; j++)
+        if (nv[j] > 0) {
+          const double q = rv[j] / sigma;
+          term += av[j] / (p.scalerV + q * q);
+        }
       // one barrier per step: warp partials alternate between two shared buffers
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) term += __shfl_xor_sync(0xffffffffu, term, o);
@@ -114,7 +123,10 @@ __device__ void scale_and_weights(
   } else if (p.scalerKind == VSLAMB200_SCALER_MEAN || p.scalerKind == VSLAMB200_SCALER_MEDIAN) {
     if (n > 0) {
       if (p.scalerKind == VSLAMB200_SCALER_MEAN) {
-        const double sum = block_sum256(n0 * r0 + n1 * r1, red);  // exact: integers < 2^53
+        double t = 0.0;
+#pragma unroll
+        for (int j = 0; j < BPT; j++) t += nv[j] * rv[j];
+        const double sum = block_sum(t, red);  // exact: integers < 2^53
         offset = sum / (double)n;
       } else {
         if (tid == 0) {
@@ -146,7 +158,10 @@ __device__ void scale_and_weights(
         __syncthreads();
         offset = s_offset;
       }
-      const double a = block_sum256(n0 * fabs(r0 - offset) + n1 * fabs(r1 - offset), red);
+      double t = 0.0;
+#pragma unroll
+      for (int j = 0; j < BPT; j++) t += nv[j] * fabs(rv[j] - offset);
+      const double a = block_sum(t, red);
       scale = sqrt(a / (double)(n - 1));
     }
   }
@@ -157,8 +172,8 @@ __device__ void scale_and_weights(
   }
   __syncthreads();
   scale = s_scale;
-  lut[tid] = loss_weight(p, (r0 - offset) / scale);
-  if (tid < 255) lut[tid + 256] = loss_weight(p, (r1 - offset) / scale);
+#pragma unroll
+  for (int j = 0; j < BPT; j++) lut[tid + j * GT] = loss_weight(p, (rv[j] - offset) / scale);
 }
 
 // Exact warp of one interest point, operation for operation the oracle's (fp64, explicit fma):
@@ -221,7 +236,7 @@ __device__ __forceinline__ int warp_filtered(const ViewState & V, const WarpCons
 // ------------------------------------------------------------------------------------------------
 // shared-memory ring fed by TMA bulk copies
 // ------------------------------------------------------------------------------------------------
-constexpr int CH = 1024;                 // interest points per chunk (4 per thread)
+constexpr int CH = 4 * GT;               // interest points per chunk (4 per thread)
 constexpr int NS = 4;                    // ring stages
 constexpr int OFF_UVT = 0;               // u | v<<12 | T<<24   (CH x 4 B)
 constexpr int OFF_DG = CH * 4;           // phase A: depth f32; phase C: packed gradients (CH x 4 B)
@@ -237,6 +252,10 @@ __device__ __forceinline__ void mbar_init(uint64_t * bar, uint32_t count)
 __device__ __forceinline__ void mbar_expect_tx(uint64_t * bar, uint32_t bytes)
 {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t * bar)
+{
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 __device__ __forceinline__ void mbar_wait(uint64_t * bar, uint32_t parity)
 {
@@ -262,15 +281,18 @@ __device__ __forceinline__ void bulk_g2s(void * dst, const void * src, uint32_t 
 struct LevelShared
 {
   JobState J;
-  ViewState Vs[MAX_VIEWS];
   int hist[2][HIST_BINS];
   int tot[HIST_BINS];
   double lut[HIST_BINS];
-  double partial[2][MAX_VIEWS][NE_TERMS];
-  double sums[MAX_VIEWS * NE_TERMS];
   double red[GT / 32 * NE_TERMS];
-  alignas(8) uint64_t full[NS];
+  alignas(8) uint64_t full[NS];   // TMA bytes of the stage have landed
+  alignas(8) uint64_t empty[NS];  // every warp has copied the stage into registers
 };
+// dynamic shared memory: ring | ViewState[K] | partial[2][K][28] | sums[K][28]
+__host__ __device__ inline size_t level_dyn_smem(int K)
+{
+  return (size_t)NS * STAGE_BYTES + (size_t)K * (sizeof(ViewState) + 3 * NE_TERMS * sizeof(double));
+}
 
 template <typename T>
 __device__ __forceinline__ void block_copy(T * dst, const T * src)
@@ -309,7 +331,7 @@ __device__ __forceinline__ void issue_chunk(
   }
 }
 
-__global__ void __launch_bounds__(GT, 2) gn_level_kernel(
+__global__ void __launch_bounds__(GT, CTAS_PER_SM) gn_level_kernel(
   JobState * __restrict__ jobs, ViewState * __restrict__ views, SolverParams p, int level, int maxEvals,
   double * __restrict__ trace, size_t traceJobStride, double * __restrict__ viewSums)
 {
@@ -324,9 +346,15 @@ __global__ void __launch_bounds__(GT, 2) gn_level_kernel(
   __syncthreads();
   if (!S.J.active) return;  // uniform over the cluster: nobody writes jobs[job] before the final barrier
   const int K = S.J.nViews;
-  for (int k = 0; k < K; k++) block_copy(&S.Vs[k], views + S.J.view0 + k);
+  ViewState * Vs = reinterpret_cast<ViewState *>(ring + (size_t)NS * STAGE_BYTES);
+  double * partial = reinterpret_cast<double *>(Vs + K);       // [2][K][28]: this CTA's block sums, double buffered
+  double * sums = partial + 2 * K * NE_TERMS;                  // [K][28]: cluster totals
+  for (int k = 0; k < K; k++) block_copy(&Vs[k], views + S.J.view0 + k);
   if (tid == 0) {
-    for (int s = 0; s < NS; s++) mbar_init(&S.full[s], 1);
+    for (int s = 0; s < NS; s++) {
+      mbar_init(&S.full[s], 1);
+      mbar_init(&S.empty[s], GT / 32);
+    }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
@@ -337,23 +365,23 @@ __global__ void __launch_bounds__(GT, 2) gn_level_kernel(
   // prologue of the very first phase A
   {
     int p0, p1;
-    slice_of(S.Vs[0].nIp, C, rank, p0, p1);
+    slice_of(Vs[0].nIp, C, rank, p0, p1);
     const int nCh = (p1 - p0 + CH - 1) / CH;
     if (tid == 0)
-      for (int c = 0; c < min(NS, nCh); c++) issue_chunk(S, ring, S.Vs[0], false, p0, p1, c, item + c);
+      for (int c = 0; c < min(NS, nCh); c++) issue_chunk(S, ring, Vs[0], false, p0, p1, c, item + c);
   }
 
   for (;;) {
     const int pb = evals & 1;
     for (int k = 0; k < K; k++) {
-      ViewState & V = S.Vs[k];
+      ViewState & V = Vs[k];
       int p0, p1;
       slice_of(V.nIp, C, rank, p0, p1);
       const int nCh = (p1 - p0 + CH - 1) / CH;
       int * hist = S.hist[hb];
       if (weighted) {
-        hist[tid] = 0;
-        hist[tid + 256] = 0;
+#pragma unroll
+        for (int j = 0; j < BPT; j++) hist[tid + j * GT] = 0;
         __syncthreads();
       }
       // ---------------------------------------------------------------- phase A
@@ -366,34 +394,64 @@ __global__ void __launch_bounds__(GT, 2) gn_level_kernel(
         c.epsA = V.epsA; c.epsB = V.epsB; c.Wt = V.Wt; c.Ht = V.Ht;
         const uint8_t * __restrict__ I = V.I;
         uint2 * __restrict__ r4 = reinterpret_cast<uint2 *>(V.r);
-        for (int ch = 0; ch < nCh; ch++, item++) {
-          const unsigned char * st = ring + (size_t)(item % NS) * STAGE_BYTES;
-          mbar_wait(&S.full[item % NS], (item / NS) & 1);
-          const int g = p0 + ch * CH + 4 * tid;
+        // Software pipeline: the gathers of chunk ch are issued, then chunk ch-1 (whose gathers have had a whole
+        // chunk of arithmetic to arrive) is finished: residual, histogram, store.
+        struct Pend
+        {
+          int g, pix[4], val[4];
+          uint32_t T[4];
+        };
+        auto start_chunk = [&](int ch, Pend & P) {
+          const uint32_t it = item + ch;
+          if (tid == 0 && ch >= 1 && ch - 1 + NS < nCh) {
+            mbar_wait(&S.empty[(it - 1) % NS], ((it - 1) / NS) & 1);
+            issue_chunk(S, ring, V, false, p0, p1, ch - 1 + NS, it - 1 + NS);
+          }
+          const unsigned char * st = ring + (size_t)(it % NS) * STAGE_BYTES;
+          mbar_wait(&S.full[it % NS], (it / NS) & 1);
           const uint4 pk4 = *reinterpret_cast<const uint4 *>(st + OFF_UVT + tid * 16);
           const float4 dd4 = *reinterpret_cast<const float4 *>(st + OFF_DG + tid * 16);
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&S.empty[it % NS]);
           const uint32_t pk[4] = {pk4.x, pk4.y, pk4.z, pk4.w};
           const float dd[4] = {dd4.x, dd4.y, dd4.z, dd4.w};
-          int pix[4];
+          P.g = p0 + ch * CH + 4 * tid;
 #pragma unroll
           for (int q = 0; q < 4; q++) {
-            pix[q] = -1;
-            if (g + q < p1) pix[q] = warp_filtered(V, c, pk[q] & 0xfff, (pk[q] >> 12) & 0xfff, dd[q]);
+            P.pix[q] = -1;
+            P.T[q] = pk[q] >> 24;
+            if (P.g + q < p1) P.pix[q] = warp_filtered(V, c, pk[q] & 0xfff, (pk[q] >> 12) & 0xfff, dd[q]);
           }
-          int val[4];
 #pragma unroll
-          for (int q = 0; q < 4; q++) val[q] = pix[q] >= 0 ? (int)__ldg(I + pix[q]) : 0;
+          for (int q = 0; q < 4; q++) P.val[q] = P.pix[q] >= 0 ? (int)__ldg(I + P.pix[q]) : 0;
+        };
+        auto finish_chunk = [&](const Pend & P) {
           uint32_t rr[4];
 #pragma unroll
           for (int q = 0; q < 4; q++) {
-            const int r = val[q] - (int)(pk[q] >> 24);
-            rr[q] = pix[q] >= 0 ? (uint32_t)(uint16_t)(int16_t)r : (uint32_t)(uint16_t)R_INVISIBLE;
-            if (weighted && pix[q] >= 0) atomicAdd(&hist[r + 255], 1);
+            const int r = P.val[q] - (int)P.T[q];
+            rr[q] = P.pix[q] >= 0 ? (uint32_t)(uint16_t)(int16_t)r : (uint32_t)(uint16_t)R_INVISIBLE;
+            if (weighted && P.pix[q] >= 0) atomicAdd(&hist[r + 255], 1);
           }
-          if (g < p1) r4[g >> 2] = make_uint2(rr[0] | (rr[1] << 16), rr[2] | (rr[3] << 16));
-          __syncthreads();  // stage consumed by everybody: refill it
-          if (tid == 0 && ch + NS < nCh) issue_chunk(S, ring, V, false, p0, p1, ch + NS, item + NS);
+          if (P.g < p1) r4[P.g >> 2] = make_uint2(rr[0] | (rr[1] << 16), rr[2] | (rr[3] << 16));
+        };
+        Pend Pa, Pb;
+        int ch = 0;
+        if (nCh > 0) start_chunk(0, Pa);
+        for (ch = 1; ch + 1 < nCh; ch += 2) {
+          start_chunk(ch, Pb);
+          finish_chunk(Pa);
+          start_chunk(ch + 1, Pa);
+          finish_chunk(Pb);
         }
+        if (ch < nCh) {
+          start_chunk(ch, Pb);
+          finish_chunk(Pa);
+          finish_chunk(Pb);
+        } else if (nCh > 0) {
+          finish_chunk(Pa);
+        }
+        item += nCh;
       }
       // the residuals were written through the generic proxy and are read back by TMA (async proxy)
       asm volatile("fence.proxy.async;" ::: "memory");
@@ -403,14 +461,16 @@ __global__ void __launch_bounds__(GT, 2) gn_level_kernel(
       // ---------------------------------------------------------------- scale + weight table
       if (weighted) {
         cluster.sync();
-        int a = 0, b = 0;
+        int a[BPT];
+#pragma unroll
+        for (int j = 0; j < BPT; j++) a[j] = 0;
         for (unsigned rk = 0; rk < C; rk++) {
           const int * h = cluster.map_shared_rank(hist, rk);
-          a += h[tid];
-          b += h[tid + 256];
+#pragma unroll
+          for (int j = 0; j < BPT; j++) a[j] += h[tid + j * GT];
         }
-        S.tot[tid] = a;
-        S.tot[tid + 256] = b;
+#pragma unroll
+        for (int j = 0; j < BPT; j++) S.tot[tid + j * GT] = a[j];
         __syncthreads();
         scale_and_weights(V, p, S.tot, S.lut, S.red);
         __syncthreads();
@@ -425,6 +485,10 @@ __global__ void __launch_bounds__(GT, 2) gn_level_kernel(
         const double * __restrict__ lut = S.lut;
 #pragma unroll 1
         for (int ch = 0; ch < nCh; ch++, item++) {
+          if (tid == 0 && ch >= 1 && ch - 1 + NS < nCh) {
+            mbar_wait(&S.empty[(item - 1) % NS], ((item - 1) / NS) & 1);
+            issue_chunk(S, ring, V, true, p0, p1, ch - 1 + NS, item - 1 + NS);
+          }
           const unsigned char * st = ring + (size_t)(item % NS) * STAGE_BYTES;
           mbar_wait(&S.full[item % NS], (item / NS) & 1);
           const int g = p0 + ch * CH + 4 * tid;
@@ -433,6 +497,8 @@ __global__ void __launch_bounds__(GT, 2) gn_level_kernel(
           const double2 za = *reinterpret_cast<const double2 *>(st + OFF_ZI + tid * 32);
           const double2 zb = *reinterpret_cast<const double2 *>(st + OFF_ZI + tid * 32 + 16);
           const uint2 packed = *reinterpret_cast<const uint2 *>(st + OFF_R + tid * 8);
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&S.empty[item % NS]);
           const uint32_t pk[4] = {pk4.x, pk4.y, pk4.z, pk4.w};
           const uint32_t gg[4] = {gg4.x, gg4.y, gg4.z, gg4.w};
           const double zz[4] = {za.x, za.y, zb.x, zb.y};
@@ -475,21 +541,20 @@ __global__ void __launch_bounds__(GT, 2) gn_level_kernel(
             }
             acc[27] = fma(w * r, r, acc[27]);
           }
-          __syncthreads();
-          if (tid == 0 && ch + NS < nCh) issue_chunk(S, ring, V, true, p0, p1, ch + NS, item + NS);
         }
       }
+      __syncthreads();  // every warp is done with the ring
       // prologue of the next phase A (next keyframe, or keyframe 0 of the next iteration): the list does not
       // depend on the pose, so it streams in behind the reduction and the solve
       {
-        const ViewState & Vn = S.Vs[k + 1 < K ? k + 1 : 0];
+        const ViewState & Vn = Vs[k + 1 < K ? k + 1 : 0];
         int q0, q1;
         slice_of(Vn.nIp, C, rank, q0, q1);
         const int nChN = (q1 - q0 + CH - 1) / CH;
         if (tid == 0)
           for (int c = 0; c < min(NS, nChN); c++) issue_chunk(S, ring, Vn, false, q0, q1, c, item + c);
       }
-      // fixed-order block reduction: lanes (xor tree), then warps 0..7
+      // fixed-order block reduction: lanes (xor tree), then warps in order
 #pragma unroll
       for (int s = 0; s < NE_TERMS; s++) {
         double v = acc[s];
@@ -502,7 +567,7 @@ __global__ void __launch_bounds__(GT, 2) gn_level_kernel(
         double v = 0.0;
 #pragma unroll
         for (int w = 0; w < GT / 32; w++) v += S.red[w * NE_TERMS + tid];
-        S.partial[pb][k][tid] = v;
+        partial[(pb * K + k) * NE_TERMS + tid] = v;
       }
       __syncthreads();
     }
@@ -511,8 +576,8 @@ __global__ void __launch_bounds__(GT, 2) gn_level_kernel(
     for (int i = tid; i < K * NE_TERMS; i += GT) {
       const int k = i / NE_TERMS, t = i - k * NE_TERMS;
       double v = 0.0;
-      for (unsigned rk = 0; rk < C; rk++) v += cluster.map_shared_rank(&S.partial[pb][k][t], rk)[0];
-      S.sums[i] = v;
+      for (unsigned rk = 0; rk < C; rk++) v += cluster.map_shared_rank(&partial[(pb * K + k) * NE_TERMS + t], rk)[0];
+      sums[i] = v;
       if (viewSums && rank == 0) viewSums[(size_t)(S.J.view0 + k) * NE_TERMS + t] = v;
     }
     __syncthreads();
@@ -520,8 +585,8 @@ __global__ void __launch_bounds__(GT, 2) gn_level_kernel(
     if (tid == 0) {
       S.J.evals[level]++;
       S.J.pointIters += (unsigned long long)S.J.totalPoints;
-      gn_step(S.J, S.Vs, S.sums, p, level, (trace && rank == 0) ? trace + (size_t)job * traceJobStride : nullptr);
-      if (S.J.active && evals >= maxEvals) finish_level(S.J, S.Vs, level, VSLAMB200_STOP_MAXITER);
+      gn_step(S.J, Vs, sums, p, level, (trace && rank == 0) ? trace + (size_t)job * traceJobStride : nullptr);
+      if (S.J.active && evals >= maxEvals) finish_level(S.J, Vs, level, VSLAMB200_STOP_MAXITER);
     }
     __syncthreads();
     if (!S.J.active) break;
@@ -529,25 +594,25 @@ __global__ void __launch_bounds__(GT, 2) gn_level_kernel(
   // drain the speculative prologue of the phase A that will not run: no bulk copy may be in flight at exit
   {
     int p0, p1;
-    slice_of(S.Vs[0].nIp, C, rank, p0, p1);
+    slice_of(Vs[0].nIp, C, rank, p0, p1);
     const int nCh = (p1 - p0 + CH - 1) / CH;
     for (int c = 0; c < min(NS, nCh); c++) mbar_wait(&S.full[(item + c) % NS], ((item + c) / NS) & 1);
   }
   cluster.sync();  // nobody leaves while its shared memory may still be read remotely
   if (rank == 0) {
     block_copy(jobs + job, &S.J);
-    for (int k = 0; k < K; k++) block_copy(views + S.J.view0 + k, &S.Vs[k]);
+    for (int k = 0; k < K; k++) block_copy(views + S.J.view0 + k, &Vs[k]);
   }
 }
 
 size_t gn_level_static_smem() { return sizeof(LevelShared); }
 
 cudaError_t launch_gn_level(
-  JobState * jobs, ViewState * views, int nJobs, int clusterSize, SolverParams p, int level, int maxEvals,
-  double * trace, size_t traceJobStride, double * viewSums, cudaStream_t s)
+  JobState * jobs, ViewState * views, int nJobs, int maxViewsPerJob, int clusterSize, SolverParams p, int level,
+  int maxEvals, double * trace, size_t traceJobStride, double * viewSums, cudaStream_t s)
 {
   if (nJobs <= 0) return cudaSuccess;
-  const size_t dyn = (size_t)NS * STAGE_BYTES;
+  const size_t dyn = level_dyn_smem(maxViewsPerJob);
   cudaError_t e = cudaFuncSetAttribute(gn_level_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
   if (e != cudaSuccess) return e;
   cudaLaunchConfig_t cfg = {};
