@@ -23,5 +23,13 @@ ident = np.array([0, 0, 0, 1, 0, 0, 0.0])
 jobs = [dict(to=i + 1, to_pose=ident, frm=[i], from_poses=ident, multi=False) for i in range(args.frames - 1)]
 for _ in range(2):
     res = ctx.align(jobs)
-print("iters", res[0]["iters"][:args.levels], ctx.stats())
+st = ctx.stats()
+print("iters", res[0]["iters"][:args.levels])
+names = ["phaseA", "bar_hist", "scale", "phaseC", "blockred", "bar_sums", "solve"]
+for l in range(args.levels):
+    pc = st["phase_clocks"][l]
+    tot = sum(pc) or 1
+    print("level", l, "clocks/job-eval", {n: round(c / max(1, st["gn_iterations"]) , 1) for n, c in zip(names, pc)},
+          "share", {n: round(c / tot, 3) for n, c in zip(names, pc)})
+print({k: v for k, v in st.items() if k not in ("phase_clocks",)})
 ctx.close()

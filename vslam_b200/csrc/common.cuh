@@ -65,6 +65,7 @@ struct ViewState
   float rI[9], t32[3];      // R - I and t rounded to fp32
   float epsA, epsB;         // per-view terms of the fast-path error bound
   double xPred[6];          // MotionPrior::_xPred (SE3Alignment.cpp:32)
+  double xCur[6];           // log(se3), kept in step with se3
   // robust weights of the current iteration
   int * hist;               // HIST_BINS global bins
   float * wlut;             // HIST_BINS weights
@@ -93,6 +94,9 @@ struct JobState
   int totalPoints;          // sum of nIp over the job's views at the current level
   int evals[MAX_LEVELS];    // computeNormalEquations calls per level (completed steps + a final rejected one)
   unsigned long long pointIters;  // sum over evaluations of the interest points visited
+  // SM clocks spent by the cluster's rank-0 CTA per level: phase A, histogram barrier, scale + weights, phase C,
+  // block reduction, sums barrier, solve
+  long long clk[MAX_LEVELS][7];
 };
 
 struct SolverParams

@@ -74,10 +74,14 @@ __device__ void scale_and_weights(
 {
   const int tid = threadIdx.x;
   __shared__ double s_scale, s_offset;
-  // thread t owns bins t, t + GT, ... (bin b holds the residual value b - 255; bin 511 is unused)
+  // bin b holds the residual value b - 255 (bin 511 is unused).  Thread t owns bins (t + j*GT + 192) mod 512:
+  // j = 0 covers the central residuals -63..64, where nearly all the mass is, so the other j are skipped warp-wide
+  int bin[BPT];
+#pragma unroll
+  for (int j = 0; j < BPT; j++) bin[j] = (tid + j * GT + 192) & (HIST_BINS - 1);
   int c0 = 0;
 #pragma unroll
-  for (int j = 0; j < BPT; j++) c0 += h[tid + j * GT];
+  for (int j = 0; j < BPT; j++) c0 += h[bin[j]];
   const double vis = block_sum((double)c0, red);
   const long n = V.nIp;
   __syncthreads();
@@ -87,24 +91,26 @@ __device__ void scale_and_weights(
   double rv[BPT], nv[BPT];
 #pragma unroll
   for (int j = 0; j < BPT; j++) {
-    rv[j] = (double)(tid + j * GT - 255);
-    nv[j] = (double)h[tid + j * GT];
+    rv[j] = (double)(bin[j] - 255);
+    nv[j] = (double)h[bin[j]];
   }
   if (p.scalerKind == VSLAMB200_SCALER_TDIST) {
     // sigma^2 <- mean(r^2 (nu+1) / (nu + (r/sigma)^2)), from sigma = 1, <= 30 steps, until |step| <= 1e-5
-    double av[BPT];
+    // r^2 (nu+1) / (nu + r^2/sigma^2) == r^2 (nu+1) sigma^2 / (nu sigma^2 + r^2): one division per populated bin
+    double av[BPT], r2[BPT];
 #pragma unroll
-    for (int j = 0; j < BPT; j++) av[j] = nv[j] * (rv[j] * rv[j] * (p.scalerV + 1));
+    for (int j = 0; j < BPT; j++) {
+      r2[j] = rv[j] * rv[j];
+      av[j] = nv[j] * (r2[j] * (p.scalerV + 1));
+    }
     double step = 1.79769313486231570e308, sigma = 1.0;
     __syncthreads();
     for (int it = 0; it < 30 && step > 1e-5; it++) {
       double term = 0.0;
+      const double s2 = sigma * sigma, vs2 = p.scalerV * s2;
 #pragma unroll
       for (int j = 0; j < BPT; j++)
-        if (nv[j] > 0) {
-          const double q = rv[j] / sigma;
-          term += av[j] / (p.scalerV + q * q);
-        }
+        if (nv[j] > 0) term += (av[j] * s2) / (vs2 + r2[j]);
       // one barrier per step: warp partials alternate between two shared buffers
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) term += __shfl_xor_sync(0xffffffffu, term, o);
@@ -173,7 +179,7 @@ __device__ void scale_and_weights(
   __syncthreads();
   scale = s_scale;
 #pragma unroll
-  for (int j = 0; j < BPT; j++) lut[tid + j * GT] = loss_weight(p, (rv[j] - offset) / scale);
+  for (int j = 0; j < BPT; j++) lut[bin[j]] = loss_weight(p, (rv[j] - offset) / scale);
 }
 
 // Exact warp of one interest point, operation for operation the oracle's (fp64, explicit fma):
@@ -285,6 +291,7 @@ struct LevelShared
   int tot[HIST_BINS];
   double lut[HIST_BINS];
   double red[GT / 32 * NE_TERMS];
+  SolveScratch X;
   alignas(8) uint64_t full[NS];   // TMA bytes of the stage have landed
   alignas(8) uint64_t empty[NS];  // every warp has copied the stage into registers
 };
@@ -371,6 +378,14 @@ __global__ void __launch_bounds__(GT, CTAS_PER_SM) gn_level_kernel(
       for (int c = 0; c < min(NS, nCh); c++) issue_chunk(S, ring, Vs[0], false, p0, p1, c, item + c);
   }
 
+  long long tc = clock64();
+  auto lap = [&](int slot) {
+    if (tid == 0) {
+      const long long now = clock64();
+      S.J.clk[level][slot] += now - tc;
+      tc = now;
+    }
+  };
   for (;;) {
     const int pb = evals & 1;
     for (int k = 0; k < K; k++) {
@@ -458,9 +473,11 @@ __global__ void __launch_bounds__(GT, CTAS_PER_SM) gn_level_kernel(
       __syncthreads();
       if (tid == 0)
         for (int c = 0; c < min(NS, nCh); c++) issue_chunk(S, ring, V, true, p0, p1, c, item + c);
+      lap(0);
       // ---------------------------------------------------------------- scale + weight table
       if (weighted) {
         cluster.sync();
+        lap(1);
         int a[BPT];
 #pragma unroll
         for (int j = 0; j < BPT; j++) a[j] = 0;
@@ -475,6 +492,7 @@ __global__ void __launch_bounds__(GT, CTAS_PER_SM) gn_level_kernel(
         scale_and_weights(V, p, S.tot, S.lut, S.red);
         __syncthreads();
         hb ^= 1;
+        lap(2);
       }
       // ---------------------------------------------------------------- phase C
       double acc[NE_TERMS];
@@ -544,6 +562,7 @@ __global__ void __launch_bounds__(GT, CTAS_PER_SM) gn_level_kernel(
         }
       }
       __syncthreads();  // every warp is done with the ring
+      lap(3);
       // prologue of the next phase A (next keyframe, or keyframe 0 of the next iteration): the list does not
       // depend on the pose, so it streams in behind the reduction and the solve
       {
@@ -571,6 +590,7 @@ __global__ void __launch_bounds__(GT, CTAS_PER_SM) gn_level_kernel(
       }
       __syncthreads();
     }
+    lap(4);
     // ------------------------------------------------------------------ cluster reduction + solve
     cluster.sync();
     for (int i = tid; i < K * NE_TERMS; i += GT) {
@@ -581,14 +601,15 @@ __global__ void __launch_bounds__(GT, CTAS_PER_SM) gn_level_kernel(
       if (viewSums && rank == 0) viewSums[(size_t)(S.J.view0 + k) * NE_TERMS + t] = v;
     }
     __syncthreads();
+    lap(5);
     evals++;
     if (tid == 0) {
       S.J.evals[level]++;
       S.J.pointIters += (unsigned long long)S.J.totalPoints;
-      gn_step(S.J, Vs, sums, p, level, (trace && rank == 0) ? trace + (size_t)job * traceJobStride : nullptr);
-      if (S.J.active && evals >= maxEvals) finish_level(S.J, Vs, level, VSLAMB200_STOP_MAXITER);
     }
-    __syncthreads();
+    gn_step_block(S.J, Vs, sums, S.X, p, level, (trace && rank == 0) ? trace + (size_t)job * traceJobStride : nullptr,
+                  evals >= maxEvals);
+    lap(6);
     if (!S.J.active) break;
   }
   // drain the speculative prologue of the phase A that will not run: no bulk copy may be in flight at exit

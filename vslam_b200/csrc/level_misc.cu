@@ -51,6 +51,7 @@ __global__ void level_setup_kernel(
   V.offset = 0.0;
   V.se3 = se3_mul(J.pose, se3_inv(V.poseRef));
   view_set_warp(V);
+  view_set_x(V);
   se3_log(se3_mul(J.toPose, se3_inv(V.poseRef)), V.xPred);  // MotionPrior ctor (SE3Alignment.cpp:32)
   if (vi == J.view0) {
     J.iter = 0;
@@ -59,6 +60,7 @@ __global__ void level_setup_kernel(
     J.active = J.dead ? 0 : 1;
     for (int k = 0; k < 6; k++) J.xPrev[k] = 0.0;
     J.evals[level] = 0;
+    for (int k = 0; k < 7; k++) J.clk[level][k] = 0;
   }
 }
 

@@ -119,6 +119,9 @@ static __device__ __noinline__ void inverse6(const double * A, double * out)
     for (int j = 0; j < 6; j++) out[i * 6 + j] = m[i][6 + j];
 }
 
+// x() of the view's problem: log of the current relative transform (Warp.cpp:157)
+__host__ __device__ inline void view_set_x(ViewState & V) { se3_log(V.se3, V.xCur); }
+
 __host__ __device__ inline void view_set_warp(ViewState & V)
 {
   quat_to_R(V.se3.q, V.R);
@@ -161,100 +164,166 @@ static __device__ __noinline__ void finish_level(JobState & J, ViewState * jv, i
   J.pose = se3_mul(V0.se3, V0.poseRef);  // WarpSE3::poseCur (Warp.cpp:239)
 }
 
-// One GaussNewton::solve iteration (GaussNewton.cpp:44-99) on the stacked, normalised, prior-augmented
-// normal equations.  sums: per view 28 raw terms (21 upper A, 6 b, chi2), view-major.
-static __device__ __noinline__ void gn_step(
-  JobState & J, ViewState * jv, const double * sums, const SolverParams & p, int level, double * trace)
+// Scratch of the block-cooperative Gauss-Newton step (shared memory).
+struct SolveScratch
 {
-  double A[36], b[6], chi2 = 0.0;
-  for (int i = 0; i < 36; i++) A[i] = 0.0;
-  for (int i = 0; i < 6; i++) b[i] = 0.0;
-  long nTotal = 0;
-  for (int k = 0; k < J.nViews; k++) {
-    ViewState & V = jv[k];
-    const double * s = sums + k * NE_TERMS;
-    double Av[36], bv[6], c2 = s[27];
+  double ne[NE_TERMS];  // stacked, normalised, prior-augmented terms: 21 upper A, 6 b, chi2
+  double A[36];
+  double dx[6];
+  double det;
+  double dChi2;
+  Pose inc;             // exp(-dx)
+  long nTotal;
+  int decision;         // -1: accept the step, else VSLAMB200_STOP_*
+};
+
+// One GaussNewton::solve iteration (GaussNewton.cpp:44-99) on the stacked, normalised, prior-augmented
+// normal equations, executed by the whole thread block (>= 64 threads; contains block barriers):
+//   1. threads 0..27 assemble one term each over the job's views (InverseCompositional.cpp:139-147,
+//      MotionPrior::apply SE3Alignment.cpp:37-47, InverseCompositionalStacked.cpp:45-46)
+//   2. thread 0 takes the determinant while thread 32 solves and exponentiates the step
+//   3. thread 0 decides (GaussNewton.cpp:53-75); on acceptance the views are updated in parallel
+//      (one thread per view composes, then logarithm and warp constants side by side)
+//   4. thread 0 records the step and applies the convergence rules (GaussNewton.cpp:77-98)
+// sums: per view 28 raw terms (21 upper A, 6 b, chi2), view-major.  forceStop: end the level after this step.
+__device__ __forceinline__ void gn_step_block(
+  JobState & J, ViewState * jv, const double * sums, SolveScratch & X, const SolverParams & p, int level,
+  double * trace, bool forceStop)
+{
+  const int tid = threadIdx.x;
+  const int K = J.nViews;
+  // ---- 1. assemble
+  if (tid < NE_TERMS) {
+    // which entry of A / b this term is
+    int di = -1, bi = -1;  // diagonal index / b index
+    {
+      int idx = 0;
+      for (int i = 0; i < 6; i++)
+        for (int j = i; j < 6; j++) {
+          if (idx == tid && i == j) di = i;
+          idx++;
+        }
+      if (tid >= 21 && tid < 27) bi = tid - 21;
+    }
+    double acc = 0.0;
+    long nTotal = 0;
+    for (int k = 0; k < K; k++) {
+      const ViewState & V = jv[k];
+      double v = sums[k * NE_TERMS + tid];
+      const long n = V.nIp;
+      if (n > 1) v /= (double)n;                 // InverseCompositional.cpp:139-143
+      if (p.includePrior && tid < 27) {          // MotionPrior::apply (chi2 is left alone)
+        v *= 1.0 / (255.0 * 255.0);
+        if (di >= 0) v += 1.0;
+        if (bi >= 0) v += V.xPred[bi] - V.xCur[bi];
+      }
+      acc += v;
+      nTotal += n;
+    }
+    X.ne[tid] = acc;
+    if (tid == 0) X.nTotal = nTotal;
+  }
+  __syncthreads();
+  // ---- 2. determinant || solve
+  if (tid == 0 || tid == 32) {
+    double A[36], b[6];
     int idx = 0;
+#pragma unroll
     for (int i = 0; i < 6; i++)
+#pragma unroll
       for (int j = i; j < 6; j++) {
-        Av[i * 6 + j] = s[idx];
-        Av[j * 6 + i] = s[idx++];
+        A[i * 6 + j] = X.ne[idx];
+        A[j * 6 + i] = X.ne[idx];
+        idx++;
       }
-    for (int i = 0; i < 6; i++) bv[i] = s[21 + i];
-    const long n = V.nIp;
-    if (n > 1) {  // InverseCompositional.cpp:139-143
-      const double dn = (double)n;
-      for (int i = 0; i < 36; i++) Av[i] /= dn;
-      for (int i = 0; i < 6; i++) bv[i] /= dn;
-      c2 /= dn;
-    }
-    if (p.includePrior) {  // MotionPrior::apply (SE3Alignment.cpp:37-47)
-      const double normalizer = 1.0 / (255.0 * 255.0);
-      double x[6];
-      se3_log(V.se3, x);
-      for (int i = 0; i < 36; i++) Av[i] *= normalizer;
-      for (int i = 0; i < 6; i++) bv[i] *= normalizer;
+    if (tid == 0) {
+#pragma unroll
+      for (int i = 0; i < 36; i++) X.A[i] = A[i];
+      X.det = det6(A);
+    } else {
+#pragma unroll
+      for (int i = 0; i < 6; i++) b[i] = X.ne[21 + i];
+      double dx[6], mdx[6];
+      ldlt_solve(A, b, dx);
+#pragma unroll
       for (int i = 0; i < 6; i++) {
-        Av[i * 6 + i] += 1.0;
-        bv[i] += V.xPred[i] - x[i];
+        X.dx[i] = dx[i];
+        mdx[i] = -dx[i];
+      }
+      X.inc = se3_exp(mdx);  // updateCompositional(-dx) (InverseCompositional.cpp:104, Warp.cpp:153-157)
+    }
+  }
+  __syncthreads();
+  // ---- 3. decision
+  const int it = J.iter;
+  if (tid == 0) {
+    const double chi2 = X.ne[27];
+    int dec = -1;
+    X.dChi2 = it > 0 ? chi2 - J.chi2Prev : 0.0;
+    if (X.nTotal < 6)
+      dec = VSLAMB200_STOP_CONSTRAINTS;
+    else if (!isfinite(X.det) || fabs(X.det) < 1e-6)
+      dec = VSLAMB200_STOP_HESSIAN;
+    else if (it > 0 && X.dChi2 > 0)
+      dec = VSLAMB200_STOP_CHI2;
+    X.decision = dec;
+  }
+  __syncthreads();
+  if (X.decision < 0) {
+    if (tid < K) jv[tid].se3 = se3_mul(jv[tid].se3, X.inc);
+    __syncthreads();
+    if (tid < K) se3_log(jv[tid].se3, jv[tid].xCur);
+    if (tid >= 32 && tid < 32 + K) view_set_warp(jv[tid - 32]);
+    __syncthreads();
+  }
+  // ---- 4. bookkeeping and stop rules
+  if (tid == 0) {
+    int stop = X.decision;
+    bool rollback = stop == VSLAMB200_STOP_CHI2;  // problem->setX(x.row(i-1)) (GaussNewton.cpp:73)
+    if (stop < 0) {
+      const double * x = jv[0].xCur;
+      double nrm = 0;
+#pragma unroll
+      for (int k = 0; k < 6; k++) nrm += X.dx[k] * X.dx[k];
+      const double step = sqrt(nrm);
+#pragma unroll
+      for (int k = 0; k < 36; k++) J.lastA[k] = X.A[k];
+      J.nPushed++;
+      if (trace) {
+        double * t = trace + ((size_t)level * p.maxIterations + it) * TRACE_STRIDE;
+        t[0] = 1;
+        t[1] = (double)X.nTotal;
+        t[2] = X.ne[27];
+        t[3] = step;
+        t[4] = jv[0].scale;
+        t[5] = jv[0].offset;
+        for (int k = 0; k < 6; k++) t[6 + k] = x[k];
+        for (int k = 0; k < 6; k++) t[12 + k] = X.ne[21 + k];
+        for (int k = 0; k < 36; k++) t[18 + k] = X.A[k];
+        for (int k = 0; k < 6; k++) t[54 + k] = X.dx[k];
+      }
+      double bmax = X.ne[21];
+#pragma unroll
+      for (int k = 1; k < 6; k++) bmax = fmax(bmax, X.ne[21 + k]);
+      if (it > 0 && (step < p.minStepSize || fabs(bmax) < p.minStepSize || fabs(X.dChi2) < p.minStepSize)) {
+        stop = VSLAMB200_STOP_CONVERGED;
+      } else if (!isfinite(step)) {
+        stop = VSLAMB200_STOP_NAN;
+        rollback = it > 0;
+      } else {
+#pragma unroll
+        for (int k = 0; k < 6; k++) J.xPrev[k] = x[k];
+        J.chi2Prev = X.ne[27];
+        J.iter = it + 1;
+        if (J.iter >= p.maxIterations || forceStop) stop = VSLAMB200_STOP_MAXITER;
       }
     }
-    for (int i = 0; i < 36; i++) A[i] += Av[i];
-    for (int i = 0; i < 6; i++) b[i] += bv[i];
-    chi2 += c2;
-    nTotal += n;
+    if (stop >= 0) {
+      if (rollback)
+        for (int k = 0; k < K; k++) jv[k].se3 = se3_exp(J.xPrev);  // se3 = exp(x) for every stacked frame
+      finish_level(J, jv, level, stop);
+    }
   }
-  const int i = J.iter;
-  const double det = det6(A);
-  if (nTotal < 6) return finish_level(J, jv, level, VSLAMB200_STOP_CONSTRAINTS);
-  if (!isfinite(det) || fabs(det) < 1e-6) return finish_level(J, jv, level, VSLAMB200_STOP_HESSIAN);
-  const double dChi2 = i > 0 ? chi2 - J.chi2Prev : 0.0;
-  if (i > 0 && dChi2 > 0) {
-    // problem->setX(x.row(i-1)) (GaussNewton.cpp:73): se3 = exp(x) for every stacked frame
-    for (int k = 0; k < J.nViews; k++) jv[k].se3 = se3_exp(J.xPrev);
-    return finish_level(J, jv, level, VSLAMB200_STOP_CHI2);
-  }
-  double dx[6], mdx[6];
-  ldlt_solve(A, b, dx);
-  for (int k = 0; k < 6; k++) mdx[k] = -dx[k];
-  const Pose inc = se3_exp(mdx);  // updateCompositional(-dx) (InverseCompositional.cpp:104, Warp.cpp:153-157)
-  for (int k = 0; k < J.nViews; k++) {
-    ViewState & V = jv[k];
-    V.se3 = se3_mul(V.se3, inc);
-  }
-  double x[6];
-  se3_log(jv[0].se3, x);
-  double nrm = 0;
-  for (int k = 0; k < 6; k++) nrm += dx[k] * dx[k];
-  const double step = sqrt(nrm);
-  for (int k = 0; k < 36; k++) J.lastA[k] = A[k];
-  J.nPushed++;
-  if (trace) {
-    double * t = trace + ((size_t)level * p.maxIterations + i) * TRACE_STRIDE;
-    t[0] = 1;
-    t[1] = (double)nTotal;
-    t[2] = chi2;
-    t[3] = step;
-    t[4] = jv[0].scale;
-    t[5] = jv[0].offset;
-    for (int k = 0; k < 6; k++) t[6 + k] = x[k];
-    for (int k = 0; k < 6; k++) t[12 + k] = b[k];
-    for (int k = 0; k < 36; k++) t[18 + k] = A[k];
-    for (int k = 0; k < 6; k++) t[54 + k] = dx[k];
-  }
-  double bmax = b[0];
-  for (int k = 1; k < 6; k++) bmax = fmax(bmax, b[k]);
-  if (i > 0 && (step < p.minStepSize || fabs(bmax) < p.minStepSize || fabs(dChi2) < p.minStepSize))
-    return finish_level(J, jv, level, VSLAMB200_STOP_CONVERGED);
-  if (!isfinite(step)) {
-    if (i > 0)
-      for (int k = 0; k < J.nViews; k++) jv[k].se3 = se3_exp(J.xPrev);
-    return finish_level(J, jv, level, VSLAMB200_STOP_NAN);
-  }
-  for (int k = 0; k < 6; k++) J.xPrev[k] = x[k];
-  J.chi2Prev = chi2;
-  J.iter = i + 1;
-  if (J.iter >= p.maxIterations) return finish_level(J, jv, level, VSLAMB200_STOP_MAXITER);
-  for (int k = 0; k < J.nViews; k++) view_set_warp(jv[k]);
+  __syncthreads();
 }
 }  // namespace vb
