@@ -14,6 +14,7 @@ constexpr int NE_TERMS = 28;           // 21 (upper A) + 6 (b) + 1 (chi2)
 constexpr int TRACE_STRIDE = VSLAMB200_TRACE_STRIDE;
 constexpr int16_t R_NOT_INTEREST = -32768;
 constexpr int16_t R_INVISIBLE = -32767;
+constexpr int R_CODE_INVISIBLE = HIST_BINS - 1;  // device-side residual code: r + 255, or 511 when not visible
 
 // One frame's pyramid in HBM.  All planes are row-major, tightly packed (pitch == width).
 struct FrameDev
@@ -55,7 +56,7 @@ struct ViewState
   float * d;                // depth of the point
   double * zi;              // 1 / depth in fp64 (Warp.cpp:170 zi), computed once per level
   uint32_t * g;             // dIx (low 16) | dIy (high 16)
-  int16_t * r;              // residual of the current iteration (R_INVISIBLE if not visible)
+  int16_t * r;              // residual code of the current iteration: r + 255, R_CODE_INVISIBLE if not visible
   int nIp;                  // retained interest points (nConstraints of this view)
   // warp
   Pose poseRef;             // keyframe pose

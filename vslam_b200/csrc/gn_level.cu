@@ -69,8 +69,9 @@ __device__ __forceinline__ double loss_weight(const SolverParams & p, double r)
 
 // Scale / offset from the residual histogram (h[b] = #visible points with r = b-255; invisible points
 // count as r = 0, InverseCompositional.cpp:111,130) and the weight table.  Whole block.
-__device__ void scale_and_weights(
-  ViewState & V, const SolverParams & p, int * h /* smem 512 */, double * lut /* smem 512 */, double * red)
+// Also returns chi2 = sum_k w_k r_k^2 (NormalEquations.cpp:58), which is a function of the histogram too.
+__device__ double scale_and_weights(
+  ViewState & V, const SolverParams & p, int * h /* smem 512 */, double2 * lut /* smem 512: {w, w r} */, double * red)
 {
   const int tid = threadIdx.x;
   __shared__ double s_scale, s_offset;
@@ -84,6 +85,9 @@ __device__ void scale_and_weights(
   for (int j = 0; j < BPT; j++) c0 += h[bin[j]];
   const double vis = block_sum((double)c0, red);
   const long n = V.nIp;
+  double nvis[BPT];  // visible points per bin (before the zeros of the invisible points join bin 255)
+#pragma unroll
+  for (int j = 0; j < BPT; j++) nvis[j] = (double)h[bin[j]];
   __syncthreads();
   if (tid == 0) h[255] += (int)(n - (long)vis);  // zeros of the invisible points
   __syncthreads();
@@ -178,8 +182,15 @@ __device__ void scale_and_weights(
   }
   __syncthreads();
   scale = s_scale;
+  double c2 = 0.0;
 #pragma unroll
-  for (int j = 0; j < BPT; j++) lut[bin[j]] = loss_weight(p, (rv[j] - offset) / scale);
+  for (int j = 0; j < BPT; j++) {
+    const double w = p.lossKind == VSLAMB200_LOSS_NONE ? 1.0 : loss_weight(p, (rv[j] - offset) / scale);
+    const double wr = w * rv[j];
+    lut[bin[j]] = bin[j] == HIST_BINS - 1 ? make_double2(0.0, 0.0) : make_double2(w, wr);  // 511: not visible
+    c2 = fma(nvis[j], wr * rv[j], c2);
+  }
+  return block_sum(c2, red);
 }
 
 // Exact warp of one interest point, operation for operation the oracle's (fp64, explicit fma):
@@ -207,36 +218,74 @@ struct WarpConsts
   int Wt, Ht;
 };
 
+// Rare continuation of warp_fast(): the fp32 result is trustworthy (ok) but the rounded target lies on the
+// border ring or outside the image, or it is not trustworthy at all.
+__device__ __noinline__ int warp_slow(const ViewState & V, int u, int v, float d, float du, float dv, float eps, int iu,
+                                      int iv, bool ok)
+{
+  if (ok) {
+    // visibility is 1 < u' < W-1 and 1 < v' < H-1 with u' in (iu - 0.5, iu + 0.5): clearly outside, or on the
+    // ring iu == 1 / iu == W-1, where the displacement is compared with the exact integer offset of the boundary
+    const int Wt = V.Wt, Ht = V.Ht;
+    if (iu < 1 || iu > Wt - 1 || iv < 1 || iv > Ht - 1) return -1;
+    bool sure = true, vis = true;
+    if (iu == 1) {
+      const float l = du - (float)(1 - u);
+      sure = sure && fabsf(l) > eps;
+      vis = vis && l > 0.f;
+    }
+    if (iu == Wt - 1) {
+      const float r = (float)(Wt - 1 - u) - du;
+      sure = sure && fabsf(r) > eps;
+      vis = vis && r > 0.f;
+    }
+    if (iv == 1) {
+      const float l = dv - (float)(1 - v);
+      sure = sure && fabsf(l) > eps;
+      vis = vis && l > 0.f;
+    }
+    if (iv == Ht - 1) {
+      const float r = (float)(Ht - 1 - v) - dv;
+      sure = sure && fabsf(r) > eps;
+      vis = vis && r > 0.f;
+    }
+    if (sure) return vis ? iv * Wt + iu : -1;
+  }
+  return warp_exact(V, u, v, d);
+}
+
 // Sampled target pixel index of one interest point, or -1 when it is not visible.  The index and the
 // visibility flag are integer decisions and must be the fp64 oracle's.  A filtered evaluation gets them
 // without fp64 in the common case: in exact arithmetic u' = u + fx*(Dx - xn*Dz)/(z + Dz) with
 // D = (R - I) p + t, because p was back-projected from the integer pixel (u, v).  The displacement is
 // small, so fp32 carries it with an absolute error far below a pixel; only when it lands within the
-// error bound eps of a rounding boundary (u' = k + 0.5) or of a visibility boundary (u' = 1, W-1; v' = 1,
-// H-1) is the point re-evaluated by warp_exact().
-__device__ __forceinline__ int warp_filtered(const ViewState & V, const WarpConsts & c, int u, int v, float d)
+// error bound eps of a rounding boundary (u' = k + 0.5), or the rounded target is not strictly inside the
+// border ring, does warp_slow() take over (visibility boundaries u' = 1, W-1, v' = 1, H-1, or warp_exact()).
+__device__ __forceinline__ int warp_fast(const ViewState & V, const WarpConsts & c, uint32_t pk, float d)
 {
+  const int u = pk & 0xfff, v = (pk >> 12) & 0xfff;
   const float xn = fmaf((float)u, c.ifx, c.kx), yn = fmaf((float)v, c.ify, c.ky);
   const float px = xn * d, py = yn * d;
   const float Dx = fmaf(c.r02, d, fmaf(c.r01, py, fmaf(c.r00, px, c.t0)));
   const float Dy = fmaf(c.r12, d, fmaf(c.r11, py, fmaf(c.r10, px, c.t1)));
   const float Dz = fmaf(c.r22, d, fmaf(c.r21, py, fmaf(c.r20, px, c.t2)));
   const float qz = d + Dz;
-  const float iz = __frcp_rn(qz);
-  const float du = c.fx * fmaf(-xn, Dz, Dx) * iz;
-  const float dv = c.fy * fmaf(-yn, Dz, Dy) * iz;
-  // distance of the displacement to the nearest half-integer (u, v are integers: rounding boundaries of u')
-  const float hu = du - 0.5f, hv = dv - 0.5f;
-  const float distu = fabsf(hu - rintf(hu)), distv = fabsf(hv - rintf(hv));
-  // distance to the four visibility boundaries, as exact integer offsets of the displacement
-  const float lu = du - (float)(1 - u), ru = (float)(c.Wt - 1 - u) - du;
-  const float lv = dv - (float)(1 - v), rv = (float)(c.Ht - 1 - v) - dv;
-  const float dist = fminf(fminf(distu, distv), fminf(fminf(fabsf(lu), fabsf(ru)), fminf(fabsf(lv), fabsf(rv))));
-  const float eps = fmaf(c.epsA, d, c.epsB) * fabsf(iz) + 3.8e-6f * (fabsf(du) + fabsf(dv)) + 6.1e-5f;
-  if (!(qz > 0.25f * d) || !(dist > eps) || !(fabsf(du) + fabsf(dv) < 4096.f)) return warp_exact(V, u, v, d);
-  const bool vis = lu > 0.f && ru > 0.f && lv > 0.f && rv > 0.f;
-  const int iu = u + __float2int_rd(du + 0.5f), iv = v + __float2int_rd(dv + 0.5f);
-  return vis ? iv * c.Wt + iu : -1;
+  float iz;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(iz) : "f"(qz));  // 1 ulp; covered by the 2^-18 (|du|+|dv|) term of eps
+  const float du = (c.fx * iz) * fmaf(-xn, Dz, Dx);
+  const float dv = (c.fy * iz) * fmaf(-yn, Dz, Dy);
+  // nearest integer of the displacement through the 1.5 * 2^23 trick (|du| < 4096 is checked below)
+  const float MAGIC = 12582912.f;
+  const float mu = du + MAGIC, mv = dv + MAGIC;
+  const float fu = du - (mu - MAGIC), fv = dv - (mv - MAGIC);  // in [-0.5, 0.5]
+  const int iu = u + (__float_as_int(mu) - 0x4B400000), iv = v + (__float_as_int(mv) - 0x4B400000);
+  const float dist = 0.5f - fmaxf(fabsf(fu), fabsf(fv));       // distance to the nearest rounding boundary
+  const float s = fabsf(du) + fabsf(dv);
+  const float eps = fmaf(fmaf(c.epsA, d, c.epsB), fabsf(iz), fmaf(3.8e-6f, s, 6.1e-5f));
+  const bool ok = qz > 0.25f * d && dist > eps && s < 4096.f;
+  const bool inside = (unsigned)(iu - 2) <= (unsigned)(c.Wt - 4) && (unsigned)(iv - 2) <= (unsigned)(c.Ht - 4);
+  if (ok && inside) return iv * c.Wt + iu;
+  return warp_slow(V, u, v, d, du, dv, eps, iu, iv, ok);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -288,8 +337,7 @@ struct LevelShared
 {
   JobState J;
   int hist[2][HIST_BINS];
-  int tot[HIST_BINS];
-  double lut[HIST_BINS];
+  double2 lut[HIST_BINS];  // {w(r), w(r) r} per residual code; code 511 (not visible) -> {0, 0}
   double red[GT / 32 * NE_TERMS];
   SolveScratch X;
   alignas(8) uint64_t full[NS];   // TMA bytes of the stage have landed
@@ -365,7 +413,6 @@ __global__ void __launch_bounds__(GT, CTAS_PER_SM) gn_level_kernel(
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
-  const bool weighted = p.lossKind != VSLAMB200_LOSS_NONE;
   int hb = 0, evals = 0;
   uint32_t item = 0;  // chunks consumed so far == ring position of the next chunk (uniform over the CTA)
 
@@ -394,11 +441,9 @@ __global__ void __launch_bounds__(GT, CTAS_PER_SM) gn_level_kernel(
       slice_of(V.nIp, C, rank, p0, p1);
       const int nCh = (p1 - p0 + CH - 1) / CH;
       int * hist = S.hist[hb];
-      if (weighted) {
 #pragma unroll
-        for (int j = 0; j < BPT; j++) hist[tid + j * GT] = 0;
-        __syncthreads();
-      }
+      for (int j = 0; j < BPT; j++) hist[tid + j * GT] = 0;
+      __syncthreads();
       // ---------------------------------------------------------------- phase A
       {
         WarpConsts c;
@@ -407,6 +452,7 @@ __global__ void __launch_bounds__(GT, CTAS_PER_SM) gn_level_kernel(
         c.t0 = V.t32[0]; c.t1 = V.t32[1]; c.t2 = V.t32[2];
         c.fx = V.fx32; c.fy = V.fy32; c.ifx = V.ifxH; c.ify = V.ifyH; c.kx = V.kxH; c.ky = V.kyH;
         c.epsA = V.epsA; c.epsB = V.epsB; c.Wt = V.Wt; c.Ht = V.Ht;
+        if (V.Wt < 4 || V.Ht < 4) c.epsB = __int_as_float(0x7f800000);  // no strict interior: always the exact path
         const uint8_t * __restrict__ I = V.I;
         uint2 * __restrict__ r4 = reinterpret_cast<uint2 *>(V.r);
         // Software pipeline: the gathers of chunk ch are issued, then chunk ch-1 (whose gathers have had a whole
@@ -433,9 +479,9 @@ __global__ void __launch_bounds__(GT, CTAS_PER_SM) gn_level_kernel(
           P.g = p0 + ch * CH + 4 * tid;
 #pragma unroll
           for (int q = 0; q < 4; q++) {
-            P.pix[q] = -1;
             P.T[q] = pk[q] >> 24;
-            if (P.g + q < p1) P.pix[q] = warp_filtered(V, c, pk[q] & 0xfff, (pk[q] >> 12) & 0xfff, dd[q]);
+            const int px = warp_fast(V, c, pk[q], dd[q]);  // padding lanes compute on stale ring data: harmless
+            P.pix[q] = P.g + q < p1 ? px : -1;
           }
 #pragma unroll
           for (int q = 0; q < 4; q++) P.val[q] = P.pix[q] >= 0 ? (int)__ldg(I + P.pix[q]) : 0;
@@ -445,8 +491,8 @@ __global__ void __launch_bounds__(GT, CTAS_PER_SM) gn_level_kernel(
 #pragma unroll
           for (int q = 0; q < 4; q++) {
             const int r = P.val[q] - (int)P.T[q];
-            rr[q] = P.pix[q] >= 0 ? (uint32_t)(uint16_t)(int16_t)r : (uint32_t)(uint16_t)R_INVISIBLE;
-            if (weighted && P.pix[q] >= 0) atomicAdd(&hist[r + 255], 1);
+            rr[q] = P.pix[q] >= 0 ? (uint32_t)(r + 255) : (uint32_t)R_CODE_INVISIBLE;  // residual code
+            if (P.pix[q] >= 0) atomicAdd(&hist[r + 255], 1);
           }
           if (P.g < p1) r4[P.g >> 2] = make_uint2(rr[0] | (rr[1] << 16), rr[2] | (rr[3] << 16));
         };
@@ -475,7 +521,8 @@ __global__ void __launch_bounds__(GT, CTAS_PER_SM) gn_level_kernel(
         for (int c = 0; c < min(NS, nCh); c++) issue_chunk(S, ring, V, true, p0, p1, c, item + c);
       lap(0);
       // ---------------------------------------------------------------- scale + weight table
-      if (weighted) {
+      double chi2View;
+      {
         cluster.sync();
         lap(1);
         int a[BPT];
@@ -486,10 +533,12 @@ __global__ void __launch_bounds__(GT, CTAS_PER_SM) gn_level_kernel(
 #pragma unroll
           for (int j = 0; j < BPT; j++) a[j] += h[tid + j * GT];
         }
+        // the other histogram buffer is idle (its last remote readers passed a cluster barrier since): totals go there
+        int * tot = S.hist[hb ^ 1];
 #pragma unroll
-        for (int j = 0; j < BPT; j++) S.tot[tid + j * GT] = a[j];
+        for (int j = 0; j < BPT; j++) tot[tid + j * GT] = a[j];
         __syncthreads();
-        scale_and_weights(V, p, S.tot, S.lut, S.red);
+        chi2View = scale_and_weights(V, p, tot, S.lut, S.red);
         __syncthreads();
         hb ^= 1;
         lap(2);
@@ -500,7 +549,7 @@ __global__ void __launch_bounds__(GT, CTAS_PER_SM) gn_level_kernel(
       for (int s = 0; s < NE_TERMS; s++) acc[s] = 0.0;
       {
         const double ifx = V.ifx, ify = V.ify, kx = V.kx, ky = V.ky, fxJ = V.fxJd, fyJ = V.fyJd;
-        const double * __restrict__ lut = S.lut;
+        const double2 * __restrict__ lut = S.lut;
 #pragma unroll 1
         for (int ch = 0; ch < nCh; ch++, item++) {
           if (tid == 0 && ch >= 1 && ch - 1 + NS < nCh) {
@@ -520,22 +569,20 @@ __global__ void __launch_bounds__(GT, CTAS_PER_SM) gn_level_kernel(
           const uint32_t pk[4] = {pk4.x, pk4.y, pk4.z, pk4.w};
           const uint32_t gg[4] = {gg4.x, gg4.y, gg4.z, gg4.w};
           const double zz[4] = {za.x, za.y, zb.x, zb.y};
-          const int rq[4] = {(int)(int16_t)(packed.x & 0xffff), (int)(int16_t)(packed.x >> 16),
-                             (int)(int16_t)(packed.y & 0xffff), (int)(int16_t)(packed.y >> 16)};
+          const int rq[4] = {(int)(packed.x & 0xffff), (int)(packed.x >> 16), (int)(packed.y & 0xffff),
+                             (int)(packed.y >> 16)};  // residual codes: r + 255, or 511 when not visible
 #pragma unroll
           for (int q = 0; q < 4; q++) {
             // branch-free: a point outside the slice or not visible gets weight 0 (and a zero Jacobian when its
-            // list entry is padding), which adds exact zeros - the oracle skips w == 0 points the same way
-            const bool inside = g + q < p1;
-            const bool use = inside && rq[q] != R_INVISIBLE;
+            // list entry is padding), which adds exact zeros - the oracle skips w == 0 points the same way.
             // WarpSE3::J rows (Warp.cpp:184-199) contracted with the template gradient
             // (InverseCompositional.cpp:79-80), in normalised coordinates xn = x/z, yn = y/z
+            const bool inside = g + q < p1;
             const double u = (double)(int)(pk[q] & 0xfff), v = (double)(int)((pk[q] >> 12) & 0xfff);
             const double a = inside ? (double)(int)(int16_t)(gg[q] & 0xffff) * fxJ : 0.0;  // dIx * fx
             const double b = inside ? (double)(int)(int16_t)(gg[q] >> 16) * fyJ : 0.0;     // dIy * fy
-            const int ri = use ? rq[q] : 0;
-            const double w = use ? (weighted ? lut[ri + 255] : 1.0) : 0.0;
-            const double r = (double)ri;
+            const double2 wwr = lut[inside ? rq[q] : R_CODE_INVISIBLE];                    // {w, w r}
+            const double w = wwr.x, wr = wwr.y;
             const double zi = inside ? zz[q] : 0.0;
             const double xn = fma(ifx, u, kx), yn = fma(ify, v, ky);
             const double cc = fma(a, xn, b * yn);
@@ -555,9 +602,8 @@ __global__ void __launch_bounds__(GT, CTAS_PER_SM) gn_level_kernel(
                 acc[s] = fma(wj, J[j], acc[s]);
                 s++;
               }
-              acc[21 + i] = fma(wj, r, acc[21 + i]);
+              acc[21 + i] = fma(J[i], wr, acc[21 + i]);
             }
-            acc[27] = fma(w * r, r, acc[27]);
           }
         }
       }
@@ -586,6 +632,8 @@ __global__ void __launch_bounds__(GT, CTAS_PER_SM) gn_level_kernel(
         double v = 0.0;
 #pragma unroll
         for (int w = 0; w < GT / 32; w++) v += S.red[w * NE_TERMS + tid];
+        // chi2 came out of the histogram (every CTA holds the view's total): rank 0 contributes it
+        if (tid == NE_TERMS - 1) v = rank == 0 ? chi2View : 0.0;
         partial[(pb * K + k) * NE_TERMS + tid] = v;
       }
       __syncthreads();
