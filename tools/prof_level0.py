@@ -29,7 +29,8 @@ names = ["phaseA", "bar_hist", "scale", "phaseC", "blockred", "bar_sums", "solve
 for l in range(args.levels):
     pc = st["phase_clocks"][l]
     tot = sum(pc) or 1
-    print("level", l, "clocks/job-eval", {n: round(c / max(1, st["gn_iterations"]) , 1) for n, c in zip(names, pc)},
+    ev = st["pixel_iterations_level"][l] / (W * H / 4 ** l)   # job-evaluations at this level (single keyframe)
+    print("level", l, "evals", int(ev), "clocks/job-eval", {n: round(c / max(1, ev), 1) for n, c in zip(names, pc)},
           "share", {n: round(c / tot, 3) for n, c in zip(names, pc)})
 print({k: v for k, v in st.items() if k not in ("phase_clocks",)})
 ctx.close()

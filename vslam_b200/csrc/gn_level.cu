@@ -218,53 +218,23 @@ struct WarpConsts
   int Wt, Ht;
 };
 
-// Rare continuation of warp_fast(): the fp32 result is trustworthy (ok) but the rounded target lies on the
-// border ring or outside the image, or it is not trustworthy at all.
-__device__ __noinline__ int warp_slow(const ViewState & V, int u, int v, float d, float du, float dv, float eps, int iu,
-                                      int iv, bool ok)
-{
-  if (ok) {
-    // visibility is 1 < u' < W-1 and 1 < v' < H-1 with u' in (iu - 0.5, iu + 0.5): clearly outside, or on the
-    // ring iu == 1 / iu == W-1, where the displacement is compared with the exact integer offset of the boundary
-    const int Wt = V.Wt, Ht = V.Ht;
-    if (iu < 1 || iu > Wt - 1 || iv < 1 || iv > Ht - 1) return -1;
-    bool sure = true, vis = true;
-    if (iu == 1) {
-      const float l = du - (float)(1 - u);
-      sure = sure && fabsf(l) > eps;
-      vis = vis && l > 0.f;
-    }
-    if (iu == Wt - 1) {
-      const float r = (float)(Wt - 1 - u) - du;
-      sure = sure && fabsf(r) > eps;
-      vis = vis && r > 0.f;
-    }
-    if (iv == 1) {
-      const float l = dv - (float)(1 - v);
-      sure = sure && fabsf(l) > eps;
-      vis = vis && l > 0.f;
-    }
-    if (iv == Ht - 1) {
-      const float r = (float)(Ht - 1 - v) - dv;
-      sure = sure && fabsf(r) > eps;
-      vis = vis && r > 0.f;
-    }
-    if (sure) return vis ? iv * Wt + iu : -1;
-  }
-  return warp_exact(V, u, v, d);
-}
-
 // Sampled target pixel index of one interest point, or -1 when it is not visible.  The index and the
 // visibility flag are integer decisions and must be the fp64 oracle's.  A filtered evaluation gets them
 // without fp64 in the common case: in exact arithmetic u' = u + fx*(Dx - xn*Dz)/(z + Dz) with
-// D = (R - I) p + t, because p was back-projected from the integer pixel (u, v).  The displacement is
-// small, so fp32 carries it with an absolute error far below a pixel; only when it lands within the
-// error bound eps of a rounding boundary (u' = k + 0.5), or the rounded target is not strictly inside the
-// border ring, does warp_slow() take over (visibility boundaries u' = 1, W-1, v' = 1, H-1, or warp_exact()).
-__device__ __forceinline__ int warp_fast(const ViewState & V, const WarpConsts & c, uint32_t pk, float d)
+// D = (R - I) p + t, because p was back-projected from the integer pixel (u, v).  The displacement du is
+// small, so fp32 carries it with an absolute error far below a pixel.  With iu = u + rint(du) and the exact
+// fp32 remainder fu = du - rint(du) in [-0.5, 0.5], u' = iu + fu, so
+//   - the rounded target round(u') is iu unless |fu| is within eps of 0.5,
+//   - visibility 1 < u' < W-1 is decided by iu alone, except on the ring iu == 1 (visible iff fu > 0) and
+//     iu == W-1 (visible iff fu < 0), where it is safe unless |fu| <= eps.
+// warp_fast() is branch-free (the four points of a thread interleave) and reports `ok`; the few points within
+// eps of a boundary are redone by warp_exact().
+__device__ __forceinline__ int warp_fast(const WarpConsts & c, uint32_t pk, float d, bool & ok)
 {
   const int u = pk & 0xfff, v = (pk >> 12) & 0xfff;
-  const float xn = fmaf((float)u, c.ifx, c.kx), yn = fmaf((float)v, c.ify, c.ky);
+  // int -> float without the conversion unit (it is the scarce pipe of this kernel): 2^23 + n is exact
+  const float uf = __int_as_float(0x4B000000 | u) - 8388608.f, vf = __int_as_float(0x4B000000 | v) - 8388608.f;
+  const float xn = fmaf(uf, c.ifx, c.kx), yn = fmaf(vf, c.ify, c.ky);
   const float px = xn * d, py = yn * d;
   const float Dx = fmaf(c.r02, d, fmaf(c.r01, py, fmaf(c.r00, px, c.t0)));
   const float Dy = fmaf(c.r12, d, fmaf(c.r11, py, fmaf(c.r10, px, c.t1)));
@@ -277,15 +247,20 @@ __device__ __forceinline__ int warp_fast(const ViewState & V, const WarpConsts &
   // nearest integer of the displacement through the 1.5 * 2^23 trick (|du| < 4096 is checked below)
   const float MAGIC = 12582912.f;
   const float mu = du + MAGIC, mv = dv + MAGIC;
-  const float fu = du - (mu - MAGIC), fv = dv - (mv - MAGIC);  // in [-0.5, 0.5]
+  const float fu = du - (mu - MAGIC), fv = dv - (mv - MAGIC);
   const int iu = u + (__float_as_int(mu) - 0x4B400000), iv = v + (__float_as_int(mv) - 0x4B400000);
-  const float dist = 0.5f - fmaxf(fabsf(fu), fabsf(fv));       // distance to the nearest rounding boundary
+  const float au = fabsf(fu), av = fabsf(fv);
+  const bool ringu = iu == 1 || iu == c.Wt - 1, ringv = iv == 1 || iv == c.Ht - 1;
+  float dist = 0.5f - fmaxf(au, av);  // distance to the nearest rounding boundary ...
+  dist = ringu ? fminf(dist, au) : dist;  // ... and, on the ring, to the visibility boundary
+  dist = ringv ? fminf(dist, av) : dist;
   const float s = fabsf(du) + fabsf(dv);
   const float eps = fmaf(fmaf(c.epsA, d, c.epsB), fabsf(iz), fmaf(3.8e-6f, s, 6.1e-5f));
-  const bool ok = qz > 0.25f * d && dist > eps && s < 4096.f;
-  const bool inside = (unsigned)(iu - 2) <= (unsigned)(c.Wt - 4) && (unsigned)(iv - 2) <= (unsigned)(c.Ht - 4);
-  if (ok && inside) return iv * c.Wt + iu;
-  return warp_slow(V, u, v, d, du, dv, eps, iu, iv, ok);
+  ok = qz > 0.25f * d && dist > eps && s < 4096.f;
+  bool vis = (unsigned)(iu - 1) <= (unsigned)(c.Wt - 2) && (unsigned)(iv - 1) <= (unsigned)(c.Ht - 2);
+  vis = vis && !(iu == 1 && fu < 0.f) && !(iu == c.Wt - 1 && fu > 0.f);
+  vis = vis && !(iv == 1 && fv < 0.f) && !(iv == c.Ht - 1 && fv > 0.f);
+  return vis ? iv * c.Wt + iu : -1;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -323,6 +298,22 @@ __device__ __forceinline__ void mbar_wait(uint64_t * bar, uint32_t parity)
       : "r"(a), "r"(parity)
       : "memory");
   } while (!done);
+}
+// L2 policy for data that is streamed once per phase (the static interest lists): evict first, so that the lines
+// which are re-used within an iteration (the gathered target image, the residual codes) stay in L2
+__device__ __forceinline__ uint64_t l2_evict_first_policy()
+{
+  uint64_t pol;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+  return pol;
+}
+__device__ __forceinline__ void bulk_g2s_stream(void * dst, const void * src, uint32_t bytes, uint64_t * bar, uint64_t pol)
+{
+  asm volatile(
+    "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;" ::"r"(
+      smem_u32(dst)),
+    "l"(src), "r"(bytes), "r"(smem_u32(bar)), "l"(pol)
+    : "memory");
 }
 // global -> own shared memory, completion counted in bytes on an mbarrier of this CTA
 __device__ __forceinline__ void bulk_g2s(void * dst, const void * src, uint32_t bytes, uint64_t * bar)
@@ -375,14 +366,15 @@ __device__ __forceinline__ void issue_chunk(
   const int cnt = (min(CH, p1 - start) + 7) & ~7;
   unsigned char * st = ring + (size_t)(item % NS) * STAGE_BYTES;
   uint64_t * bar = &S.full[item % NS];
+  const uint64_t pol = l2_evict_first_policy();
   mbar_expect_tx(bar, (uint32_t)cnt * (phaseC ? 18u : 8u));
-  bulk_g2s(st + OFF_UVT, V.uvt + start, cnt * 4, bar);
+  bulk_g2s_stream(st + OFF_UVT, V.uvt + start, cnt * 4, bar, pol);
   if (phaseC) {
-    bulk_g2s(st + OFF_DG, V.g + start, cnt * 4, bar);
-    bulk_g2s(st + OFF_ZI, V.zi + start, cnt * 8, bar);
+    bulk_g2s_stream(st + OFF_DG, V.g + start, cnt * 4, bar, pol);
+    bulk_g2s_stream(st + OFF_ZI, V.zi + start, cnt * 8, bar, pol);
     bulk_g2s(st + OFF_R, V.r + start, cnt * 2, bar);
   } else {
-    bulk_g2s(st + OFF_DG, V.d + start, cnt * 4, bar);
+    bulk_g2s_stream(st + OFF_DG, V.d + start, cnt * 4, bar, pol);
   }
 }
 
@@ -477,12 +469,19 @@ __global__ void __launch_bounds__(GT, CTAS_PER_SM) gn_level_kernel(
           const uint32_t pk[4] = {pk4.x, pk4.y, pk4.z, pk4.w};
           const float dd[4] = {dd4.x, dd4.y, dd4.z, dd4.w};
           P.g = p0 + ch * CH + 4 * tid;
+          bool good[4];
 #pragma unroll
           for (int q = 0; q < 4; q++) {
             P.T[q] = pk[q] >> 24;
-            const int px = warp_fast(V, c, pk[q], dd[q]);  // padding lanes compute on stale ring data: harmless
-            P.pix[q] = P.g + q < p1 ? px : -1;
+            P.pix[q] = warp_fast(c, pk[q], dd[q], good[q]);  // padding lanes compute on stale ring data: harmless
           }
+          if (!(good[0] && good[1] && good[2] && good[3])) {
+#pragma unroll
+            for (int q = 0; q < 4; q++)
+              if (!good[q]) P.pix[q] = warp_exact(V, pk[q] & 0xfff, (pk[q] >> 12) & 0xfff, dd[q]);
+          }
+#pragma unroll
+          for (int q = 0; q < 4; q++) P.pix[q] = P.g + q < p1 ? P.pix[q] : -1;
 #pragma unroll
           for (int q = 0; q < 4; q++) P.val[q] = P.pix[q] >= 0 ? (int)__ldg(I + P.pix[q]) : 0;
         };
@@ -578,9 +577,13 @@ __global__ void __launch_bounds__(GT, CTAS_PER_SM) gn_level_kernel(
             // WarpSE3::J rows (Warp.cpp:184-199) contracted with the template gradient
             // (InverseCompositional.cpp:79-80), in normalised coordinates xn = x/z, yn = y/z
             const bool inside = g + q < p1;
-            const double u = (double)(int)(pk[q] & 0xfff), v = (double)(int)((pk[q] >> 12) & 0xfff);
-            const double a = inside ? (double)(int)(int16_t)(gg[q] & 0xffff) * fxJ : 0.0;  // dIx * fx
-            const double b = inside ? (double)(int)(int16_t)(gg[q] >> 16) * fyJ : 0.0;     // dIy * fy
+            // int -> double on the fp64 pipe (2^52 + n is exact) instead of the conversion unit
+            const double u = __hiloint2double(0x43300000, (int)(pk[q] & 0xfff)) - 4503599627370496.0;
+            const double v = __hiloint2double(0x43300000, (int)((pk[q] >> 12) & 0xfff)) - 4503599627370496.0;
+            const double gxd = __hiloint2double(0x43300000, (int)((gg[q] & 0xffff) ^ 0x8000)) - 4503599627403264.0;
+            const double gyd = __hiloint2double(0x43300000, (int)((gg[q] >> 16) ^ 0x8000)) - 4503599627403264.0;
+            const double a = inside ? gxd * fxJ : 0.0;  // dIx * fx
+            const double b = inside ? gyd * fyJ : 0.0;  // dIy * fy
             const double2 wwr = lut[inside ? rq[q] : R_CODE_INVISIBLE];                    // {w, w r}
             const double w = wwr.x, wr = wwr.y;
             const double zi = inside ? zz[q] : 0.0;
