@@ -94,8 +94,9 @@ typedef struct vslamb200_stats
   double ms_lists, ms_preprocess, ms_gn_level[VSLAMB200_MAX_LEVELS];
   uint64_t pixel_iterations_level[VSLAMB200_MAX_LEVELS];  /* pixel_iterations split by pyramid level */
   /* SM clocks of the jobs' leading CTA per level, summed over jobs: phase A, histogram barrier, scale + weights,
-     phase C, block reduction, sums barrier, solve */
-  uint64_t phase_clocks[VSLAMB200_MAX_LEVELS][7];
+     phase C, block reduction, sums barrier, solve, then the scale section split: histogram gather + scaler, publish +
+     second cluster barrier, weight table */
+  uint64_t phase_clocks[VSLAMB200_MAX_LEVELS][10];
 } vslamb200_stats;
 
 const char * vslamb200_last_error(void);

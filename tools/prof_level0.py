@@ -25,7 +25,7 @@ for _ in range(2):
     res = ctx.align(jobs)
 st = ctx.stats()
 print("iters", res[0]["iters"][:args.levels])
-names = ["phaseA", "bar_hist", "scale", "phaseC", "blockred", "bar_sums", "solve"]
+names = ["phaseA", "bar_hist", "scale", "phaseC", "blockred", "bar_sums", "solve", "sc_scaler", "sc_publish_bar", "sc_table"]
 for l in range(args.levels):
     pc = st["phase_clocks"][l]
     tot = sum(pc) or 1

@@ -657,7 +657,7 @@ int vslamb200_align(vslamb200_ctx * c, const vslamb200_job * jobs, int nJobs, vs
         const uint64_t px = (uint64_t)J.evals[l] * J.nViews * P.geo.W[l] * P.geo.H[l];
         c->stats.pixel_iterations += px;
         c->stats.pixel_iterations_level[l] += px;
-        for (int k = 0; k < 7; k++) c->stats.phase_clocks[l][k] += (uint64_t)J.clk[l][k];
+        for (int k = 0; k < 10; k++) c->stats.phase_clocks[l][k] += (uint64_t)J.clk[l][k];
         c->stats.gn_iterations += J.evals[l];
       }
     }

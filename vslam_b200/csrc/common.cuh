@@ -97,7 +97,7 @@ struct JobState
   unsigned long long pointIters;  // sum over evaluations of the interest points visited
   // SM clocks spent by the cluster's rank-0 CTA per level: phase A, histogram barrier, scale + weights, phase C,
   // block reduction, sums barrier, solve
-  long long clk[MAX_LEVELS][7];
+  long long clk[MAX_LEVELS][10];
 };
 
 struct SolverParams

@@ -67,25 +67,42 @@ __device__ __forceinline__ double loss_weight(const SolverParams & p, double r)
   }
 }
 
+// 1 / d for a positive, normal d: 20-bit seed refined by two Newton steps (relative error ~1e-16).  The scaler's
+// recurrence is a chain of dependent fp64 operations on one warp; the correctly rounded division's ~25
+// instruction sequence per term is what its latency is made of.
+__device__ __forceinline__ double rcp_newton(double d)
+{
+  double y;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(d));
+  double e = fma(-d, y, 1.0);
+  y = fma(y, e, y);
+  e = fma(-d, y, 1.0);
+  y = fma(y, e, y);
+  e = fma(-d, y, 1.0);
+  return fma(y, e, y);
+}
+
+// bin b holds the residual value b - 255 (bin 511 is unused).  Thread t owns bins (t + j*GT + 192) mod 512:
+// j = 0 covers the central residuals -63..64, where nearly all the mass is, so the other j are skipped warp-wide
+__device__ __forceinline__ int bin_of(int j) { return ((int)threadIdx.x + j * GT + 192) & (HIST_BINS - 1); }
+
 // Scale / offset from the residual histogram (h[b] = #visible points with r = b-255; invisible points
-// count as r = 0, InverseCompositional.cpp:111,130) and the weight table.  Whole block.
-// Also returns chi2 = sum_k w_k r_k^2 (NormalEquations.cpp:58), which is a function of the histogram too.
-__device__ double scale_and_weights(
-  ViewState & V, const SolverParams & p, int * h /* smem 512 */, double2 * lut /* smem 512: {w, w r} */, double * red)
+// count as r = 0, InverseCompositional.cpp:111,130).  Whole block (the leading CTA of the cluster runs it).
+// nvis: this thread's bins before the zeros of the invisible points are added (for chi2).
+__device__ void compute_scale(
+  ViewState & V, const SolverParams & p, int * h /* smem 512 */, double * red, double (&nvis)[BPT], double & scaleOut,
+  double & offsetOut)
 {
   const int tid = threadIdx.x;
   __shared__ double s_scale, s_offset;
-  // bin b holds the residual value b - 255 (bin 511 is unused).  Thread t owns bins (t + j*GT + 192) mod 512:
-  // j = 0 covers the central residuals -63..64, where nearly all the mass is, so the other j are skipped warp-wide
   int bin[BPT];
 #pragma unroll
-  for (int j = 0; j < BPT; j++) bin[j] = (tid + j * GT + 192) & (HIST_BINS - 1);
+  for (int j = 0; j < BPT; j++) bin[j] = bin_of(j);
   int c0 = 0;
 #pragma unroll
   for (int j = 0; j < BPT; j++) c0 += h[bin[j]];
   const double vis = block_sum((double)c0, red);
   const long n = V.nIp;
-  double nvis[BPT];  // visible points per bin (before the zeros of the invisible points join bin 255)
 #pragma unroll
   for (int j = 0; j < BPT; j++) nvis[j] = (double)h[bin[j]];
   __syncthreads();
@@ -100,36 +117,51 @@ __device__ double scale_and_weights(
   }
   if (p.scalerKind == VSLAMB200_SCALER_TDIST) {
     // sigma^2 <- mean(r^2 (nu+1) / (nu + (r/sigma)^2)), from sigma = 1, <= 30 steps, until |step| <= 1e-5
-    // r^2 (nu+1) / (nu + r^2/sigma^2) == r^2 (nu+1) sigma^2 / (nu sigma^2 + r^2): one division per populated bin
-    double av[BPT], r2[BPT];
-#pragma unroll
-    for (int j = 0; j < BPT; j++) {
-      r2[j] = rv[j] * rv[j];
-      av[j] = nv[j] * (r2[j] * (p.scalerV + 1));
-    }
-    double step = 1.79769313486231570e308, sigma = 1.0;
+    // (Scaler.cpp:49-67).  The steps are strictly sequential, so one warp runs them without block barriers:
+    // lane l owns the residual values whose offset from 0 is l + 32 m (both signs folded: the summand is even
+    // in r), slot m = 0..7; slots nobody populates are skipped warp-wide.
+    // r^2 (nu+1) / (nu + r^2/sigma^2) == r^2 (nu+1) sigma^2 / (nu sigma^2 + r^2): one division per slot.
     __syncthreads();
-    for (int it = 0; it < 30 && step > 1e-5; it++) {
-      double term = 0.0;
-      const double s2 = sigma * sigma, vs2 = p.scalerV * s2;
+    if (tid < 32) {
+      double av[8], r2[8];
+      unsigned populated = 0;
 #pragma unroll
-      for (int j = 0; j < BPT; j++)
-        if (nv[j] > 0) term += (av[j] * s2) / (vs2 + r2[j]);
-      // one barrier per step: warp partials alternate between two shared buffers
+      for (int m = 0; m < 8; m++) {
+        const int r = tid + 32 * m;  // 0..255
+        const int cnt = r == 0 ? h[255] : h[255 + r] + h[255 - r];
+        r2[m] = (double)(r * r);
+        av[m] = (double)cnt * (r2[m] * (p.scalerV + 1));
+        if (__any_sync(0xffffffffu, cnt > 0 && r > 0)) populated |= 1u << m;
+      }
+      // The recurrence is carried in x = sigma^2 (x' = mean(a x / (nu x + r^2))); sigma' = sqrt(x') only feeds the
+      // stopping test, so it is evaluated next to the following step's terms and the loop runs one step ahead
+      // (the look-ahead step is discarded on exit).
+      const double invn = 1.0 / (double)n;
+      auto next_x = [&](double x) {
+        const double vs2 = p.scalerV * x;
+        double t0 = 0.0, t1 = 0.0;
 #pragma unroll
-      for (int o = 16; o > 0; o >>= 1) term += __shfl_xor_sync(0xffffffffu, term, o);
-      double * buf = red + (it & 1) * (GT / 32);
-      if ((tid & 31) == 0) buf[tid >> 5] = term;
-      __syncthreads();
-      double sum = 0.0;
+        for (int m = 0; m < 8; m += 2) {
+          if (populated & (1u << m)) t0 = fma(av[m] * x, rcp_newton(vs2 + r2[m]), t0);
+          if (populated & (2u << m)) t1 = fma(av[m + 1] * x, rcp_newton(vs2 + r2[m + 1]), t1);
+        }
+        double term = t0 + t1;
 #pragma unroll
-      for (int w = 0; w < GT / 32; w++) sum += buf[w];
-      const double s = sqrt(sum / (double)n);
-      step = fabs(sigma - s);
-      sigma = s;
+        for (int o = 16; o > 0; o >>= 1) term += __shfl_xor_sync(0xffffffffu, term, o);
+        return term * invn;
+      };
+      double sigma = 1.0;
+      double x1 = next_x(1.0);  // sigma_1^2
+      for (int it = 0; it < 30; it++) {
+        const double x2 = next_x(x1);        // look-ahead: sigma_{it+2}^2
+        const double sg = sqrt(x1);          // sigma_{it+1}
+        const double step = fabs(sigma - sg);
+        sigma = sg;
+        x1 = x2;
+        if (!(step > 1e-5)) break;
+      }
+      scale = sigma;
     }
-    __syncthreads();
-    scale = sigma;
   } else if (p.scalerKind == VSLAMB200_SCALER_MEAN || p.scalerKind == VSLAMB200_SCALER_MEDIAN) {
     if (n > 0) {
       if (p.scalerKind == VSLAMB200_SCALER_MEAN) {
@@ -177,20 +209,31 @@ __device__ double scale_and_weights(
   }
   if (tid == 0) {
     s_scale = scale;
+    s_offset = offset;
     V.scale = scale;
     V.offset = offset;
   }
   __syncthreads();
-  scale = s_scale;
+  scaleOut = s_scale;
+  offsetOut = s_offset;
+}
+
+// Weight table {w(r), w(r) r} per residual code (Loss.cpp:51-92); code 511 (not visible) -> {0, 0}.
+// Returns this thread's share of chi2 = sum_k w_k r_k^2 (NormalEquations.cpp:58) given its visible counts.
+__device__ __forceinline__ double build_weights(
+  const SolverParams & p, double scale, double offset, double2 * lut, const double (&nvis)[BPT])
+{
   double c2 = 0.0;
 #pragma unroll
   for (int j = 0; j < BPT; j++) {
-    const double w = p.lossKind == VSLAMB200_LOSS_NONE ? 1.0 : loss_weight(p, (rv[j] - offset) / scale);
-    const double wr = w * rv[j];
-    lut[bin[j]] = bin[j] == HIST_BINS - 1 ? make_double2(0.0, 0.0) : make_double2(w, wr);  // 511: not visible
-    c2 = fma(nvis[j], wr * rv[j], c2);
+    const int b = bin_of(j);
+    const double r = (double)(b - 255);
+    const double w = p.lossKind == VSLAMB200_LOSS_NONE ? 1.0 : loss_weight(p, (r - offset) / scale);
+    const double wr = w * r;
+    lut[b] = b == HIST_BINS - 1 ? make_double2(0.0, 0.0) : make_double2(w, wr);
+    c2 = fma(nvis[j], wr * r, c2);
   }
-  return block_sum(c2, red);
+  return c2;
 }
 
 // Exact warp of one interest point, operation for operation the oracle's (fp64, explicit fma):
@@ -293,9 +336,9 @@ __device__ __forceinline__ void mbar_wait(uint64_t * bar, uint32_t parity)
   uint32_t done;
   do {
     asm volatile(
-      "{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+      "{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\tselp.u32 %0, 1, 0, p;\n\t}"
       : "=r"(done)
-      : "r"(a), "r"(parity)
+      : "r"(a), "r"(parity), "r"(0x989680u)  // suspend-time hint: sleep in hardware instead of re-polling
       : "memory");
   } while (!done);
 }
@@ -331,6 +374,7 @@ struct LevelShared
   double2 lut[HIST_BINS];  // {w(r), w(r) r} per residual code; code 511 (not visible) -> {0, 0}
   double red[GT / 32 * NE_TERMS];
   SolveScratch X;
+  double so[2];  // {scale, offset} of the current view, written by the cluster's leading CTA
   alignas(8) uint64_t full[NS];   // TMA bytes of the stage have landed
   alignas(8) uint64_t empty[NS];  // every warp has copied the stage into registers
 };
@@ -423,6 +467,14 @@ __global__ void __launch_bounds__(GT, CTAS_PER_SM) gn_level_kernel(
       const long long now = clock64();
       S.J.clk[level][slot] += now - tc;
       tc = now;
+    }
+  };
+  long long ts = 0;  // sub-laps of the scale section (do not reset the main lap clock)
+  auto sublap = [&](int slot) {
+    if (tid == 0) {
+      const long long now = clock64();
+      S.J.clk[level][slot] += now - ts;
+      ts = now;
     }
   };
   for (;;) {
@@ -520,25 +572,46 @@ __global__ void __launch_bounds__(GT, CTAS_PER_SM) gn_level_kernel(
         for (int c = 0; c < min(NS, nCh); c++) issue_chunk(S, ring, V, true, p0, p1, c, item + c);
       lap(0);
       // ---------------------------------------------------------------- scale + weight table
-      double chi2View;
+      // The leading CTA sums the cluster's histograms, runs the scaler and publishes {scale, offset} into every
+      // CTA's shared memory; the others only wait (they would repeat the same arithmetic, and the kernel is bound
+      // by instruction issue).  Every CTA then builds its own weight table.
+      double chi2View = 0.0;
       {
         cluster.sync();
         lap(1);
-        int a[BPT];
+        if (tid == 0) ts = clock64();
+        double nvis[BPT];
 #pragma unroll
-        for (int j = 0; j < BPT; j++) a[j] = 0;
-        for (unsigned rk = 0; rk < C; rk++) {
-          const int * h = cluster.map_shared_rank(hist, rk);
+        for (int j = 0; j < BPT; j++) nvis[j] = 0.0;
+        if (rank == 0) {
+          int a[BPT];
 #pragma unroll
-          for (int j = 0; j < BPT; j++) a[j] += h[tid + j * GT];
+          for (int j = 0; j < BPT; j++) a[j] = 0;
+          for (unsigned rk = 0; rk < C; rk++) {
+            const int * h = cluster.map_shared_rank(hist, rk);
+#pragma unroll
+            for (int j = 0; j < BPT; j++) a[j] += h[tid + j * GT];
+          }
+          // the other histogram buffer is idle (its last remote readers passed a cluster barrier since)
+          int * tot = S.hist[hb ^ 1];
+#pragma unroll
+          for (int j = 0; j < BPT; j++) tot[tid + j * GT] = a[j];
+          __syncthreads();
+          double sc, of;
+          compute_scale(V, p, tot, S.red, nvis, sc, of);
+          if (tid < (int)C) {
+            double * dst = cluster.map_shared_rank(S.so, tid);
+            dst[0] = sc;
+            dst[1] = of;
+          }
         }
-        // the other histogram buffer is idle (its last remote readers passed a cluster barrier since): totals go there
-        int * tot = S.hist[hb ^ 1];
-#pragma unroll
-        for (int j = 0; j < BPT; j++) tot[tid + j * GT] = a[j];
-        __syncthreads();
-        chi2View = scale_and_weights(V, p, tot, S.lut, S.red);
-        __syncthreads();
+        sublap(7);
+        cluster.sync();
+        sublap(8);
+        const double c2 = build_weights(p, S.so[0], S.so[1], S.lut, nvis);
+        if (rank == 0) chi2View = block_sum(c2, S.red);  // contains the barrier that publishes the table
+        else __syncthreads();
+        sublap(9);
         hb ^= 1;
         lap(2);
       }

@@ -60,7 +60,7 @@ __global__ void level_setup_kernel(
     J.active = J.dead ? 0 : 1;
     for (int k = 0; k < 6; k++) J.xPrev[k] = 0.0;
     J.evals[level] = 0;
-    for (int k = 0; k < 7; k++) J.clk[level][k] = 0;
+    for (int k = 0; k < 10; k++) J.clk[level][k] = 0;
   }
 }
 
