@@ -2,6 +2,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <unordered_map>
@@ -553,6 +554,10 @@ int build_problem(vslamb200_ctx * c, const vslamb200_job * jobs, int nJobs, Prob
 int pick_cluster(int npx, int maxViewsPerJob)
 {
   (void)maxViewsPerJob;
+  if (const char * e = std::getenv("VSLAMB200_CLUSTER")) {  // tuning override
+    const int c = std::atoi(e);
+    if (c == 1 || c == 2 || c == 4 || c == 8) return c;
+  }
   if (npx > 160000) return 8;
   if (npx > 40000) return 4;
   if (npx > 12000) return 2;

@@ -270,14 +270,22 @@ struct WarpConsts
 //   - the rounded target round(u') is iu unless |fu| is within eps of 0.5,
 //   - visibility 1 < u' < W-1 is decided by iu alone, except on the ring iu == 1 (visible iff fu > 0) and
 //     iu == W-1 (visible iff fu < 0), where it is safe unless |fu| <= eps.
-// warp_fast() is branch-free (the four points of a thread interleave) and reports `ok`; the few points within
-// eps of a boundary are redone by warp_exact().
-__device__ __forceinline__ int warp_fast(const WarpConsts & c, uint32_t pk, float d, bool & ok)
+// warp_eval() is branch-free (the four points of a thread interleave).  When every rounded target of the warp lies
+// strictly inside the ring (the common case, decided by two unsigned compares per point) warp_pick_interior()
+// finishes with the rounding distance alone; otherwise warp_pick_ring() adds the visibility logic.  Both report
+// `ok`; the few points within eps of a boundary are redone by warp_exact().
+struct WarpEval
 {
+  float fu, fv, eps;
+  int iu, iv;
+  bool okb;       // depth / magnitude guards of the fp32 evaluation
+  bool interior;  // 2 <= iu <= W-2 and 2 <= iv <= H-2
+};
+__device__ __forceinline__ WarpEval warp_eval(const WarpConsts & c, uint32_t pk, float d)
+{
+  WarpEval e;
   const int u = pk & 0xfff, v = (pk >> 12) & 0xfff;
-  // int -> float without the conversion unit (it is the scarce pipe of this kernel): 2^23 + n is exact
-  const float uf = __int_as_float(0x4B000000 | u) - 8388608.f, vf = __int_as_float(0x4B000000 | v) - 8388608.f;
-  const float xn = fmaf(uf, c.ifx, c.kx), yn = fmaf(vf, c.ify, c.ky);
+  const float xn = fmaf((float)u, c.ifx, c.kx), yn = fmaf((float)v, c.ify, c.ky);
   const float px = xn * d, py = yn * d;
   const float Dx = fmaf(c.r02, d, fmaf(c.r01, py, fmaf(c.r00, px, c.t0)));
   const float Dy = fmaf(c.r12, d, fmaf(c.r11, py, fmaf(c.r10, px, c.t1)));
@@ -287,22 +295,36 @@ __device__ __forceinline__ int warp_fast(const WarpConsts & c, uint32_t pk, floa
   asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(iz) : "f"(qz));  // 1 ulp; covered by the 2^-18 (|du|+|dv|) term of eps
   const float du = (c.fx * iz) * fmaf(-xn, Dz, Dx);
   const float dv = (c.fy * iz) * fmaf(-yn, Dz, Dy);
-  // nearest integer of the displacement through the 1.5 * 2^23 trick (|du| < 4096 is checked below)
+  // nearest integer of the displacement through the 1.5 * 2^23 trick (|du| < 4096 is part of okb)
   const float MAGIC = 12582912.f;
   const float mu = du + MAGIC, mv = dv + MAGIC;
-  const float fu = du - (mu - MAGIC), fv = dv - (mv - MAGIC);
-  const int iu = u + (__float_as_int(mu) - 0x4B400000), iv = v + (__float_as_int(mv) - 0x4B400000);
-  const float au = fabsf(fu), av = fabsf(fv);
-  const bool ringu = iu == 1 || iu == c.Wt - 1, ringv = iv == 1 || iv == c.Ht - 1;
-  float dist = 0.5f - fmaxf(au, av);  // distance to the nearest rounding boundary ...
-  dist = ringu ? fminf(dist, au) : dist;  // ... and, on the ring, to the visibility boundary
-  dist = ringv ? fminf(dist, av) : dist;
+  e.fu = du - (mu - MAGIC);
+  e.fv = dv - (mv - MAGIC);
+  e.iu = u + (__float_as_int(mu) - 0x4B400000);
+  e.iv = v + (__float_as_int(mv) - 0x4B400000);
   const float s = fabsf(du) + fabsf(dv);
-  const float eps = fmaf(fmaf(c.epsA, d, c.epsB), fabsf(iz), fmaf(3.8e-6f, s, 6.1e-5f));
-  ok = qz > 0.25f * d && dist > eps && s < 4096.f;
+  e.eps = fmaf(fmaf(c.epsA, d, c.epsB), fabsf(iz), fmaf(3.8e-6f, s, 6.1e-5f));
+  e.okb = qz > 0.25f * d && s < 4096.f;
+  e.interior = (unsigned)(e.iu - 2) <= (unsigned)(c.Wt - 4) && (unsigned)(e.iv - 2) <= (unsigned)(c.Ht - 4);
+  return e;
+}
+__device__ __forceinline__ int warp_pick_interior(const WarpConsts & c, const WarpEval & e, bool & ok)
+{
+  ok = e.okb && 0.5f - fmaxf(fabsf(e.fu), fabsf(e.fv)) > e.eps;  // distance to the nearest rounding boundary
+  return e.iv * c.Wt + e.iu;
+}
+__device__ __forceinline__ int warp_pick_ring(const WarpConsts & c, const WarpEval & e, bool & ok)
+{
+  const int iu = e.iu, iv = e.iv;
+  const float au = fabsf(e.fu), av = fabsf(e.fv);
+  const bool ringu = iu == 1 || iu == c.Wt - 1, ringv = iv == 1 || iv == c.Ht - 1;
+  float dist = 0.5f - fmaxf(au, av);
+  dist = ringu ? fminf(dist, au) : dist;  // on the ring: distance to the visibility boundary as well
+  dist = ringv ? fminf(dist, av) : dist;
+  ok = e.okb && dist > e.eps;
   bool vis = (unsigned)(iu - 1) <= (unsigned)(c.Wt - 2) && (unsigned)(iv - 1) <= (unsigned)(c.Ht - 2);
-  vis = vis && !(iu == 1 && fu < 0.f) && !(iu == c.Wt - 1 && fu > 0.f);
-  vis = vis && !(iv == 1 && fv < 0.f) && !(iv == c.Ht - 1 && fv > 0.f);
+  vis = vis && !(iu == 1 && e.fu < 0.f) && !(iu == c.Wt - 1 && e.fu > 0.f);
+  vis = vis && !(iv == 1 && e.fv < 0.f) && !(iv == c.Ht - 1 && e.fv > 0.f);
   return vis ? iv * c.Wt + iu : -1;
 }
 
@@ -522,10 +544,18 @@ __global__ void __launch_bounds__(GT, CTAS_PER_SM) gn_level_kernel(
           const float dd[4] = {dd4.x, dd4.y, dd4.z, dd4.w};
           P.g = p0 + ch * CH + 4 * tid;
           bool good[4];
+          WarpEval ev[4];
 #pragma unroll
           for (int q = 0; q < 4; q++) {
             P.T[q] = pk[q] >> 24;
-            P.pix[q] = warp_fast(c, pk[q], dd[q], good[q]);  // padding lanes compute on stale ring data: harmless
+            ev[q] = warp_eval(c, pk[q], dd[q]);  // padding lanes compute on stale ring data: harmless
+          }
+          if (__all_sync(0xffffffffu, ev[0].interior && ev[1].interior && ev[2].interior && ev[3].interior)) {
+#pragma unroll
+            for (int q = 0; q < 4; q++) P.pix[q] = warp_pick_interior(c, ev[q], good[q]);
+          } else {
+#pragma unroll
+            for (int q = 0; q < 4; q++) P.pix[q] = warp_pick_ring(c, ev[q], good[q]);
           }
           if (!(good[0] && good[1] && good[2] && good[3])) {
 #pragma unroll
@@ -650,13 +680,9 @@ __global__ void __launch_bounds__(GT, CTAS_PER_SM) gn_level_kernel(
             // WarpSE3::J rows (Warp.cpp:184-199) contracted with the template gradient
             // (InverseCompositional.cpp:79-80), in normalised coordinates xn = x/z, yn = y/z
             const bool inside = g + q < p1;
-            // int -> double on the fp64 pipe (2^52 + n is exact) instead of the conversion unit
-            const double u = __hiloint2double(0x43300000, (int)(pk[q] & 0xfff)) - 4503599627370496.0;
-            const double v = __hiloint2double(0x43300000, (int)((pk[q] >> 12) & 0xfff)) - 4503599627370496.0;
-            const double gxd = __hiloint2double(0x43300000, (int)((gg[q] & 0xffff) ^ 0x8000)) - 4503599627403264.0;
-            const double gyd = __hiloint2double(0x43300000, (int)((gg[q] >> 16) ^ 0x8000)) - 4503599627403264.0;
-            const double a = inside ? gxd * fxJ : 0.0;  // dIx * fx
-            const double b = inside ? gyd * fyJ : 0.0;  // dIy * fy
+            const double u = (double)(int)(pk[q] & 0xfff), v = (double)(int)((pk[q] >> 12) & 0xfff);
+            const double a = inside ? (double)(int)(int16_t)(gg[q] & 0xffff) * fxJ : 0.0;  // dIx * fx
+            const double b = inside ? (double)(int)(int16_t)(gg[q] >> 16) * fyJ : 0.0;     // dIy * fy
             const double2 wwr = lut[inside ? rq[q] : R_CODE_INVISIBLE];                    // {w, w r}
             const double w = wwr.x, wr = wwr.y;
             const double zi = inside ? zz[q] : 0.0;
