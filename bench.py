@@ -30,6 +30,17 @@ W, H, LEVELS = 640, 480, 4
 ALGO_BYTES_PER_PIXEL_ITER = 10  # T u8 + dIx s16 + dIy s16 + depth f32 + gathered I u8
 
 
+def load_traffic(frames):
+    """dram__bytes_read.sum + dram__bytes_write.sum of the level-0 launch from the committed ncu --set full capture
+    (profiles/traffic.json); only valid for the batch size it was captured on."""
+    p = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(p):
+        t = json.load(open(p))
+        if t.get("frames") == frames:
+            return t.get("dram_bytes_per_launch")
+    return None
+
+
 def load_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -128,7 +139,7 @@ def run_reference(args, rank, world):
         return
     from vslam_b200 import synth
     threads = os.cpu_count() or 1
-    n_pairs = max(threads, 8)
+    n_pairs = max(4 * threads, 16)
     cam = synth.cam_for(W, H)
     gray, depth, _ = synth.make_sequence(n_pairs + 1, W, H, seed=1234, cam=cam)
     for _ in range(args.warmup):
@@ -157,7 +168,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--frames", type=int, default=1000)
     ap.add_argument("--impl", default="ours")
-    ap.add_argument("--cpu-pairs", type=int, default=8, help="pairs timed on the host cores for cpu_baseline")
+    ap.add_argument("--cpu-pairs", type=int, default=32, help="pairs timed on the host cores for cpu_baseline")
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()
     rank, world, local = dist_env()
@@ -252,7 +263,7 @@ def main():
     roofline = {
         "bound": "hbm", "kernel": "gn_level_kernel (level 0: all Gauss-Newton iterations of 640x480 for the batch)",
         "achieved": achieved, "peak": peak, "peak_kind": peak_kind, "unit": "GB/s", "frac": achieved / peak,
-        "traffic": None,
+        "traffic": load_traffic(F),
         "algorithmic_bytes_per_launch": l0_bytes, "ms_per_launch": l0_ms,
         "all_levels": {"ms": tst["ms_gn_level"][:LEVELS], "pixel_iterations": tst["pixel_iterations_level"][:LEVELS],
                        "achieved": ALGO_BYTES_PER_PIXEL_ITER * tst["pixel_iterations"] / (all_ms * 1e-3) / 1e9 if all_ms > 0 else 0.0},
@@ -284,7 +295,7 @@ def main():
         print(json.dumps({
             "metric": "aligned frame pairs/sec at 640x480 RGB-D", "value": value, "unit": "pairs/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64/f32 (u8 images)",
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
             "data": "synthetic",
             "config": {"workload": f"synthetic TUM-shape 640x480 sequence of {F} frames per GPU, frame-to-frame "
                                    f"alignment ({F - 1} pairs per batch), t-distribution weights, {LEVELS} levels, "

@@ -60,6 +60,7 @@ struct Arena
   void * ptr = nullptr;
   size_t bytes = 0;
   int refs = 0;
+  bool spare = false;  // no live frames; kept for the next upload of the same size (no cudaMalloc/cudaFree per batch)
 };
 
 struct FrameHost
@@ -134,13 +135,23 @@ int release_slot(vslamb200_ctx * c, int slot)
   c->idToSlot.erase(f.id);
   f.used = false;
   Arena & a = c->arenas[f.arena];
-  if (--a.refs == 0) {
-    cudaFree(a.ptr);
-    a.ptr = nullptr;
-    a.bytes = 0;
-  }
+  if (--a.refs == 0) a.spare = true;
   c->freeSlots.push_back(slot);
   return 0;
+}
+
+// frees spare arenas, keeping the `keep` largest
+void trim_spares(vslamb200_ctx * c, int keep)
+{
+  std::vector<int> sp;
+  for (size_t i = 0; i < c->arenas.size(); i++)
+    if (c->arenas[i].ptr && c->arenas[i].spare) sp.push_back((int)i);
+  std::sort(sp.begin(), sp.end(), [&](int x, int y) { return c->arenas[x].bytes > c->arenas[y].bytes; });
+  for (size_t k = keep; k < sp.size(); k++) {
+    Arena & a = c->arenas[sp[k]];
+    cudaFree(a.ptr);
+    a = Arena();
+  }
 }
 
 int upload_table(vslamb200_ctx * c, const std::vector<int> & slots)
@@ -188,23 +199,43 @@ int make_frames(vslamb200_ctx * c, int n, const uint64_t * ids, int W, int H, co
   std::memset(&proto, 0, sizeof(proto));
   level_dims(W, H, nLevels, proto);
   const size_t frameBytes = layout_frame(proto, nullptr);
-  Arena a;
-  a.bytes = frameBytes * n;
-  CK(cudaMalloc(&a.ptr, a.bytes));
-  a.refs = n;
-  int arenaIdx = -1;
-  for (size_t i = 0; i < c->arenas.size(); i++)
-    if (!c->arenas[i].ptr) arenaIdx = (int)i;
-  if (arenaIdx < 0) {
-    c->arenas.push_back(a);
-    arenaIdx = (int)c->arenas.size() - 1;
-  } else {
-    c->arenas[arenaIdx] = a;
-  }
-  slots.resize(n);
+  // frames re-uploaded under the same id are replaced (work in flight is ordered before the new upload on the stream)
   for (int i = 0; i < n; i++) {
     auto it = c->idToSlot.find(ids[i]);
     if (it != c->idToSlot.end()) release_slot(c, it->second);
+  }
+  const size_t need = frameBytes * n;
+  int arenaIdx = -1;
+  for (size_t i = 0; i < c->arenas.size(); i++) {  // smallest spare arena that fits without wasting half of it
+    const Arena & s = c->arenas[i];
+    if (s.ptr && s.spare && s.bytes >= need && s.bytes <= 2 * need &&
+        (arenaIdx < 0 || s.bytes < c->arenas[arenaIdx].bytes))
+      arenaIdx = (int)i;
+  }
+  if (arenaIdx < 0) {
+    Arena a;
+    a.bytes = need;
+    if (cudaMalloc(&a.ptr, a.bytes) != cudaSuccess) {
+      cudaGetLastError();
+      CK(cudaStreamSynchronize(c->stream));
+      trim_spares(c, 0);
+      CK(cudaMalloc(&a.ptr, a.bytes));
+    }
+    for (size_t i = 0; i < c->arenas.size(); i++)
+      if (!c->arenas[i].ptr) arenaIdx = (int)i;
+    if (arenaIdx < 0) {
+      c->arenas.push_back(a);
+      arenaIdx = (int)c->arenas.size() - 1;
+    } else {
+      c->arenas[arenaIdx] = a;
+    }
+  }
+  Arena & a = c->arenas[arenaIdx];
+  a.spare = false;
+  a.refs = n;
+  trim_spares(c, 2);
+  slots.resize(n);
+  for (int i = 0; i < n; i++) {
     int slot;
     if (!c->freeSlots.empty()) {
       slot = c->freeSlots.back();
@@ -418,6 +449,7 @@ int vslamb200_frame_release_all(vslamb200_ctx * c)
   CK(cudaSetDevice(c->device));
   CK(cudaStreamSynchronize(c->stream));
   for (size_t i = 0; i < c->frames.size(); i++) release_slot(c, (int)i);
+  trim_spares(c, 0);
   return 0;
 }
 
