@@ -1,0 +1,160 @@
+"""CPU suite, part 2: the C-ABI library (loads, exports every declared symbol, fails loudly without a GPU), the
+ctypes mirror of its structs, and the host-side sharding logic incl. a world_size-2 gloo run.  No compute calls."""
+import ctypes as C
+import os
+import re
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+HEADER = os.path.join(ROOT, "include", "vslam_b200.h")
+
+
+def _declared_symbols():
+    src = open(HEADER).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(vslamb200_[a-z_0-9]+)\s*\(", src)))
+
+
+def test_header_declares_the_expected_entry_points():
+    syms = _declared_symbols()
+    for s in ("vslamb200_create", "vslamb200_destroy", "vslamb200_frames_upload", "vslamb200_frames_upload_device",
+              "vslamb200_align", "vslamb200_evaluate", "vslamb200_get_stats", "vslamb200_last_error"):
+        assert s in syms
+    assert len(syms) >= 20
+
+
+def test_library_loads_and_exports_every_declared_symbol(capi):
+    assert os.path.exists(capi.LIB_PATH), "libvslam_b200.so missing: run `python -c 'import __graft_entry__ as g; g.build()'`"
+    lib = C.CDLL(capi.LIB_PATH)
+    missing = [s for s in _declared_symbols() if not hasattr(lib, s)]
+    assert not missing, missing
+    lib.vslamb200_version.restype = C.c_int
+    assert lib.vslamb200_version() >= 100
+
+
+def test_library_is_built_for_sm_100a(capi):
+    out = subprocess.run(["cuobjdump", "-lelf", capi.LIB_PATH], capture_output=True, text=True)
+    if out.returncode != 0:
+        pytest.skip("cuobjdump unavailable")
+    assert "sm_100a" in out.stdout, out.stdout[:400]
+
+
+def test_ctypes_structs_match_the_header_layout(capi, tmp_path):
+    """The header compiles as plain C, and the ctypes mirrors have the sizes / key offsets the C compiler gives."""
+    src = tmp_path / "sizes.c"
+    src.write_text(
+        '#include <stdio.h>\n#include <stddef.h>\n#include "vslam_b200.h"\n'
+        'int main(void) { printf("%zu %zu %zu %zu %zu %zu %zu\\n", sizeof(vslamb200_config), sizeof(vslamb200_job), '
+        'sizeof(vslamb200_result), sizeof(vslamb200_stats), offsetof(vslamb200_result, iters), '
+        'offsetof(vslamb200_job, from_poses), offsetof(vslamb200_stats, phase_clocks)); return 0; }\n')
+    exe = tmp_path / "sizes"
+    subprocess.run(["gcc", "-std=c99", "-Wall", "-Werror", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)],
+                   check=True)
+    got = [int(x) for x in subprocess.run([str(exe)], capture_output=True, text=True, check=True).stdout.split()]
+    want = [C.sizeof(capi.Config), C.sizeof(capi.Job), C.sizeof(capi.Result), C.sizeof(capi.Stats),
+            capi.Result.iters.offset, capi.Job.from_poses.offset, capi.Stats.phase_clocks.offset]
+    assert got == want
+
+
+def test_create_fails_loudly_without_a_gpu(capi):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a CUDA device is present")
+    with pytest.raises(capi.VslamB200Error) as e:
+        capi.Context(capi.make_config())
+    assert "no CPU fallback" in str(e.value)
+
+
+def test_bad_arguments_are_rejected_before_any_device_work(capi):
+    lib = capi.lib()
+    out = C.c_void_p()
+    assert lib.vslamb200_create(None, 0, C.byref(out)) == -1
+    cfg = capi.make_config()
+    cfg.max_iterations = 0
+    assert lib.vslamb200_create(C.byref(cfg), 0, C.byref(out)) == -1
+    cfg = capi.make_config()
+    cfg.loss_kind = 99
+    assert lib.vslamb200_create(C.byref(cfg), 0, C.byref(out)) == -1
+    assert lib.vslamb200_align(None, None, 0, None) < 0
+    assert lib.vslamb200_get_stats(None, None) < 0
+    lib.vslamb200_destroy(None)  # no-op
+
+
+# ---------------------------------------------------------------------------------------------------------
+# sharding of a sequence over ranks
+# ---------------------------------------------------------------------------------------------------------
+def test_pair_ranges_partition_the_sequence():
+    from vslam_b200 import shard
+    for n in (0, 1, 7, 8, 999, 1000):
+        for world in (1, 2, 3, 8):
+            got = [shard.pair_range(n, world, r) for r in range(world)]
+            assert got[0][0] == 0 and got[-1][1] == n
+            for a, b in zip(got, got[1:]):
+                assert a[1] == b[0]
+            sizes = [b - a for a, b in got]
+            assert max(sizes) - min(sizes) <= 1
+            for r in range(world):
+                lo, hi = shard.frame_range(n, world, r)
+                assert hi - lo == (sizes[r] + 1 if sizes[r] else 0)
+    with pytest.raises(ValueError):
+        shard.pair_range(10, 2, 2)
+
+
+def test_chain_trajectory_composes_relative_motions(oracle):
+    from vslam_b200 import shard
+    rng = np.random.default_rng(3)
+    rel = np.stack([oracle.se3_exp(rng.normal(0, 0.05, 6)) for _ in range(6)])
+    traj = shard.chain_trajectory(rel)
+    cur = oracle.IDENTITY
+    for i, r in enumerate(rel):
+        cur = oracle.se3_mul(r, cur)
+        d = oracle.se3_log(oracle.se3_mul(traj[i + 1], oracle.se3_inv(cur)))
+        assert np.linalg.norm(d) < 1e-12
+
+
+_GLOO_WORKER = r"""
+import os, sys
+import numpy as np
+sys.path.insert(0, sys.argv[1])
+import torch.distributed as dist
+from vslam_b200 import shard
+rank, world, n_pairs = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(sys.argv[2])
+dist.init_process_group("gloo", rank=rank, world_size=world)
+def fake_pose(i):  # stands in for the aligned pose of pair i
+    return np.array([0.001 * i, -0.002 * i, 0.0005 * i, 1.0, 0.01 * i, 0.02 * i, -0.03 * i])
+lo, hi = shard.pair_range(n_pairs, world, rank)
+local = np.stack([fake_pose(i) for i in range(lo, hi)]) if hi > lo else np.zeros((0, 7))
+allp = shard.gather_poses(local, n_pairs, dist)
+want = np.stack([fake_pose(i) for i in range(n_pairs)])
+assert allp.shape == (n_pairs, 7) and np.array_equal(allp, want), rank
+dist.barrier()
+dist.destroy_process_group()
+print("rank", rank, "ok", lo, hi)
+"""
+
+
+@pytest.mark.parametrize("n_pairs", [9, 1])
+def test_gather_poses_world_size_2_gloo(tmp_path, n_pairs):
+    script = tmp_path / "worker.py"
+    script.write_text(_GLOO_WORKER)
+    port = 29500 + (os.getpid() % 2000)
+    procs = []
+    for rank in range(2):
+        env = dict(os.environ, RANK=str(rank), WORLD_SIZE="2", MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+        procs.append(subprocess.Popen([sys.executable, str(script), ROOT, str(n_pairs)], env=env,
+                                      stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True))
+    outs = []
+    for p in procs:
+        try:
+            o, _ = p.communicate(timeout=180)
+        except subprocess.TimeoutExpired:
+            p.kill()
+            o, _ = p.communicate()
+        outs.append(o)
+    for rank, (p, o) in enumerate(zip(procs, outs)):
+        assert p.returncode == 0, o[-2000:]
+        assert f"rank {rank} ok" in o
