@@ -195,3 +195,29 @@ def test_multi_keyframe_matches_oracle(ctx, capi, oracle, synth, K, prior):
     if not prior:  # the stacked motion prior (+I per keyframe against A/255^2) pins the pose to the initial guess
         dt, dr = pose_err(O, got["pose"], poses[K])
         assert dt < 0.01 and dr < 0.01
+
+
+@pytest.mark.gpu
+def test_cpp_host_mirror_matches_oracle(oracle, synth, capi):
+    """include/vslam_b200.hpp (the C++ mirror of AlignmentSE3 / SE3Alignment / Frame) driven like the reference's
+    alignment test, with column-major u8 / f64 frames: same pose as the oracle on the same rendered pair."""
+    import subprocess
+    from vslam_b200 import build
+    O = oracle
+    exe = build.build_host_mirror()
+    W, H, seed, L = 320, 240, 77, 3
+    r = subprocess.run([exe, str(W), str(H), str(seed), str(L)], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr
+    lines = dict((ln.split()[0], ln.split()[1:]) for ln in r.stdout.strip().splitlines())
+    assert "ok" in lines
+    got = np.array([float(x) for x in lines["pose"]])
+    gotm = np.array([float(x) for x in lines["multi"]])
+    p = synth.make_pair(W, H, seed)
+    f0, f1 = _frames(O, p, L)
+    cfg = O.make_config(max_iterations=30)
+    ref = O.align(cfg, f0, O.IDENTITY, f1, O.IDENTITY)
+    dt, dr = pose_err(O, got, ref["pose"])
+    assert dt < POSE_TOL and dr < POSE_TOL
+    refm = O.align(cfg, [f0], [O.IDENTITY], f1, O.IDENTITY, multi=True)
+    dt, dr = pose_err(O, gotm, refm["pose"])
+    assert dt < POSE_TOL and dr < POSE_TOL

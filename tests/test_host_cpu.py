@@ -158,3 +158,20 @@ def test_gather_poses_world_size_2_gloo(tmp_path, n_pairs):
     for rank, (p, o) in enumerate(zip(procs, outs)):
         assert p.returncode == 0, o[-2000:]
         assert f"rank {rank} ok" in o
+
+
+# ---------------------------------------------------------------------------------------------------------
+# C++ mirror of the reference interface (include/vslam_b200.hpp)
+# ---------------------------------------------------------------------------------------------------------
+def test_cpp_host_mirror_builds_and_fails_loudly_without_a_gpu(capi):
+    """-Wall -Wextra -Werror build of the header-only mirror + link against the C ABI; without a device the aligner
+    constructor throws std::runtime_error (what OdometryRgbd catches, odometry/src/Odometry.cpp:52-56)."""
+    import torch
+    from vslam_b200 import build
+    exe = build.build_host_mirror()
+    assert os.path.exists(exe)
+    if torch.cuda.is_available():
+        pytest.skip("a CUDA device is present: covered by the gpu test")
+    r = subprocess.run([exe, "160", "120", "5", "2"], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 3, (r.returncode, r.stderr)
+    assert "no CPU fallback" in r.stderr

@@ -47,10 +47,28 @@ def build_cuda(force=False, verbose=False):
     return LIB
 
 
+HOST_MIRROR = os.path.join(LIBDIR, "host_mirror")
+
+
+def build_host_mirror(force=False):
+    """g++ build of tests/cpp/host_mirror.cpp: the C++ mirror of the reference interface (include/vslam_b200.hpp)
+    linked against the C-ABI library and the synthetic-scene helper."""
+    root = os.path.join(_HERE, "..")
+    src = os.path.join(root, "tests", "cpp", "host_mirror.cpp")
+    inc = os.path.join(root, "include")
+    deps = [src, os.path.join(inc, "vslam_b200.hpp"), os.path.join(inc, "vslam_b200.h")]
+    if force or _stale(HOST_MIRROR, deps):
+        subprocess.check_call(["/usr/bin/g++", "-std=c++17", "-O2", "-Wall", "-Wextra", "-Werror", "-I", inc, src, "-o", HOST_MIRROR,
+                               "-L", LIBDIR, "-lvslam_b200", "-lvslam_synth", "-Wl,-rpath,$ORIGIN", "-lpthread"])
+    return HOST_MIRROR
+
+
 def build_all(force=False):
     from . import synth
     synth.build(force)
-    return build_cuda(force)
+    lib = build_cuda(force)
+    build_host_mirror(force)
+    return lib
 
 
 if __name__ == "__main__":
