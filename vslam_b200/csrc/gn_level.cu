@@ -334,10 +334,12 @@ __device__ __forceinline__ int warp_pick_ring(const WarpConsts & c, const WarpEv
 constexpr int CH = 4 * GT;               // interest points per chunk (4 per thread)
 constexpr int NS = 4;                    // ring stages
 constexpr int OFF_UVT = 0;               // u | v<<12 | T<<24   (CH x 4 B)
-constexpr int OFF_DG = CH * 4;           // phase A: depth f32; phase C: packed gradients (CH x 4 B)
-constexpr int OFF_ZI = CH * 8;           // phase C: 1/z f64 (CH x 8 B)
-constexpr int OFF_R = CH * 16;           // phase C: residuals s16 (CH x 2 B)
+constexpr int OFF_DG = WCH * 4;           // phase A: depth f32; phase C: packed gradients (CH x 4 B)
+constexpr int OFF_ZI = WCH * 8;           // phase C: 1/z f64 (CH x 8 B)
+constexpr int OFF_R = WCH * 16;           // phase C: residuals s16 (CH x 2 B)
+constexpr int WCH = CH / (GT / 32);         // points of a chunk owned by one warp
 constexpr int STAGE_BYTES = CH * 18;
+constexpr int WSTAGE_BYTES = WCH * 18;     // one stage of one warp's private ring
 
 __device__ __forceinline__ uint32_t smem_u32(const void * p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(uint64_t * bar, uint32_t count)
@@ -397,8 +399,7 @@ struct LevelShared
   double red[GT / 32 * NE_TERMS];
   SolveScratch X;
   double so[2];  // {scale, offset} of the current view, written by the cluster's leading CTA
-  alignas(8) uint64_t full[NS];   // TMA bytes of the stage have landed
-  alignas(8) uint64_t empty[NS];  // every warp has copied the stage into registers
+  alignas(8) uint64_t full[GT / 32][NS];  // per warp and stage: the TMA bytes have landed
 };
 // dynamic shared memory: ring | ViewState[K] | partial[2][K][28] | sums[K][28]
 __host__ __device__ inline size_t level_dyn_smem(int K)
@@ -424,14 +425,20 @@ __device__ __forceinline__ void slice_of(int n, unsigned C, unsigned rank, int &
   p1 = min(n, p0 + per);
 }
 
-// one elected thread: bulk copies of chunk c of the slice [p0, p1) into ring stage (item % NS)
+// Every warp owns a private ring: lane 0 streams the warp's quarter of chunk c of the slice [p0, p1) into stage
+// (item % NS) of that ring.  A warp refills a stage right after it has copied it into registers, so no warp ever
+// waits for another one (no "empty" barriers, no producer thread that can fall behind).
 __device__ __forceinline__ void issue_chunk(
-  LevelShared & S, unsigned char * ring, const ViewState & V, bool phaseC, int p0, int p1, int c, uint32_t item)
+  LevelShared & S, unsigned char * ring, const ViewState & V, bool phaseC, int p0, int p1, int c, uint32_t item, int warp)
 {
-  const int start = p0 + c * CH;
-  const int cnt = (min(CH, p1 - start) + 7) & ~7;
-  unsigned char * st = ring + (size_t)(item % NS) * STAGE_BYTES;
-  uint64_t * bar = &S.full[item % NS];
+  const int start = p0 + c * CH + warp * WCH;
+  uint64_t * bar = &S.full[warp][item % NS];
+  if (start >= p1) {  // nothing of the chunk belongs to this warp: keep the barrier's phase in step with `item`
+    mbar_arrive(bar);
+    return;
+  }
+  const int cnt = (min(WCH, p1 - start) + 7) & ~7;
+  unsigned char * st = ring + (size_t)(warp * NS + item % NS) * WSTAGE_BYTES;
   const uint64_t pol = l2_evict_first_policy();
   mbar_expect_tx(bar, (uint32_t)cnt * (phaseC ? 18u : 8u));
   bulk_g2s_stream(st + OFF_UVT, V.uvt + start, cnt * 4, bar, pol);
@@ -464,10 +471,8 @@ __global__ void __launch_bounds__(GT, CTAS_PER_SM) gn_level_kernel(
   double * sums = partial + 2 * K * NE_TERMS;                  // [K][28]: cluster totals
   for (int k = 0; k < K; k++) block_copy(&Vs[k], views + S.J.view0 + k);
   if (tid == 0) {
-    for (int s = 0; s < NS; s++) {
-      mbar_init(&S.full[s], 1);
-      mbar_init(&S.empty[s], GT / 32);
-    }
+    for (int w = 0; w < GT / 32; w++)
+      for (int s = 0; s < NS; s++) mbar_init(&S.full[w][s], 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
@@ -479,8 +484,8 @@ __global__ void __launch_bounds__(GT, CTAS_PER_SM) gn_level_kernel(
     int p0, p1;
     slice_of(Vs[0].nIp, C, rank, p0, p1);
     const int nCh = (p1 - p0 + CH - 1) / CH;
-    if (tid == 0)
-      for (int c = 0; c < min(NS, nCh); c++) issue_chunk(S, ring, Vs[0], false, p0, p1, c, item + c);
+    if (lane == 0)
+      for (int c = 0; c < min(NS, nCh); c++) issue_chunk(S, ring, Vs[0], false, p0, p1, c, item + c, warp);
   }
 
   long long tc = clock64();
@@ -530,19 +535,21 @@ __global__ void __launch_bounds__(GT, CTAS_PER_SM) gn_level_kernel(
         };
         auto start_chunk = [&](int ch, Pend & P) {
           const uint32_t it = item + ch;
-          if (tid == 0 && ch >= 1 && ch - 1 + NS < nCh) {
-            mbar_wait(&S.empty[(it - 1) % NS], ((it - 1) / NS) & 1);
-            issue_chunk(S, ring, V, false, p0, p1, ch - 1 + NS, it - 1 + NS);
+          P.g = p0 + ch * CH + 4 * tid;
+          const unsigned char * st = ring + (size_t)(warp * NS + it % NS) * WSTAGE_BYTES;
+          mbar_wait(&S.full[warp][it % NS], (it / NS) & 1);
+          if (p0 + ch * CH + warp * WCH >= p1) {  // warp-uniform: nothing of this chunk belongs to the warp
+            if (lane == 0 && ch + NS < nCh) issue_chunk(S, ring, V, false, p0, p1, ch + NS, it + NS, warp);
+#pragma unroll
+            for (int q = 0; q < 4; q++) P.pix[q] = -1, P.val[q] = 0, P.T[q] = 0;
+            return;
           }
-          const unsigned char * st = ring + (size_t)(it % NS) * STAGE_BYTES;
-          mbar_wait(&S.full[it % NS], (it / NS) & 1);
-          const uint4 pk4 = *reinterpret_cast<const uint4 *>(st + OFF_UVT + tid * 16);
-          const float4 dd4 = *reinterpret_cast<const float4 *>(st + OFF_DG + tid * 16);
+          const uint4 pk4 = *reinterpret_cast<const uint4 *>(st + OFF_UVT + lane * 16);
+          const float4 dd4 = *reinterpret_cast<const float4 *>(st + OFF_DG + lane * 16);
           __syncwarp();
-          if (lane == 0) mbar_arrive(&S.empty[it % NS]);
+          if (lane == 0 && ch + NS < nCh) issue_chunk(S, ring, V, false, p0, p1, ch + NS, it + NS, warp);
           const uint32_t pk[4] = {pk4.x, pk4.y, pk4.z, pk4.w};
           const float dd[4] = {dd4.x, dd4.y, dd4.z, dd4.w};
-          P.g = p0 + ch * CH + 4 * tid;
           bool good[4];
           WarpEval ev[4];
 #pragma unroll
@@ -595,11 +602,12 @@ __global__ void __launch_bounds__(GT, CTAS_PER_SM) gn_level_kernel(
         }
         item += nCh;
       }
-      // the residuals were written through the generic proxy and are read back by TMA (async proxy)
+      // the residuals were written through the generic proxy and are read back by TMA (async proxy); a warp reads
+      // back exactly the entries it wrote, so its phase-C prologue can start as soon as the warp itself is done
       asm volatile("fence.proxy.async;" ::: "memory");
-      __syncthreads();
-      if (tid == 0)
-        for (int c = 0; c < min(NS, nCh); c++) issue_chunk(S, ring, V, true, p0, p1, c, item + c);
+      __syncwarp();
+      if (lane == 0)
+        for (int c = 0; c < min(NS, nCh); c++) issue_chunk(S, ring, V, true, p0, p1, c, item + c, warp);
       lap(0);
       // ---------------------------------------------------------------- scale + weight table
       // The leading CTA sums the cluster's histograms, runs the scaler and publishes {scale, offset} into every
@@ -654,20 +662,20 @@ __global__ void __launch_bounds__(GT, CTAS_PER_SM) gn_level_kernel(
         const double2 * __restrict__ lut = S.lut;
 #pragma unroll 1
         for (int ch = 0; ch < nCh; ch++, item++) {
-          if (tid == 0 && ch >= 1 && ch - 1 + NS < nCh) {
-            mbar_wait(&S.empty[(item - 1) % NS], ((item - 1) / NS) & 1);
-            issue_chunk(S, ring, V, true, p0, p1, ch - 1 + NS, item - 1 + NS);
+          const unsigned char * st = ring + (size_t)(warp * NS + item % NS) * WSTAGE_BYTES;
+          mbar_wait(&S.full[warp][item % NS], (item / NS) & 1);
+          if (p0 + ch * CH + warp * WCH >= p1) {  // warp-uniform: nothing of this chunk belongs to the warp
+            if (lane == 0 && ch + NS < nCh) issue_chunk(S, ring, V, true, p0, p1, ch + NS, item + NS, warp);
+            continue;
           }
-          const unsigned char * st = ring + (size_t)(item % NS) * STAGE_BYTES;
-          mbar_wait(&S.full[item % NS], (item / NS) & 1);
           const int g = p0 + ch * CH + 4 * tid;
-          const uint4 pk4 = *reinterpret_cast<const uint4 *>(st + OFF_UVT + tid * 16);
-          const uint4 gg4 = *reinterpret_cast<const uint4 *>(st + OFF_DG + tid * 16);
-          const double2 za = *reinterpret_cast<const double2 *>(st + OFF_ZI + tid * 32);
-          const double2 zb = *reinterpret_cast<const double2 *>(st + OFF_ZI + tid * 32 + 16);
-          const uint2 packed = *reinterpret_cast<const uint2 *>(st + OFF_R + tid * 8);
+          const uint4 pk4 = *reinterpret_cast<const uint4 *>(st + OFF_UVT + lane * 16);
+          const uint4 gg4 = *reinterpret_cast<const uint4 *>(st + OFF_DG + lane * 16);
+          const double2 za = *reinterpret_cast<const double2 *>(st + OFF_ZI + lane * 32);
+          const double2 zb = *reinterpret_cast<const double2 *>(st + OFF_ZI + lane * 32 + 16);
+          const uint2 packed = *reinterpret_cast<const uint2 *>(st + OFF_R + lane * 8);
           __syncwarp();
-          if (lane == 0) mbar_arrive(&S.empty[item % NS]);
+          if (lane == 0 && ch + NS < nCh) issue_chunk(S, ring, V, true, p0, p1, ch + NS, item + NS, warp);
           const uint32_t pk[4] = {pk4.x, pk4.y, pk4.z, pk4.w};
           const uint32_t gg[4] = {gg4.x, gg4.y, gg4.z, gg4.w};
           const double zz[4] = {za.x, za.y, zb.x, zb.y};
@@ -709,7 +717,6 @@ __global__ void __launch_bounds__(GT, CTAS_PER_SM) gn_level_kernel(
           }
         }
       }
-      __syncthreads();  // every warp is done with the ring
       lap(3);
       // prologue of the next phase A (next keyframe, or keyframe 0 of the next iteration): the list does not
       // depend on the pose, so it streams in behind the reduction and the solve
@@ -718,8 +725,8 @@ __global__ void __launch_bounds__(GT, CTAS_PER_SM) gn_level_kernel(
         int q0, q1;
         slice_of(Vn.nIp, C, rank, q0, q1);
         const int nChN = (q1 - q0 + CH - 1) / CH;
-        if (tid == 0)
-          for (int c = 0; c < min(NS, nChN); c++) issue_chunk(S, ring, Vn, false, q0, q1, c, item + c);
+        if (lane == 0)  // the warp's own ring is free as soon as the warp leaves phase C
+          for (int c = 0; c < min(NS, nChN); c++) issue_chunk(S, ring, Vn, false, q0, q1, c, item + c, warp);
       }
       // fixed-order block reduction: lanes (xor tree), then warps in order
 #pragma unroll
@@ -767,7 +774,7 @@ __global__ void __launch_bounds__(GT, CTAS_PER_SM) gn_level_kernel(
     int p0, p1;
     slice_of(Vs[0].nIp, C, rank, p0, p1);
     const int nCh = (p1 - p0 + CH - 1) / CH;
-    for (int c = 0; c < min(NS, nCh); c++) mbar_wait(&S.full[(item + c) % NS], ((item + c) / NS) & 1);
+    for (int c = 0; c < min(NS, nCh); c++) mbar_wait(&S.full[warp][(item + c) % NS], ((item + c) / NS) & 1);
   }
   cluster.sync();  // nobody leaves while its shared memory may still be read remotely
   if (rank == 0) {
