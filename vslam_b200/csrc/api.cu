@@ -634,20 +634,18 @@ int prepare_workspace(vslamb200_ctx * c, Problem & P, const vb::SolverParams & s
 {
   const int nJobs = (int)P.jobs.size(), nViews = (int)P.views.size();
   const size_t npx0 = (size_t)P.W * P.H;
-  const size_t listStride = align_up(npx0, 64);
-  // per view: zi f64 | uvt u32 | d f32 | g u32 | r s16   (22 bytes per candidate pixel)
-  CK(c->lists.ensure(listStride * 22 * nViews));
+  const size_t listStride = align_up(npx0, vb::LIST_TILE);
+  // per view: list tiles (20 B per candidate pixel) | r u16   (22 bytes per candidate pixel)
+  const size_t tileBytes = listStride / vb::LIST_TILE * vb::LIST_TILE_BYTES;
+  CK(c->lists.ensure((tileBytes + listStride * 2) * nViews));
   CK(c->chunkCounts.ensure((size_t)nViews * vb::list_chunks_for((int)npx0) * sizeof(int)));
   CK(c->partials.ensure((size_t)nViews * vb::NE_TERMS * sizeof(double)));
   uint8_t * base = c->lists.as<uint8_t>();
   for (int v = 0; v < nViews; v++) {
     vb::ViewState & V = P.views[v];
-    uint8_t * b = base + (size_t)v * listStride * 22;
-    V.zi = (double *)b;
-    V.uvt = (uint32_t *)(b + listStride * 8);
-    V.d = (float *)(b + listStride * 12);
-    V.g = (uint32_t *)(b + listStride * 16);
-    V.r = (int16_t *)(b + listStride * 20);
+    uint8_t * b = base + (size_t)v * (tileBytes + listStride * 2);
+    V.tiles = b;
+    V.r = (int16_t *)(b + tileBytes);
   }
   CK(c->jobs.ensure(nJobs * sizeof(vb::JobState)));
   CK(c->views.ensure(nViews * sizeof(vb::ViewState)));

@@ -37,6 +37,9 @@ struct Pose
 };
 
 // Per (job, keyframe) state of the current pyramid level.
+constexpr int LIST_TILE = 128;
+constexpr int TILE_OFF_D = 0, TILE_OFF_UVT = 512, TILE_OFF_G = 1024, TILE_OFF_ZI = 1536, LIST_TILE_BYTES = 2560;
+
 struct ViewState
 {
   // static per level
@@ -51,11 +54,10 @@ struct ViewState
   // fp32 hi/lo splits of the fp64 constants: keeps the fp32 Jacobian free of coherent rounding bias
   float ifxH, ifxL, ifyH, ifyL, kxH, kxL, kyH, kyL, fxJH, fxJL, fyJH, fyJL;
   float fx32, fy32;
-  // interest list (SoA)
-  uint32_t * uvt;           // u | v<<12 | T<<24
-  float * d;                // depth of the point
-  double * zi;              // 1 / depth in fp64 (Warp.cpp:170 zi), computed once per level
-  uint32_t * g;             // dIx (low 16) | dIy (high 16)
+  // interest list: LIST_TILE-point tiles, each  d f32[128] | uvt u32[128] | g u32[128] | zi f64[128]  so that one
+  // bulk copy brings what a phase needs ([d|uvt] for the warp phase, [uvt|g|zi] for the Jacobian phase)
+  //   uvt = u | v<<12 | T<<24, d = depth, g = dIx (low 16) | dIy (high 16), zi = 1 / depth in fp64 (Warp.cpp:170)
+  unsigned char * tiles;
   int16_t * r;              // residual code of the current iteration: r + 255, R_CODE_INVISIBLE if not visible
   int nIp;                  // retained interest points (nConstraints of this view)
   // warp

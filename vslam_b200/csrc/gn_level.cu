@@ -331,15 +331,18 @@ __device__ __forceinline__ int warp_pick_ring(const WarpConsts & c, const WarpEv
 // ------------------------------------------------------------------------------------------------
 // shared-memory ring fed by TMA bulk copies
 // ------------------------------------------------------------------------------------------------
-constexpr int CH = 4 * GT;               // interest points per chunk (4 per thread)
-constexpr int NS = 4;                    // ring stages
-constexpr int OFF_UVT = 0;               // u | v<<12 | T<<24   (CH x 4 B)
-constexpr int OFF_DG = WCH * 4;           // phase A: depth f32; phase C: packed gradients (CH x 4 B)
-constexpr int OFF_ZI = WCH * 8;           // phase C: 1/z f64 (CH x 8 B)
-constexpr int OFF_R = WCH * 16;           // phase C: residuals s16 (CH x 2 B)
-constexpr int WCH = CH / (GT / 32);         // points of a chunk owned by one warp
-constexpr int STAGE_BYTES = CH * 18;
-constexpr int WSTAGE_BYTES = WCH * 18;     // one stage of one warp's private ring
+constexpr int CH = 4 * GT;                  // interest points per chunk (4 per thread)
+constexpr int NS = 4;                       // ring stages
+constexpr int WCH = CH / (GT / 32);         // points of a chunk owned by one warp == one list tile
+static_assert(WCH == LIST_TILE, "a warp's share of a chunk is one list tile");
+// one stage of a warp's private ring.  Phase A: [d | uvt] (the first 1024 B of the tile).  Phase C: [uvt | g | zi]
+// (the last 2048 B of the tile) followed by the tile's 128 residual codes.
+constexpr int A_OFF_D = 0, A_OFF_UVT = 512, A_BYTES = 1024;
+constexpr int C_OFF_UVT = 0, C_OFF_G = 512, C_OFF_ZI = 1024, C_OFF_R = 2048, C_TILE_BYTES = 2048, C_R_BYTES = 2 * WCH;
+constexpr int WSTAGE_BYTES = C_OFF_R + C_R_BYTES;
+constexpr int STAGE_BYTES = WSTAGE_BYTES * (GT / 32);
+static_assert(TILE_OFF_D == 0 && TILE_OFF_UVT == A_OFF_UVT && TILE_OFF_G - TILE_OFF_UVT == C_OFF_G &&
+              TILE_OFF_ZI - TILE_OFF_UVT == C_OFF_ZI && LIST_TILE_BYTES - TILE_OFF_UVT == C_TILE_BYTES, "tile layout");
 
 __device__ __forceinline__ uint32_t smem_u32(const void * p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(uint64_t * bar, uint32_t count)
@@ -416,11 +419,10 @@ __device__ __forceinline__ void block_copy(T * dst, const T * src)
   for (int i = threadIdx.x; i < (int)(sizeof(T) / 4); i += GT) d[i] = s[i];
 }
 
-// slice of a view's interest list owned by one CTA of the cluster (multiples of 8 points: 16-byte TMA alignment
-// of the 2-byte residual array)
+// slice of a view's interest list owned by one CTA of the cluster: whole list tiles
 __device__ __forceinline__ void slice_of(int n, unsigned C, unsigned rank, int & p0, int & p1)
 {
-  const int per = (((n + (int)C - 1) / (int)C) + 7) & ~7;
+  const int per = (((n + (int)C - 1) / (int)C) + LIST_TILE - 1) / LIST_TILE * LIST_TILE;
   p0 = min(n, (int)rank * per);
   p1 = min(n, p0 + per);
 }
@@ -437,17 +439,16 @@ __device__ __forceinline__ void issue_chunk(
     mbar_arrive(bar);
     return;
   }
-  const int cnt = (min(WCH, p1 - start) + 7) & ~7;
   unsigned char * st = ring + (size_t)(warp * NS + item % NS) * WSTAGE_BYTES;
+  const unsigned char * tile = V.tiles + (size_t)(start / LIST_TILE) * LIST_TILE_BYTES;
   const uint64_t pol = l2_evict_first_policy();
-  mbar_expect_tx(bar, (uint32_t)cnt * (phaseC ? 18u : 8u));
-  bulk_g2s_stream(st + OFF_UVT, V.uvt + start, cnt * 4, bar, pol);
   if (phaseC) {
-    bulk_g2s_stream(st + OFF_DG, V.g + start, cnt * 4, bar, pol);
-    bulk_g2s_stream(st + OFF_ZI, V.zi + start, cnt * 8, bar, pol);
-    bulk_g2s(st + OFF_R, V.r + start, cnt * 2, bar);
+    mbar_expect_tx(bar, C_TILE_BYTES + C_R_BYTES);
+    bulk_g2s_stream(st, tile + TILE_OFF_UVT, C_TILE_BYTES, bar, pol);
+    bulk_g2s(st + C_OFF_R, V.r + start, C_R_BYTES, bar);
   } else {
-    bulk_g2s_stream(st + OFF_DG, V.d + start, cnt * 4, bar, pol);
+    mbar_expect_tx(bar, A_BYTES);
+    bulk_g2s_stream(st, tile, A_BYTES, bar, pol);
   }
 }
 
@@ -544,8 +545,8 @@ __global__ void __launch_bounds__(GT, CTAS_PER_SM) gn_level_kernel(
             for (int q = 0; q < 4; q++) P.pix[q] = -1, P.val[q] = 0, P.T[q] = 0;
             return;
           }
-          const uint4 pk4 = *reinterpret_cast<const uint4 *>(st + OFF_UVT + lane * 16);
-          const float4 dd4 = *reinterpret_cast<const float4 *>(st + OFF_DG + lane * 16);
+          const uint4 pk4 = *reinterpret_cast<const uint4 *>(st + A_OFF_UVT + lane * 16);
+          const float4 dd4 = *reinterpret_cast<const float4 *>(st + A_OFF_D + lane * 16);
           __syncwarp();
           if (lane == 0 && ch + NS < nCh) issue_chunk(S, ring, V, false, p0, p1, ch + NS, it + NS, warp);
           const uint32_t pk[4] = {pk4.x, pk4.y, pk4.z, pk4.w};
@@ -669,11 +670,11 @@ __global__ void __launch_bounds__(GT, CTAS_PER_SM) gn_level_kernel(
             continue;
           }
           const int g = p0 + ch * CH + 4 * tid;
-          const uint4 pk4 = *reinterpret_cast<const uint4 *>(st + OFF_UVT + lane * 16);
-          const uint4 gg4 = *reinterpret_cast<const uint4 *>(st + OFF_DG + lane * 16);
-          const double2 za = *reinterpret_cast<const double2 *>(st + OFF_ZI + lane * 32);
-          const double2 zb = *reinterpret_cast<const double2 *>(st + OFF_ZI + lane * 32 + 16);
-          const uint2 packed = *reinterpret_cast<const uint2 *>(st + OFF_R + lane * 8);
+          const uint4 pk4 = *reinterpret_cast<const uint4 *>(st + C_OFF_UVT + lane * 16);
+          const uint4 gg4 = *reinterpret_cast<const uint4 *>(st + C_OFF_G + lane * 16);
+          const double2 za = *reinterpret_cast<const double2 *>(st + C_OFF_ZI + lane * 32);
+          const double2 zb = *reinterpret_cast<const double2 *>(st + C_OFF_ZI + lane * 32 + 16);
+          const uint2 packed = *reinterpret_cast<const uint2 *>(st + C_OFF_R + lane * 8);
           __syncwarp();
           if (lane == 0 && ch + NS < nCh) issue_chunk(S, ring, V, true, p0, p1, ch + NS, item + NS, warp);
           const uint32_t pk[4] = {pk4.x, pk4.y, pk4.z, pk4.w};

@@ -101,7 +101,8 @@ __global__ void scatter_rcode_kernel2(const ViewState * __restrict__ views, int 
 {
   const ViewState & V = views[view];
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < V.nIp; i += gridDim.x * blockDim.x) {
-    const uint32_t pk = V.uvt[i];
+    const uint32_t pk =
+      reinterpret_cast<const uint32_t *>(V.tiles + (size_t)(i / LIST_TILE) * LIST_TILE_BYTES + TILE_OFF_UVT)[i % LIST_TILE];
     const int code = V.r[i];
     plane[(size_t)((pk >> 12) & 0xfff) * V.W + (pk & 0xfff)] = code == R_CODE_INVISIBLE ? R_INVISIBLE : (int16_t)(code - 255);
   }

@@ -116,10 +116,12 @@ __global__ void __launch_bounds__(LTHREADS) list_write_kernel(
     if (keep) {
       const int o = running + woff + __popc(m & ((1u << lane) - 1u));
       const int v = i / W, u = i - v * W;
-      V.uvt[o] = (uint32_t)u | ((uint32_t)v << 12) | ((uint32_t)f.I[level][i] << 24);
-      V.d[o] = d;
-      V.zi[o] = 1.0 / (double)d;   // Warp.cpp:170
-      V.g[o] = g;
+      unsigned char * tile = V.tiles + (size_t)(o / LIST_TILE) * LIST_TILE_BYTES;
+      const int j = o % LIST_TILE;
+      reinterpret_cast<float *>(tile + TILE_OFF_D)[j] = d;
+      reinterpret_cast<uint32_t *>(tile + TILE_OFF_UVT)[j] = (uint32_t)u | ((uint32_t)v << 12) | ((uint32_t)f.I[level][i] << 24);
+      reinterpret_cast<uint32_t *>(tile + TILE_OFF_G)[j] = g;
+      reinterpret_cast<double *>(tile + TILE_OFF_ZI)[j] = 1.0 / (double)d;  // Warp.cpp:170
     }
     running += tot;
     __syncthreads();
