@@ -105,14 +105,14 @@ def dist_env():
     return rank, world, local
 
 
-def make_jobs(capi, n_frames):
+def make_jobs(capi, n_frames, id0=0):
     ident = (C.c_double * 7)(0, 0, 0, 1, 0, 0, 0)
     n = n_frames - 1
     jobs = (capi.Job * n)()
-    ids = np.arange(n_frames, dtype=np.uint64)
+    ids = np.arange(id0, id0 + n_frames, dtype=np.uint64)
     poses = np.tile(np.array([0, 0, 0, 1, 0, 0, 0], np.float64), (n, 1))
     for i in range(n):
-        jobs[i].to = i + 1
+        jobs[i].to = id0 + i + 1
         jobs[i].to_pose = ident
         jobs[i].n_from = 1
         jobs[i].multi = 0
@@ -206,21 +206,38 @@ def main():
         ctx.upload_device(ids, d_gray.data_ptr(), d_depth.data_ptr(), F, W, H, cams, LEVELS)
         ctx.align_raw(jobs, F - 1, results)
 
-    def step_e2e():
-        capi.check(capi.lib().vslamb200_frames_upload(
-            ctx.h, F, capi.ptr(ids), W, H, C.c_void_p(h_gray.data_ptr()), 0, C.c_void_p(h_depth.data_ptr()),
-            capi.DEPTH_F32, 0, capi.ROW_MAJOR, capi.ptr(cams), LEVELS))
-        ctx.align_raw(jobs, F - 1, results)
+    # End to end through the C ABI with pinned HOST buffers.  Successive steps (batches) alternate between two sets of
+    # frame ids: the upload of the next step's frames (copy stream) is queued before this step's alignment is called, so
+    # in steady state the PCIe transfer hides under the kernels.  Every step's upload, including the first one, and
+    # every step's result read-back are inside the timed region.
+    ids2 = [ids, ids + np.uint64(F)]
+    jobs2, keep2 = [jobs], [_keep]
+    j1, k1 = make_jobs(capi, F, id0=F)
+    jobs2.append(j1)
+    keep2.append(k1)
 
-    def timed(fn, steps):
+    def upload_set(q):
+        ctx.upload_async(ids2[q], h_gray.data_ptr(), h_depth.data_ptr(), F, W, H, cams, LEVELS)
+
+    def run_e2e(steps):
+        upload_set(0)
+        for st_ in range(steps):
+            if st_ + 1 < steps:
+                upload_set((st_ + 1) & 1)
+            ctx.align_raw(jobs2[st_ & 1], F - 1, results)
+
+    def timed(fn, steps, loop=True):
         if use_dist:
             dist.barrier()
         torch.cuda.synchronize()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         with torch.cuda.stream(stream):
             e0.record(stream)
-            for _ in range(steps):
-                fn()
+            if loop:
+                for _ in range(steps):
+                    fn()
+            else:
+                fn(steps)
             e1.record(stream)
         torch.cuda.synchronize()
         ms = torch.tensor([e0.elapsed_time(e1)], device="cuda")
@@ -241,8 +258,10 @@ def main():
     value = pairs / (ms * 1e-3)
 
     # end to end through the C ABI with host buffers
-    step_e2e()
-    ms_e2e = timed(step_e2e, args.steps)
+    resident_poses = np.array([list(r.pose) for r in results])
+    run_e2e(2)
+    ms_e2e = timed(run_e2e, args.steps, loop=False)
+    e2e_diff = float(np.abs(np.array([list(r.pose) for r in results]) - resident_poses).max())
     e2e = pairs / (ms_e2e * 1e-3)
     h2d = F * W * H * 5
     d2h = (F - 1) * C.sizeof(capi.Result)
@@ -303,7 +322,8 @@ def main():
                        "l2_policy": "inputs (1.5 GB of frames per step) are larger than the 126 MB L2",
                        "mean_gn_iterations_per_pair": float(iters_per_pair)},
             "e2e": {"value": e2e, "unit": "pairs/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "ms_per_step": ms_e2e / args.steps},
+                    "ms_per_step": ms_e2e / args.steps, "max_pose_diff_vs_resident": e2e_diff,
+                    "pipeline": "upload of step s+1 (copy stream) overlaps the alignment of step s; all uploads timed"},
             "gpu_launches": int(st["kernel_launches"]),
             "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
         }))

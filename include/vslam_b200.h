@@ -115,7 +115,15 @@ int vslamb200_set_stream(vslamb200_ctx * ctx, void * cuda_stream);
 int vslamb200_frames_upload(
   vslamb200_ctx * ctx, int n, const uint64_t * ids, int W, int H, const uint8_t * gray, size_t gray_stride,
   const void * depth, int depth_type, size_t depth_stride, int layout, const double * cams, int n_levels);
-/* same, gray / depth already resident on the context's device (row-major u8 / f32) */
+/* Same as vslamb200_frames_upload, but returns as soon as the work is queued (row-major u8 + f32 depth only; other
+ * layouts take the synchronous path): the host->device copies run on an internal copy stream and overlap whatever the
+ * context computes next; pyramids and gradients are queued behind them.  The host buffers should be pinned and must stay
+ * untouched until the next vslamb200_align / vslamb200_synchronize on this context.  Lets a caller pipeline
+ * "upload sub-batch k+1" under "align sub-batch k". */
+int vslamb200_frames_upload_async(
+  vslamb200_ctx * ctx, int n, const uint64_t * ids, int width, int height, const uint8_t * gray, size_t gray_stride,
+  const void * depth, int depth_type, size_t depth_stride, int layout, const double * cams, int n_levels);
+/* same as vslamb200_frames_upload, gray / depth already resident on the context's device (row-major u8 / f32) */
 int vslamb200_frames_upload_device(
   vslamb200_ctx * ctx, int n, const uint64_t * ids, int W, int H, const uint8_t * d_gray, const float * d_depth,
   const double * cams, int n_levels);

@@ -221,3 +221,48 @@ def test_cpp_host_mirror_matches_oracle(oracle, synth, capi):
     refm = O.align(cfg, [f0], [O.IDENTITY], f1, O.IDENTITY, multi=True)
     dt, dr = pose_err(O, gotm, refm["pose"])
     assert dt < POSE_TOL and dr < POSE_TOL
+
+
+@pytest.mark.gpu
+def test_async_upload_pipeline_is_identical_to_the_synchronous_path(capi, oracle, synth):
+    """vslamb200_frames_upload_async + per-sub-batch align (the end-to-end pipeline of bench.py) returns bit-identical
+    poses to one synchronous upload + one batched align, including when frame ids are re-uploaded."""
+    import torch
+    F, W, H, L = 9, 320, 240, 3
+    cam = synth.cam_for(W, H)
+    gray, depth, _ = synth.make_sequence(F, W, H, seed=99, cam=cam)
+    ident = oracle.IDENTITY
+    jobs = [dict(to=i + 1, to_pose=ident, frm=[i], from_poses=ident, multi=False) for i in range(F - 1)]
+    ctx = capi.Context(capi.make_config(max_iterations=30))
+    try:
+        ctx.upload(np.arange(F), gray, depth, cam, L)
+        want = ctx.align(jobs)
+        hg = torch.from_numpy(gray).pin_memory()
+        hd = torch.from_numpy(depth).pin_memory()
+        for rep in range(2):  # the second round replaces every frame while the arenas are recycled
+            got = []
+            bounds = [0, 4, 7, F]
+            ids = np.arange(F, dtype=np.uint64)
+            cams = np.tile(np.array(cam, np.float64), (F, 1))
+
+            def up(k):
+                a, b = bounds[k], bounds[k + 1]
+                ctx.upload_async(ids[a:b], hg.data_ptr() + a * W * H, hd.data_ptr() + a * W * H * 4, b - a, W, H, cams[a:b], L)
+
+            up(0)
+            for k in range(3):
+                if k + 1 < 3:
+                    up(k + 1)
+                p0, p1 = max(bounds[k] - 1, 0), bounds[k + 1] - 1
+                got += ctx.align(jobs[p0:p1])
+            assert len(got) == F - 1
+            for a, b in zip(got, want):
+                assert np.array_equal(a["pose"], b["pose"]) and list(a["iters"]) == list(b["iters"])
+        # download after an asynchronous upload waits for it
+        ctx.upload_async(ids[:2], hg.data_ptr(), hd.data_ptr(), 2, W, H, cams[:2], L)
+        lv = ctx.download(1, 1)
+        f1 = oracle.Frame(gray[1], depth[1].astype(np.float64), *cam, L)
+        assert np.array_equal(lv["I"], f1.level(1)["I"])
+        ctx.synchronize()
+    finally:
+        ctx.close()

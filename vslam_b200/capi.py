@@ -74,6 +74,7 @@ def lib():
         L.vslamb200_set_config.argtypes = [vp, vp]
         L.vslamb200_set_stream.argtypes = [vp, vp]
         L.vslamb200_frames_upload.argtypes = [vp, i, vp, i, i, vp, sz, vp, i, sz, i, vp, i]
+        L.vslamb200_frames_upload_async.argtypes = [vp, i, vp, i, i, vp, sz, vp, i, sz, i, vp, i]
         L.vslamb200_frames_upload_device.argtypes = [vp, i, vp, i, i, vp, vp, vp, i]
         L.vslamb200_frame_release.argtypes = [vp, u64]
         L.vslamb200_frame_release_all.argtypes = [vp]
@@ -143,6 +144,14 @@ class Context:
         dt = DEPTH_F32 if depth.dtype == np.float32 else DEPTH_F64
         check(lib().vslamb200_frames_upload(self.h, n, ptr(ids), W, H, ptr(gray), 0, ptr(depth), dt, 0, layout,
                                             ptr(cams), n_levels))
+
+    def upload_async(self, ids, gray_ptr, depth_ptr, n, W, H, cams, n_levels):
+        """Queues the upload of n row-major u8 / f32 frames from (pinned) host memory at the given addresses and returns;
+        the buffers must stay untouched until the next align() / synchronize()."""
+        ids = np.ascontiguousarray(np.atleast_1d(ids), np.uint64)
+        cams = np.ascontiguousarray(np.broadcast_to(np.asarray(cams, np.float64).reshape(-1, 4), (n, 4)))
+        check(lib().vslamb200_frames_upload_async(self.h, n, ptr(ids), W, H, C.c_void_p(gray_ptr), 0,
+                                                  C.c_void_p(depth_ptr), DEPTH_F32, 0, ROW_MAJOR, ptr(cams), n_levels))
 
     def upload_device(self, ids, d_gray_ptr, d_depth_ptr, n, W, H, cams, n_levels):
         ids = np.ascontiguousarray(np.atleast_1d(ids), np.uint64)

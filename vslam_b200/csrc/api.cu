@@ -61,6 +61,10 @@ struct Arena
   size_t bytes = 0;
   int refs = 0;
   bool spare = false;  // no live frames; kept for the next upload of the same size (no cudaMalloc/cudaFree per batch)
+  // asynchronous upload: `ready` is recorded on the copy stream behind the copies and the preprocessing kernels;
+  // work that reads the frames waits for it on the compute stream
+  cudaEvent_t ready = nullptr;
+  bool pending = false;
 };
 
 struct FrameHost
@@ -91,6 +95,19 @@ struct vslamb200_ctx
   int traceJobs = 0, traceLevels = 0, traceMaxIter = 0;
   vslamb200_stats stats;
   cudaEvent_t ev[3] = {nullptr, nullptr, nullptr};
+  // asynchronous uploads: copies run on their own stream; the slot lists of the preprocessing launches live in a
+  // small ring of pinned buffers so that no launch needs a host synchronisation
+  cudaStream_t copyStream = nullptr;
+  cudaEvent_t copyDone = nullptr, computeMark = nullptr;
+  static constexpr int kSlotRing = 4;
+  int * hSlots[kSlotRing] = {nullptr, nullptr, nullptr, nullptr};
+  size_t hSlotsCap[kSlotRing] = {0, 0, 0, 0};
+  DevBuf dSlots[kSlotRing];
+  // pinned staging for the job / view tables of an alignment call (read by a copy kernel, see launch_stage_copy)
+  void * hStage = nullptr;
+  size_t hStageCap = 0;
+  cudaEvent_t slotsEv[kSlotRing] = {nullptr, nullptr, nullptr, nullptr};
+  unsigned slotsNext = 0;
 };
 
 namespace
@@ -149,6 +166,8 @@ void trim_spares(vslamb200_ctx * c, int keep)
   std::sort(sp.begin(), sp.end(), [&](int x, int y) { return c->arenas[x].bytes > c->arenas[y].bytes; });
   for (size_t k = keep; k < sp.size(); k++) {
     Arena & a = c->arenas[sp[k]];
+    if (a.pending) cudaEventSynchronize(a.ready);
+    if (a.ready) cudaEventDestroy(a.ready);
     cudaFree(a.ptr);
     a = Arena();
   }
@@ -231,6 +250,7 @@ int make_frames(vslamb200_ctx * c, int n, const uint64_t * ids, int W, int H, co
     }
   }
   Arena & a = c->arenas[arenaIdx];
+  if (a.pending) CK(cudaStreamWaitEvent(c->stream, a.ready, 0));  // a recycled arena whose asynchronous upload still runs
   a.spare = false;
   a.refs = n;
   trim_spares(c, 2);
@@ -260,28 +280,52 @@ int make_frames(vslamb200_ctx * c, int n, const uint64_t * ids, int W, int H, co
   return upload_table(c, slots);
 }
 
-// pyramid + gradients for uploaded level-0 planes
-int preprocess(vslamb200_ctx * c, const std::vector<int> & slots, int W, int H, int nLevels)
+// the compute stream waits for the asynchronous upload of the frame in `slot`, if one is still pending
+int wait_frame_ready(vslamb200_ctx * c, int slot)
+{
+  Arena & a = c->arenas[c->frames[slot].arena];
+  if (!a.pending) return 0;
+  if (cudaEventQuery(a.ready) == cudaSuccess) {
+    a.pending = false;
+    return 0;
+  }
+  cudaGetLastError();  // cudaErrorNotReady is not sticky, but clear it
+  CK(cudaStreamWaitEvent(c->stream, a.ready, 0));
+  return 0;
+}
+
+// pyramid + gradients for uploaded level-0 planes; queued on `stream`, host-synchronised only if asked
+int preprocess(vslamb200_ctx * c, const std::vector<int> & slots, int nLevels, bool sync, cudaStream_t stream)
 {
   const int n = (int)slots.size();
-  CK(c->slotsBuf.ensure(n * sizeof(int)));
-  CK(cudaMemcpyAsync(c->slotsBuf.p, slots.data(), n * sizeof(int), cudaMemcpyHostToDevice, c->stream));
+  const unsigned ring = c->slotsNext++ % vslamb200_ctx::kSlotRing;
+  CK(cudaEventSynchronize(c->slotsEv[ring]));  // the launches that last read this ring entry are done
+  if ((size_t)n > c->hSlotsCap[ring]) {
+    if (c->hSlots[ring]) cudaFreeHost(c->hSlots[ring]);
+    c->hSlots[ring] = nullptr;
+    c->hSlotsCap[ring] = 0;
+    CK(cudaHostAlloc((void **)&c->hSlots[ring], sizeof(int) * (size_t)n * 2, cudaHostAllocDefault));
+    c->hSlotsCap[ring] = (size_t)n * 2;
+  }
+  CK(c->dSlots[ring].ensure(n * sizeof(int)));
+  std::memcpy(c->hSlots[ring], slots.data(), n * sizeof(int));
+  CK(cudaMemcpyAsync(c->dSlots[ring].p, c->hSlots[ring], n * sizeof(int), cudaMemcpyHostToDevice, stream));
+  const int * dSlots = c->dSlots[ring].as<int>();
   const vb::FrameDev & f = c->frames[slots[0]].dev;
   const vb::FrameDev * table = c->dFrames.as<vb::FrameDev>();
   for (int l = 1; l < nLevels; l++) {
-    vb::launch_pyramid_level(table, c->slotsBuf.as<int>(), n, l, f.W[l], f.H[l], f.Wd[l], f.Hd[l], f.W[l - 1],
-                             f.H[l - 1], f.Wd[l - 1], f.Hd[l - 1], c->stream);
+    vb::launch_pyramid_level(table, dSlots, n, l, f.W[l], f.H[l], f.Wd[l], f.Hd[l], f.W[l - 1], f.H[l - 1], f.Wd[l - 1],
+                             f.Hd[l - 1], stream);
     c->stats.kernel_launches += 2;
   }
   for (int l = 0; l < nLevels; l++) {
-    vb::launch_gradients(table, c->slotsBuf.as<int>(), n, l, f.W[l], f.H[l], c->stream);
+    vb::launch_gradients(table, dSlots, n, l, f.W[l], f.H[l], stream);
     c->stats.kernel_launches += 1;
   }
   CK(cudaGetLastError());
-  CK(cudaStreamSynchronize(c->stream));  // slots vector / staging lifetimes
+  CK(cudaEventRecord(c->slotsEv[ring], stream));
+  if (sync) CK(cudaStreamSynchronize(stream));
   c->stats.frames_uploaded += n;
-  (void)W;
-  (void)H;
   return 0;
 }
 }  // namespace
@@ -328,6 +372,15 @@ int vslamb200_create(const vslamb200_config * cfg, int device, vslamb200_ctx ** 
     return fail(VSLAMB200_ECUDA, "context resources could not be created");
   }
   c->stream = c->own;
+  bool ok = cudaStreamCreateWithFlags(&c->copyStream, cudaStreamNonBlocking) == cudaSuccess;
+  ok = ok && cudaEventCreateWithFlags(&c->copyDone, cudaEventDisableTiming) == cudaSuccess;
+  ok = ok && cudaEventCreateWithFlags(&c->computeMark, cudaEventDisableTiming) == cudaSuccess;
+  for (int i = 0; i < vslamb200_ctx::kSlotRing; i++)
+    ok = ok && cudaEventCreateWithFlags(&c->slotsEv[i], cudaEventDisableTiming) == cudaSuccess;
+  if (!ok) {
+    vslamb200_destroy(c);
+    return fail(VSLAMB200_ECUDA, "context resources could not be created");
+  }
   *out = c;
   return 0;
 }
@@ -337,11 +390,26 @@ void vslamb200_destroy(vslamb200_ctx * c)
   if (!c) return;
   cudaSetDevice(c->device);
   cudaStreamSynchronize(c->stream);
-  for (auto & a : c->arenas)
+  if (c->copyStream) cudaStreamSynchronize(c->copyStream);
+  for (auto & a : c->arenas) {
+    if (a.ready) cudaEventDestroy(a.ready);
     if (a.ptr) cudaFree(a.ptr);
+  }
   DevBuf * bufs[] = {&c->dFrames, &c->stageGray, &c->stageDepth, &c->slotsBuf, &c->jobs, &c->views,
                      &c->chunkCounts, &c->partials, &c->lists, &c->trace, &c->plane};
   for (auto b : bufs) b->release();
+  if (c->copyStream) {
+    cudaStreamSynchronize(c->copyStream);
+    cudaStreamDestroy(c->copyStream);
+  }
+  if (c->copyDone) cudaEventDestroy(c->copyDone);
+  if (c->computeMark) cudaEventDestroy(c->computeMark);
+  for (int i = 0; i < vslamb200_ctx::kSlotRing; i++) {
+    if (c->slotsEv[i]) cudaEventDestroy(c->slotsEv[i]);
+    if (c->hSlots[i]) cudaFreeHost(c->hSlots[i]);
+    if (i == 0 && c->hStage) cudaFreeHost(c->hStage);
+    c->dSlots[i].release();
+  }
   if (c->ev[0]) cudaEventDestroy(c->ev[0]);
   if (c->ev[1]) cudaEventDestroy(c->ev[1]);
   if (c->ev[2]) cudaEventDestroy(c->ev[2]);
@@ -369,6 +437,7 @@ int vslamb200_synchronize(vslamb200_ctx * c)
 {
   if (!c) return fail(VSLAMB200_EINVAL, "ctx is null");
   CK(cudaSetDevice(c->device));
+  CK(cudaStreamSynchronize(c->copyStream));
   CK(cudaStreamSynchronize(c->stream));
   return 0;
 }
@@ -414,7 +483,38 @@ int vslamb200_frames_upload(
     }
   }
   c->stats.h2d_bytes += (uint64_t)n * npx * (1 + dsz);
-  return preprocess(c, slots, W, H, nLevels);
+  return preprocess(c, slots, nLevels, true, c->stream);
+}
+
+int vslamb200_frames_upload_async(
+  vslamb200_ctx * c, int n, const uint64_t * ids, int W, int H, const uint8_t * gray, size_t grayStride,
+  const void * depth, int depthType, size_t depthStride, int layout, const double * cams, int nLevels)
+{
+  if (!c || !gray || !depth) return fail(VSLAMB200_EINVAL, "frames_upload_async: null argument");
+  if (layout != VSLAMB200_ROW_MAJOR || depthType != VSLAMB200_DEPTH_F32)  // the transposing ingest path stages: synchronous
+    return vslamb200_frames_upload(c, n, ids, W, H, gray, grayStride, depth, depthType, depthStride, layout, cams, nLevels);
+  CK(cudaSetDevice(c->device));
+  std::vector<int> slots;
+  if (int e = make_frames(c, n, ids, W, H, cams, nLevels, slots)) return e;
+  const size_t npx = (size_t)W * H;
+  if (!grayStride) grayStride = npx;
+  if (!depthStride) depthStride = npx * 4;
+  const vb::FrameDev & f0 = c->frames[slots[0]].dev;
+  const size_t frameStride = n > 1 ? (size_t)((uint8_t *)c->frames[slots[1]].dev.I[0] - (uint8_t *)f0.I[0]) : npx;
+  // the copy may land in a recycled arena: order it after the compute work issued so far, not after what follows
+  CK(cudaEventRecord(c->computeMark, c->stream));
+  CK(cudaStreamWaitEvent(c->copyStream, c->computeMark, 0));
+  CK(cudaMemcpy2DAsync(f0.I[0], frameStride, gray, grayStride, npx, n, cudaMemcpyHostToDevice, c->copyStream));
+  CK(cudaMemcpy2DAsync(f0.Z[0], frameStride, depth, depthStride, npx * 4, n, cudaMemcpyHostToDevice, c->copyStream));
+  c->stats.h2d_bytes += (uint64_t)n * npx * 5;
+  // pyramids and gradients follow the copies on the copy stream, so the compute stream is not held up by an upload
+  // it does not depend on; whoever reads these frames first waits for the arena's event
+  if (int e = preprocess(c, slots, nLevels, false, c->copyStream)) return e;
+  Arena & a = c->arenas[c->frames[slots[0]].arena];
+  if (!a.ready) CK(cudaEventCreateWithFlags(&a.ready, cudaEventDisableTiming));
+  CK(cudaEventRecord(a.ready, c->copyStream));
+  a.pending = true;
+  return 0;
 }
 
 int vslamb200_frames_upload_device(
@@ -430,7 +530,7 @@ int vslamb200_frames_upload_device(
   const size_t frameStride = n > 1 ? (size_t)((uint8_t *)c->frames[slots[1]].dev.I[0] - (uint8_t *)f0.I[0]) : npx;
   CK(cudaMemcpy2DAsync(f0.I[0], frameStride, dGray, npx, npx, n, cudaMemcpyDeviceToDevice, c->stream));
   CK(cudaMemcpy2DAsync(f0.Z[0], frameStride, dDepth, npx * 4, npx * 4, n, cudaMemcpyDeviceToDevice, c->stream));
-  return preprocess(c, slots, W, H, nLevels);
+  return preprocess(c, slots, nLevels, true, c->stream);
 }
 
 int vslamb200_frame_release(vslamb200_ctx * c, uint64_t id)
@@ -439,6 +539,7 @@ int vslamb200_frame_release(vslamb200_ctx * c, uint64_t id)
   auto it = c->idToSlot.find(id);
   if (it == c->idToSlot.end()) return fail(VSLAMB200_ENOFRAME, "frame_release: unknown frame id");
   CK(cudaSetDevice(c->device));
+  CK(cudaStreamSynchronize(c->copyStream));
   CK(cudaStreamSynchronize(c->stream));
   return release_slot(c, it->second);
 }
@@ -447,6 +548,7 @@ int vslamb200_frame_release_all(vslamb200_ctx * c)
 {
   if (!c) return fail(VSLAMB200_EINVAL, "ctx is null");
   CK(cudaSetDevice(c->device));
+  CK(cudaStreamSynchronize(c->copyStream));
   CK(cudaStreamSynchronize(c->stream));
   for (size_t i = 0; i < c->frames.size(); i++) release_slot(c, (int)i);
   trim_spares(c, 0);
@@ -476,6 +578,7 @@ int vslamb200_frame_download(
   const vb::FrameDev & f = c->frames[it->second].dev;
   if (level < 0 || level >= f.nLevels) return fail(VSLAMB200_EINVAL, "frame_download: no such level");
   CK(cudaSetDevice(c->device));
+  if (int e = wait_frame_ready(c, it->second)) return e;
   const size_t n = (size_t)f.W[level] * f.H[level], nd = (size_t)f.Wd[level] * f.Hd[level];
   if (I) CK(cudaMemcpyAsync(I, f.I[level], n, cudaMemcpyDeviceToHost, c->stream));
   if (Z) CK(cudaMemcpyAsync(Z, f.Z[level], nd * 4, cudaMemcpyDeviceToHost, c->stream));
@@ -546,9 +649,11 @@ int build_problem(vslamb200_ctx * c, const vslamb200_job * jobs, int nJobs, Prob
     J.pose = J.toPose;
     for (int i = 0; i < 36; i++) J.cov[i] = (i % 7 == 0) ? 1.0 : 0.0;
     const vb::FrameDev & ft = c->frames[itTo->second].dev;
+    if (int e = wait_frame_ready(c, itTo->second)) return e;
     for (int k = 0; k < in.n_from; k++) {
       auto itF = c->idToSlot.find(in.from[k]);
       if (itF == c->idToSlot.end()) return fail(VSLAMB200_ENOFRAME, "align: unknown keyframe id");
+      if (int e = wait_frame_ready(c, itF->second)) return e;
       const vb::FrameDev & ff = c->frames[itF->second].dev;
       if (first) {
         P.geo = ff;
@@ -649,8 +754,23 @@ int prepare_workspace(vslamb200_ctx * c, Problem & P, const vb::SolverParams & s
   }
   CK(c->jobs.ensure(nJobs * sizeof(vb::JobState)));
   CK(c->views.ensure(nViews * sizeof(vb::ViewState)));
-  CK(cudaMemcpyAsync(c->jobs.p, P.jobs.data(), nJobs * sizeof(vb::JobState), cudaMemcpyHostToDevice, c->stream));
-  CK(cudaMemcpyAsync(c->views.p, P.views.data(), nViews * sizeof(vb::ViewState), cudaMemcpyHostToDevice, c->stream));
+  {
+    // every alignment call ends with a stream synchronisation, so the staging buffer is free here
+    const size_t jb = align_up(nJobs * sizeof(vb::JobState), 256), vbytes = nViews * sizeof(vb::ViewState);
+    if (jb + vbytes > c->hStageCap) {
+      if (c->hStage) cudaFreeHost(c->hStage);
+      c->hStage = nullptr;
+      c->hStageCap = 0;
+      const size_t want = (jb + vbytes) * 3 / 2 + 4096;
+      CK(cudaHostAlloc(&c->hStage, want, cudaHostAllocMapped | cudaHostAllocPortable));
+      c->hStageCap = want;
+    }
+    std::memcpy(c->hStage, P.jobs.data(), nJobs * sizeof(vb::JobState));
+    std::memcpy((uint8_t *)c->hStage + jb, P.views.data(), vbytes);
+    vb::launch_stage_copy(c->jobs.p, c->hStage, nJobs * sizeof(vb::JobState), c->stream);
+    vb::launch_stage_copy(c->views.p, (uint8_t *)c->hStage + jb, vbytes, c->stream);
+    c->stats.kernel_launches += 2;
+  }
   if (c->traceEnabled) {
     const size_t bytes = (size_t)nJobs * P.nLevels * sp.maxIterations * vb::TRACE_STRIDE * sizeof(double);
     CK(c->trace.ensure(bytes));

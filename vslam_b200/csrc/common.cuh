@@ -258,6 +258,7 @@ int list_chunks_for(int pixels);
 void launch_level_setup(const FrameDev * frames, JobState * jobs, ViewState * views, int nViews, int level,
                         cudaStream_t s);
 void launch_level_begin(JobState * jobs, ViewState * views, int nJobs, int level, cudaStream_t s);
+void launch_stage_copy(void * dst, const void * srcPinned, size_t bytes, cudaStream_t s);
 void launch_scatter_rcode(const ViewState * views, int view, int16_t * plane, cudaStream_t s);
 // gn_level.cu
 size_t gn_level_static_smem();

@@ -90,6 +90,21 @@ void launch_level_begin(JobState * jobs, ViewState * views, int nJobs, int level
   level_begin_kernel<<<(nJobs + 127) / 128, 128, 0, s>>>(jobs, views, nJobs, level);
 }
 
+// Host -> device hand-over of small control structures without the DMA engine: the source is pinned, mapped host
+// memory and the SMs read it over PCIe.  (A cudaMemcpyAsync would queue behind a large frame upload that is in flight
+// on the host-to-device copy engine and serialise the alignment with it.)
+__global__ void stage_copy_kernel(uint32_t * __restrict__ dst, const uint32_t * __restrict__ src, size_t words)
+{
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < words; i += (size_t)gridDim.x * blockDim.x)
+    dst[i] = src[i];
+}
+void launch_stage_copy(void * dst, const void * srcPinned, size_t bytes, cudaStream_t s)
+{
+  const size_t words = (bytes + 3) / 4;
+  const int blocks = (int)std::min<size_t>(296, (words + 255) / 256);
+  if (words) stage_copy_kernel<<<blocks, 256, 0, s>>>((uint32_t *)dst, (const uint32_t *)srcPinned, words);
+}
+
 // parity helper: residual codes of one view scattered back to a W*H plane
 __global__ void scatter_rcode_kernel(const ViewState * __restrict__ views, int view, int16_t * __restrict__ plane)
 {
