@@ -306,6 +306,11 @@ def main():
         from oracle import oracle as O
         perr = max(np.linalg.norm(O.se3_log(O.se3_mul(np.array(results[i].pose), O.se3_inv(cposes[i]))))
                    for i in range(args.cpu_pairs))
+        # spot checks across the whole batch (middle and last pair) against the oracle, and every job must have iterated
+        for m in ((F - 1) // 2, F - 2):
+            pm, _ = O.baseline_sequence(O.make_config(), gray[m:m + 2], depth[m:m + 2], *cam, LEVELS, 1)
+            perr = max(perr, np.linalg.norm(O.se3_log(O.se3_mul(np.array(results[m].pose), O.se3_inv(pm[0])))))
+        assert all(r.status == 0 and sum(r.iters[:LEVELS]) > 0 for r in results), "a job did not run"
         cpu = {"value": v1, "unit": "pairs/s", "cores": 1, "kind": "port",
                "sample": f"first {args.cpu_pairs} pairs of the sequence, frame preparation included ({dt1:.1f} s)",
                "all_cores": {"value": vN, "cores": thr, "pairs": max(args.cpu_pairs, thr)},

@@ -266,3 +266,37 @@ def test_async_upload_pipeline_is_identical_to_the_synchronous_path(capi, oracle
         ctx.synchronize()
     finally:
         ctx.close()
+
+
+@pytest.mark.gpu
+def test_large_batch_two_stream_path_matches_oracle(capi, oracle, synth):
+    """Batches of >= 192 jobs are cut into two halves that run on two streams (vslamb200_align); every pair of a
+    200-frame sequence must still match the oracle (pose, and bit-identical to the single-stream run)."""
+    import os
+    F, W, H, L = 200, 160, 120, 3
+    cam = synth.cam_for(W, H)
+    gray, depth, _ = synth.make_sequence(F, W, H, seed=5, cam=cam)
+    ident = oracle.IDENTITY
+    jobs = [dict(to=i + 1, to_pose=ident, frm=[i], from_poses=ident, multi=False) for i in range(F - 1)]
+    ref_poses, _ = oracle.baseline_sequence(oracle.make_config(), gray, depth, *cam, L, os.cpu_count() or 1)
+    got = {}
+    for parts in ("1", "2", "5"):
+        os.environ["VSLAMB200_PARTS"] = parts
+        try:
+            ctx = capi.Context(capi.make_config())
+            ctx.upload(np.arange(F), gray, depth, cam, L)
+            got[parts] = ctx.align(jobs)
+            ctx.close()
+        finally:
+            del os.environ["VSLAMB200_PARTS"]
+    ctx = capi.Context(capi.make_config())  # default policy: two halves for this batch size
+    ctx.upload(np.arange(F), gray, depth, cam, L)
+    got["default"] = ctx.align(jobs)
+    ctx.close()
+    for k in range(F - 1):
+        assert got["1"][k]["status"] == 0 and sum(got["1"][k]["iters"][:L]) > 0, k
+        dt, dr = pose_err(oracle, got["1"][k]["pose"], ref_poses[k])
+        assert dt < POSE_TOL and dr < POSE_TOL, k
+        for key in ("2", "5", "default"):
+            assert np.array_equal(got[key][k]["pose"], got["1"][k]["pose"]), (key, k)
+            assert list(got[key][k]["iters"]) == list(got["1"][k]["iters"]), (key, k)

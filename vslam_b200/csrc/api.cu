@@ -76,6 +76,7 @@ struct FrameHost
 };
 
 size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+constexpr int kMinJobsPerPart = 96;  // below this a half batch no longer fills the GPU
 }  // namespace
 
 struct vslamb200_ctx
@@ -106,6 +107,10 @@ struct vslamb200_ctx
   // pinned staging for the job / view tables of an alignment call (read by a copy kernel, see launch_stage_copy)
   void * hStage = nullptr;
   size_t hStageCap = 0;
+  // large batches run as two halves on two streams (see vslamb200_align)
+  static constexpr int kMaxParts = 8;
+  cudaStream_t part[kMaxParts] = {};
+  cudaEvent_t forkEv = nullptr, joinEv[kMaxParts] = {};
   cudaEvent_t slotsEv[kSlotRing] = {nullptr, nullptr, nullptr, nullptr};
   unsigned slotsNext = 0;
 };
@@ -377,6 +382,11 @@ int vslamb200_create(const vslamb200_config * cfg, int device, vslamb200_ctx ** 
   ok = ok && cudaEventCreateWithFlags(&c->computeMark, cudaEventDisableTiming) == cudaSuccess;
   for (int i = 0; i < vslamb200_ctx::kSlotRing; i++)
     ok = ok && cudaEventCreateWithFlags(&c->slotsEv[i], cudaEventDisableTiming) == cudaSuccess;
+  ok = ok && cudaEventCreateWithFlags(&c->forkEv, cudaEventDisableTiming) == cudaSuccess;
+  for (int q = 0; q < vslamb200_ctx::kMaxParts; q++) {
+    ok = ok && cudaStreamCreateWithFlags(&c->part[q], cudaStreamNonBlocking) == cudaSuccess;
+    ok = ok && cudaEventCreateWithFlags(&c->joinEv[q], cudaEventDisableTiming) == cudaSuccess;
+  }
   if (!ok) {
     vslamb200_destroy(c);
     return fail(VSLAMB200_ECUDA, "context resources could not be created");
@@ -403,6 +413,11 @@ void vslamb200_destroy(vslamb200_ctx * c)
     cudaStreamDestroy(c->copyStream);
   }
   if (c->copyDone) cudaEventDestroy(c->copyDone);
+  if (c->forkEv) cudaEventDestroy(c->forkEv);
+  for (int q = 0; q < vslamb200_ctx::kMaxParts; q++) {
+    if (c->part[q]) cudaStreamDestroy(c->part[q]);
+    if (c->joinEv[q]) cudaEventDestroy(c->joinEv[q]);
+  }
   if (c->computeMark) cudaEventDestroy(c->computeMark);
   for (int i = 0; i < vslamb200_ctx::kSlotRing; i++) {
     if (c->slotsEv[i]) cudaEventDestroy(c->slotsEv[i]);
@@ -701,9 +716,13 @@ int pick_cluster(int npx, int maxViewsPerJob)
   return 1;
 }
 
-int run_level(vslamb200_ctx * c, Problem & P, int level, const vb::SolverParams & sp, int maxEvals)
+// One pyramid level for the jobs [job0, job0 + nJobs) (their views are contiguous: [view0, view0 + nViews)), queued on
+// `stream`.
+int run_level(vslamb200_ctx * c, Problem & P, int level, const vb::SolverParams & sp, int maxEvals, int job0, int nJobs,
+              cudaStream_t stream)
 {
-  const int nJobs = (int)P.jobs.size(), nViews = (int)P.views.size();
+  const int view0 = P.jobs[job0].view0;
+  const int nViews = (job0 + nJobs < (int)P.jobs.size() ? P.jobs[job0 + nJobs].view0 : (int)P.views.size()) - view0;
   const int npx = P.geo.W[level] * P.geo.H[level];
   const int listChunks = vb::list_chunks_for(npx);
   vb::JobState * dJobs = c->jobs.as<vb::JobState>();
@@ -713,19 +732,19 @@ int run_level(vslamb200_ctx * c, Problem & P, int level, const vb::SolverParams 
   const size_t traceJobStride = (size_t)P.nLevels * sp.maxIterations * vb::TRACE_STRIDE;
   const int cluster = pick_cluster(npx, 1);
 
-  if (c->timing) CK(cudaEventRecord(c->ev[0], c->stream));
-  vb::launch_level_setup(table, dJobs, dViews, nViews, level, c->stream);
-  vb::launch_build_lists(table, dViews, dJobs, nViews, level, npx, sp.minGradient2, c->chunkCounts.as<int>(), listChunks,
-                         c->stream);
-  vb::launch_level_begin(dJobs, dViews, nJobs, level, c->stream);
-  if (c->timing) CK(cudaEventRecord(c->ev[1], c->stream));
-  CK(vb::launch_gn_level(dJobs, dViews, nJobs, P.maxViews, cluster, sp, level, maxEvals, dTrace,
-                         traceJobStride, c->partials.as<double>(), c->stream));
-  if (c->timing) CK(cudaEventRecord(c->ev[2], c->stream));
+  if (c->timing) CK(cudaEventRecord(c->ev[0], stream));
+  vb::launch_level_setup(table, dJobs, dViews, view0, nViews, level, stream);
+  vb::launch_build_lists(table, dViews, dJobs, view0, nViews, level, npx, sp.minGradient2, c->chunkCounts.as<int>(),
+                         listChunks, stream);
+  vb::launch_level_begin(dJobs, dViews, job0, nJobs, level, stream);
+  if (c->timing) CK(cudaEventRecord(c->ev[1], stream));
+  CK(vb::launch_gn_level(dJobs, dViews, job0, nJobs, P.maxViews, cluster, sp, level, maxEvals, dTrace, traceJobStride,
+                         c->partials.as<double>(), stream));
+  if (c->timing) CK(cudaEventRecord(c->ev[2], stream));
   c->stats.kernel_launches += 6;
   CK(cudaGetLastError());
   if (c->timing) {
-    CK(cudaStreamSynchronize(c->stream));
+    CK(cudaStreamSynchronize(stream));
     float a = 0, b = 0;
     CK(cudaEventElapsedTime(&a, c->ev[0], c->ev[1]));
     CK(cudaEventElapsedTime(&b, c->ev[1], c->ev[2]));
@@ -793,8 +812,28 @@ int vslamb200_align(vslamb200_ctx * c, const vslamb200_job * jobs, int nJobs, vs
   if (int e = build_problem(c, jobs, nJobs, P)) return e;
   const vb::SolverParams sp = solver_params(c->cfg);
   if (int e = prepare_workspace(c, P, sp)) return e;
-  for (int level = P.nLevels - 1; level >= 0; level--)
-    if (int e = run_level(c, P, level, sp, sp.maxIterations + 1)) return e;
+  // Jobs stop after different numbers of iterations, so every level kernel ends with a tail of a few long-running
+  // clusters.  A large batch is therefore cut into two halves that walk down the pyramid on their own streams: one
+  // half's tail is filled by the other half's next kernel.  (Timing mode keeps one stream: it measures whole launches.)
+  int nParts = (!c->timing && nJobs >= 2 * kMinJobsPerPart) ? 2 : 1;
+  if (const char * e = std::getenv("VSLAMB200_PARTS")) nParts = std::max(1, std::min(vslamb200_ctx::kMaxParts, std::atoi(e)));
+  nParts = std::min(nParts, nJobs);
+  if (nParts == 1) {
+    for (int level = P.nLevels - 1; level >= 0; level--)
+      if (int e = run_level(c, P, level, sp, sp.maxIterations + 1, 0, nJobs, c->stream)) return e;
+  } else {
+    CK(cudaEventRecord(c->forkEv, c->stream));
+    int cut[vslamb200_ctx::kMaxParts + 1];
+    for (int q = 0; q <= nParts; q++) cut[q] = (int)((long long)nJobs * q / nParts);
+    for (int q = 0; q < nParts; q++) CK(cudaStreamWaitEvent(c->part[q], c->forkEv, 0));
+    for (int level = P.nLevels - 1; level >= 0; level--)
+      for (int q = 0; q < nParts; q++)
+        if (int e = run_level(c, P, level, sp, sp.maxIterations + 1, cut[q], cut[q + 1] - cut[q], c->part[q])) return e;
+    for (int q = 0; q < nParts; q++) {
+      CK(cudaEventRecord(c->joinEv[q], c->part[q]));
+      CK(cudaStreamWaitEvent(c->stream, c->joinEv[q], 0));
+    }
+  }
   CK(cudaMemcpyAsync(P.jobs.data(), c->jobs.p, nJobs * sizeof(vb::JobState), cudaMemcpyDeviceToHost, c->stream));
   CK(cudaStreamSynchronize(c->stream));
   c->stats.d2h_bytes += (uint64_t)nJobs * sizeof(vb::JobState);
@@ -868,10 +907,10 @@ int vslamb200_evaluate(
   vb::JobState * dJobs = c->jobs.as<vb::JobState>();
   vb::ViewState * dViews = c->views.as<vb::ViewState>();
   const vb::FrameDev * table = c->dFrames.as<vb::FrameDev>();
-  vb::launch_level_setup(table, dJobs, dViews, nViews, level, c->stream);
-  vb::launch_build_lists(table, dViews, dJobs, nViews, level, npx, sp.minGradient2, c->chunkCounts.as<int>(),
+  vb::launch_level_setup(table, dJobs, dViews, 0, nViews, level, c->stream);
+  vb::launch_build_lists(table, dViews, dJobs, 0, nViews, level, npx, sp.minGradient2, c->chunkCounts.as<int>(),
                          vb::list_chunks_for(npx), c->stream);
-  vb::launch_level_begin(dJobs, dViews, nJobs, level, c->stream);
+  vb::launch_level_begin(dJobs, dViews, 0, nJobs, level, c->stream);
   vb::ViewState V;
   CK(cudaMemcpyAsync(&V, dViews, sizeof(V), cudaMemcpyDeviceToHost, c->stream));
   CK(cudaStreamSynchronize(c->stream));
@@ -881,7 +920,7 @@ int vslamb200_evaluate(
   CK(cudaMemcpyAsync(dViews, &V, sizeof(V), cudaMemcpyHostToDevice, c->stream));
   CK(cudaMemsetAsync(c->partials.p, 0, vb::NE_TERMS * sizeof(double), c->stream));
   const int cluster = pick_cluster(npx, 1);
-  CK(vb::launch_gn_level(dJobs, dViews, nJobs, 1, cluster, sp, level, 1, nullptr, 0, c->partials.as<double>(), c->stream));
+  CK(vb::launch_gn_level(dJobs, dViews, 0, nJobs, 1, cluster, sp, level, 1, nullptr, 0, c->partials.as<double>(), c->stream));
   c->stats.kernel_launches += 6;
   if (rcode) {
     CK(c->plane.ensure((size_t)npx * 2));

@@ -251,17 +251,17 @@ void launch_pyramid_level(const FrameDev * frames, const int * slots, int n, int
                           int Wp, int Hp, int Wdp, int Hdp, cudaStream_t s);
 void launch_gradients(const FrameDev * frames, const int * slots, int n, int level, int W, int H, cudaStream_t s);
 // lists.cu
-void launch_build_lists(const FrameDev * frames, ViewState * views, const JobState * jobs, int nViews, int level,
+void launch_build_lists(const FrameDev * frames, ViewState * views, const JobState * jobs, int view0, int nViews, int level,
                         int maxPixels, double minGradient2, int * chunkCounts, int maxChunksPerView, cudaStream_t s);
 int list_chunks_for(int pixels);
 // level_misc.cu
-void launch_level_setup(const FrameDev * frames, JobState * jobs, ViewState * views, int nViews, int level,
+void launch_level_setup(const FrameDev * frames, JobState * jobs, ViewState * views, int view0, int nViews, int level,
                         cudaStream_t s);
-void launch_level_begin(JobState * jobs, ViewState * views, int nJobs, int level, cudaStream_t s);
+void launch_level_begin(JobState * jobs, ViewState * views, int job0, int nJobs, int level, cudaStream_t s);
 void launch_stage_copy(void * dst, const void * srcPinned, size_t bytes, cudaStream_t s);
 void launch_scatter_rcode(const ViewState * views, int view, int16_t * plane, cudaStream_t s);
 // gn_level.cu
 size_t gn_level_static_smem();
-cudaError_t launch_gn_level(JobState * jobs, ViewState * views, int nJobs, int maxViewsPerJob, int clusterSize,
+cudaError_t launch_gn_level(JobState * jobs, ViewState * views, int job0, int nJobs, int maxViewsPerJob, int clusterSize,
                             SolverParams p, int level, int maxEvals, double * trace, size_t traceJobStride, double * viewSums, cudaStream_t s);
 }  // namespace vb

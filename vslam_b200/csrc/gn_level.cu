@@ -454,11 +454,11 @@ __device__ __forceinline__ void issue_chunk(
 
 __global__ void __launch_bounds__(GT, CTAS_PER_SM) gn_level_kernel(
   JobState * __restrict__ jobs, ViewState * __restrict__ views, SolverParams p, int level, int maxEvals,
-  double * __restrict__ trace, size_t traceJobStride, double * __restrict__ viewSums)
+  double * __restrict__ trace, size_t traceJobStride, double * __restrict__ viewSums, int job0)
 {
   cg::cluster_group cluster = cg::this_cluster();
   const unsigned C = cluster.num_blocks(), rank = cluster.block_rank();
-  const int job = blockIdx.x / C;
+  const int job = job0 + blockIdx.x / C;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   __shared__ LevelShared S;
   extern __shared__ __align__(128) unsigned char ring[];
@@ -787,7 +787,7 @@ __global__ void __launch_bounds__(GT, CTAS_PER_SM) gn_level_kernel(
 size_t gn_level_static_smem() { return sizeof(LevelShared); }
 
 cudaError_t launch_gn_level(
-  JobState * jobs, ViewState * views, int nJobs, int maxViewsPerJob, int clusterSize, SolverParams p, int level,
+  JobState * jobs, ViewState * views, int job0, int nJobs, int maxViewsPerJob, int clusterSize, SolverParams p, int level,
   int maxEvals, double * trace, size_t traceJobStride, double * viewSums, cudaStream_t s)
 {
   if (nJobs <= 0) return cudaSuccess;
@@ -806,6 +806,6 @@ cudaError_t launch_gn_level(
   at[0].val.clusterDim.z = 1;
   cfg.attrs = at;
   cfg.numAttrs = 1;
-  return cudaLaunchKernelEx(&cfg, gn_level_kernel, jobs, views, p, level, maxEvals, trace, traceJobStride, viewSums);
+  return cudaLaunchKernelEx(&cfg, gn_level_kernel, jobs, views, p, level, maxEvals, trace, traceJobStride, viewSums, job0);
 }
 }  // namespace vb

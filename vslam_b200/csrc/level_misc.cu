@@ -14,12 +14,12 @@ __device__ inline void split_hi_lo(double v, float & hi, float & lo)
 
 // one thread per view: static fields of the level, warp = pose * poseRef^-1 (Warp.cpp:135-147), prior
 __global__ void level_setup_kernel(
-  const FrameDev * __restrict__ frames, JobState * __restrict__ jobs, ViewState * __restrict__ views, int nViews,
-  int level)
+  const FrameDev * __restrict__ frames, JobState * __restrict__ jobs, ViewState * __restrict__ views, int view0,
+  int nViews, int level)
 {
   const int vi = blockIdx.x * blockDim.x + threadIdx.x;
   if (vi >= nViews) return;
-  ViewState & V = views[vi];
+  ViewState & V = views[view0 + vi];
   JobState & J = jobs[V.job];
   const FrameDev & ff = frames[V.fromSlot];
   const FrameDev & ft = frames[V.toSlot];
@@ -53,7 +53,7 @@ __global__ void level_setup_kernel(
   view_set_warp(V);
   view_set_x(V);
   se3_log(se3_mul(J.toPose, se3_inv(V.poseRef)), V.xPred);  // MotionPrior ctor (SE3Alignment.cpp:32)
-  if (vi == J.view0) {
+  if (view0 + vi == J.view0) {
     J.iter = 0;
     J.nPushed = 0;
     J.chi2Prev = 0.0;
@@ -66,11 +66,12 @@ __global__ void level_setup_kernel(
 
 // one thread per job, after the lists are built: total chunk count; a job without a single interest
 // point ends the level at once (NormalEquations all zero, n = 0 < 6: GaussNewton.cpp:53-58)
-__global__ void level_begin_kernel(JobState * __restrict__ jobs, ViewState * __restrict__ views, int nJobs, int level)
+__global__ void level_begin_kernel(
+  JobState * __restrict__ jobs, ViewState * __restrict__ views, int job0, int nJobs, int level)
 {
   const int j = blockIdx.x * blockDim.x + threadIdx.x;
   if (j >= nJobs) return;
-  JobState & J = jobs[j];
+  JobState & J = jobs[job0 + j];
   int tot = 0;
   for (int k = 0; k < J.nViews; k++) tot += views[J.view0 + k].nIp;
   J.totalPoints = tot;
@@ -80,14 +81,14 @@ __global__ void level_begin_kernel(JobState * __restrict__ jobs, ViewState * __r
   }
 }
 
-void launch_level_setup(const FrameDev * frames, JobState * jobs, ViewState * views, int nViews, int level,
+void launch_level_setup(const FrameDev * frames, JobState * jobs, ViewState * views, int view0, int nViews, int level,
                         cudaStream_t s)
 {
-  level_setup_kernel<<<(nViews + 127) / 128, 128, 0, s>>>(frames, jobs, views, nViews, level);
+  level_setup_kernel<<<(nViews + 127) / 128, 128, 0, s>>>(frames, jobs, views, view0, nViews, level);
 }
-void launch_level_begin(JobState * jobs, ViewState * views, int nJobs, int level, cudaStream_t s)
+void launch_level_begin(JobState * jobs, ViewState * views, int job0, int nJobs, int level, cudaStream_t s)
 {
-  level_begin_kernel<<<(nJobs + 127) / 128, 128, 0, s>>>(jobs, views, nJobs, level);
+  level_begin_kernel<<<(nJobs + 127) / 128, 128, 0, s>>>(jobs, views, job0, nJobs, level);
 }
 
 // Host -> device hand-over of small control structures without the DMA engine: the source is pinned, mapped host

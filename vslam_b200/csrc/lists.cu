@@ -23,9 +23,10 @@ __device__ __forceinline__ bool is_interest(
 
 __global__ void __launch_bounds__(LTHREADS) list_count_kernel(
   const FrameDev * __restrict__ frames, const ViewState * __restrict__ views, const JobState * __restrict__ jobs,
-  int level, double minGradient2, int * __restrict__ chunkCounts, int maxChunks)
+  int level, double minGradient2, int * __restrict__ chunkCounts, int maxChunks, int view0)
 {
-  const ViewState & V = views[blockIdx.y];
+  const int vi = view0 + blockIdx.y;
+  const ViewState & V = views[vi];
   const int npx = V.W * V.H;
   const int base = blockIdx.x * LCHUNK;
   if (base >= npx) return;
@@ -46,18 +47,19 @@ __global__ void __launch_bounds__(LTHREADS) list_count_kernel(
   if (threadIdx.x == 0) {
     int s = 0;
     for (int w = 0; w < LTHREADS / 32; w++) s += wsum[w];
-    chunkCounts[blockIdx.y * maxChunks + blockIdx.x] = s;
+    chunkCounts[vi * maxChunks + blockIdx.x] = s;
   }
 }
 
 // one block per view: exclusive scan of the chunk counts (in place), nIp and nChunks of the view
 __global__ void __launch_bounds__(256) list_scan_kernel(
-  ViewState * __restrict__ views, int * __restrict__ chunkCounts, int maxChunks)
+  ViewState * __restrict__ views, int * __restrict__ chunkCounts, int maxChunks, int view0)
 {
-  ViewState & V = views[blockIdx.x];
+  const int vi = view0 + blockIdx.x;
+  ViewState & V = views[vi];
   const int npx = V.W * V.H;
   const int n = (npx + LCHUNK - 1) / LCHUNK;
-  int * c = chunkCounts + blockIdx.x * maxChunks;
+  int * c = chunkCounts + vi * maxChunks;
   __shared__ int carry;
   __shared__ int wsum[8];
   if (threadIdx.x == 0) carry = 0;
@@ -86,9 +88,10 @@ __global__ void __launch_bounds__(256) list_scan_kernel(
 
 __global__ void __launch_bounds__(LTHREADS) list_write_kernel(
   const FrameDev * __restrict__ frames, const ViewState * __restrict__ views, const JobState * __restrict__ jobs,
-  int level, double minGradient2, const int * __restrict__ chunkOffsets, int maxChunks)
+  int level, double minGradient2, const int * __restrict__ chunkOffsets, int maxChunks, int view0)
 {
-  const ViewState & V = views[blockIdx.y];
+  const int vi = view0 + blockIdx.y;
+  const ViewState & V = views[vi];
   const int npx = V.W * V.H;
   const int base = blockIdx.x * LCHUNK;
   if (base >= npx) return;
@@ -96,7 +99,7 @@ __global__ void __launch_bounds__(LTHREADS) list_write_kernel(
   const int multi = jobs[V.job].multi;
   const int W = V.W;
   __shared__ int wsum[LTHREADS / 32];
-  int running = chunkOffsets[blockIdx.y * maxChunks + blockIdx.x];
+  int running = chunkOffsets[vi * maxChunks + blockIdx.x];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   for (int k = 0; k < LPER; k++) {
     const int i = base + k * LTHREADS + threadIdx.x;
@@ -128,13 +131,13 @@ __global__ void __launch_bounds__(LTHREADS) list_write_kernel(
   }
 }
 
-void launch_build_lists(const FrameDev * frames, ViewState * views, const JobState * jobs, int nViews, int level,
+void launch_build_lists(const FrameDev * frames, ViewState * views, const JobState * jobs, int view0, int nViews, int level,
                         int maxPixels, double minGradient2, int * chunkCounts, int maxChunksPerView, cudaStream_t s)
 {
   dim3 grid((maxPixels + LCHUNK - 1) / LCHUNK, nViews);
-  list_count_kernel<<<grid, LTHREADS, 0, s>>>(frames, views, jobs, level, minGradient2, chunkCounts, maxChunksPerView);
-  list_scan_kernel<<<nViews, 256, 0, s>>>(views, chunkCounts, maxChunksPerView);
-  list_write_kernel<<<grid, LTHREADS, 0, s>>>(frames, views, jobs, level, minGradient2, chunkCounts, maxChunksPerView);
+  list_count_kernel<<<grid, LTHREADS, 0, s>>>(frames, views, jobs, level, minGradient2, chunkCounts, maxChunksPerView, view0);
+  list_scan_kernel<<<nViews, 256, 0, s>>>(views, chunkCounts, maxChunksPerView, view0);
+  list_write_kernel<<<grid, LTHREADS, 0, s>>>(frames, views, jobs, level, minGradient2, chunkCounts, maxChunksPerView, view0);
 }
 
 int list_chunks_for(int pixels) { return (pixels + LCHUNK - 1) / LCHUNK; }
