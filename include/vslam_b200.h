@@ -97,6 +97,7 @@ typedef struct vslamb200_stats
      phase C, block reduction, sums barrier, solve, then the scale section split: histogram gather + scaler, publish +
      second cluster barrier, weight table */
   uint64_t phase_clocks[VSLAMB200_MAX_LEVELS][10];
+  uint64_t incremental_launches; /* level launches that ran the incremental (per-residual moments) kernel */
 } vslamb200_stats;
 
 const char * vslamb200_last_error(void);

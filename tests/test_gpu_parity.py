@@ -31,6 +31,19 @@ def _upload(ctx, p, levels, ids=(1, 2)):
     ctx.upload(np.array(ids), np.stack([p["gray0"], p["gray1"]]), np.stack([p["depth0"], p["depth1"]]), p["cam"], levels)
 
 
+@pytest.fixture(params=["dense", "incremental"])
+def level_kernel(request, monkeypatch):
+    """Both Gauss-Newton level kernels: the dense one (gn_level.cu) and the incremental per-residual-moments one
+    (gn_inc.cu; forced on every level it supports - one keyframe per job, scaler without offset)."""
+    monkeypatch.setenv("VSLAMB200_INC", "0" if request.param == "dense" else "2")
+    return request.param
+
+
+def _kernel_was_used(ctx, level_kernel, applicable=True):
+    n = ctx.stats()["incremental_launches"]
+    return n > 0 if (level_kernel == "incremental" and applicable) else n == 0
+
+
 def rel_fro(a, b):
     return np.linalg.norm(np.asarray(a) - np.asarray(b)) / max(np.linalg.norm(np.asarray(b)), 1e-300)
 
@@ -114,7 +127,7 @@ def _teacher_forced_check(O, ocfg, frames_from, from_poses, f1, to_pose, multi, 
 
 @pytest.mark.parametrize("loss,scaler,prior", [("TDIST", "TDIST", False), ("TDIST", "TDIST", True), ("NONE", "IDENTITY", False),
                                                ("HUBER", "MEAN", False), ("TUKEY", "MEDIAN", True)])
-def test_align_matches_oracle_per_iteration(ctx, capi, oracle, synth, loss, scaler, prior):
+def test_align_matches_oracle_per_iteration(ctx, capi, oracle, synth, loss, scaler, prior, level_kernel):
     O, A = oracle, capi
     p = _pair(synth, 640, 480, 1234)
     f0, f1 = _frames(O, p, 4)
@@ -123,8 +136,10 @@ def test_align_matches_oracle_per_iteration(ctx, capi, oracle, synth, loss, scal
     ocfg = O.make_config(loss=getattr(O, "LOSS_" + loss), scaler=getattr(O, "SCALER_" + scaler), **kw)
     ctx.set_config(A.make_config(loss=getattr(A, "LOSS_" + loss), scaler=getattr(A, "SCALER_" + scaler), **kw))
     ctx.set_trace(True)
+    ctx.reset_stats()
     ref = O.align(ocfg, f0, O.IDENTITY, f1, O.IDENTITY, want_trace=True)
     got = ctx.align([dict(to=2, to_pose=O.IDENTITY, frm=[1], from_poses=O.IDENTITY, multi=False)])[0]
+    assert _kernel_was_used(ctx, level_kernel, applicable=scaler in ("TDIST", "IDENTITY"))
     tr = ctx.get_trace(0, 4)
     _teacher_forced_check(O, ocfg, [f0], [O.IDENTITY], f1, O.IDENTITY, False, tr, got["iters"], prior, 4)
     # chained run: same number of steps, same stop reasons, same pose
@@ -141,7 +156,7 @@ def test_align_matches_oracle_per_iteration(ctx, capi, oracle, synth, loss, scal
     assert rel_fro(got["cov"], ref["cov"]) < 1e-3
 
 
-def test_batch_of_pairs_matches_oracle(ctx, capi, oracle, synth):
+def test_batch_of_pairs_matches_oracle(ctx, capi, oracle, synth, level_kernel):
     """BASELINE configs[2] in small: independent pairs in ONE batched call, each against the oracle."""
     O, A = oracle, capi
     n, L = 6, 4
@@ -149,8 +164,10 @@ def test_batch_of_pairs_matches_oracle(ctx, capi, oracle, synth):
     gray = np.stack([x for p in pairs for x in (p["gray0"], p["gray1"])])
     depth = np.stack([x for p in pairs for x in (p["depth0"], p["depth1"])])
     ctx.upload(np.arange(2 * n), gray, depth, pairs[0]["cam"], L)
+    ctx.reset_stats()
     got = ctx.align([dict(to=2 * k + 1, to_pose=O.IDENTITY, frm=[2 * k], from_poses=O.IDENTITY, multi=False)
                      for k in range(n)])
+    assert _kernel_was_used(ctx, level_kernel)
     ocfg = O.make_config()
     for k, p in enumerate(pairs):
         f0, f1 = _frames(O, p, L)
@@ -162,6 +179,45 @@ def test_batch_of_pairs_matches_oracle(ctx, capi, oracle, synth):
         # and the alignment recovers the ground-truth motion to the accuracy the reference's own tests ask for
         dt, dr = pose_err(O, got[k]["pose"], p["pose1"])
         assert dt < 0.01 and dr < 0.01, k
+
+
+def test_incremental_motion_bounds_never_miss_a_change(capi, oracle, synth, monkeypatch):
+    """Check mode of the incremental kernel: every point is re-evaluated in every iteration, and a point whose
+    residual changed although its tile's accumulated motion bound had not reached the point's limit is counted.
+    The bound is rigorous, so the count must be zero - on clean pairs, pairs with depth holes, larger motions (the
+    level kernels start far from the optimum on the coarse levels) and at every pyramid level."""
+    O, A = oracle, capi
+    monkeypatch.setenv("VSLAMB200_INC", "2")
+    monkeypatch.setenv("VSLAMB200_INC_CHECK", "1")
+    n, L = 8, 4
+    pairs = [_pair(synth, 640, 480, 4321 + k, holes=(40 if k % 2 else 0)) for k in range(n)]
+    gray = np.stack([x for p in pairs for x in (p["gray0"], p["gray1"])])
+    depth = np.stack([x for p in pairs for x in (p["depth0"], p["depth1"])])
+    ctx = A.Context(A.make_config())
+    try:
+        ctx.upload(np.arange(2 * n), gray, depth, pairs[0]["cam"], L)
+        # consecutive pairs, and pairs two "frames" apart in scene space are not available here: use the pairs as
+        # rendered plus a deliberately bad initial guess for half of them (larger per-level motion)
+        bad = O.se3_exp(np.array([0.01, -0.008, 0.012, 0.004, -0.003, 0.005]))
+        jobs = [dict(to=2 * k + 1, to_pose=(bad if k >= n // 2 else O.IDENTITY), frm=[2 * k], from_poses=O.IDENTITY,
+                     multi=False) for k in range(n)]
+        got = ctx.align(jobs)
+        st = ctx.stats()
+    finally:
+        ctx.close()
+    assert st["incremental_launches"] == L
+    flagged = sum(st["phase_clocks"][l][7] for l in range(L))
+    changed = sum(st["phase_clocks"][l][8] for l in range(L))
+    missed = sum(st["phase_clocks"][l][9] for l in range(L))
+    assert changed > 0 and flagged >= 0
+    assert missed == 0, (missed, changed)
+    ocfg = O.make_config()
+    for k, p in enumerate(pairs):
+        f0, f1 = _frames(O, p, L)
+        ref = O.align(ocfg, f0, O.IDENTITY, f1, jobs[k]["to_pose"])
+        assert list(got[k]["iters"][:L]) == list(ref["iters"]), k
+        dt, dr = pose_err(O, got[k]["pose"], ref["pose"])
+        assert dt < POSE_TOL and dr < POSE_TOL, k
 
 
 @pytest.mark.parametrize("K,prior", [(2, True), (3, False)])
@@ -269,7 +325,7 @@ def test_async_upload_pipeline_is_identical_to_the_synchronous_path(capi, oracle
 
 
 @pytest.mark.gpu
-def test_large_batch_two_stream_path_matches_oracle(capi, oracle, synth):
+def test_large_batch_two_stream_path_matches_oracle(capi, oracle, synth, level_kernel):
     """Batches of >= 192 jobs are cut into two halves that run on two streams (vslamb200_align); every pair of a
     200-frame sequence must still match the oracle (pose, and bit-identical to the single-stream run)."""
     import os

@@ -1,0 +1,40 @@
+"""Per-level timing and per-phase SM clocks of a full alignment batch (F-1 pairs of a 640x480 sequence, 4 levels).
+Phase slots of the dense kernel: phaseA, bar_hist, scale, phaseC, blockred, bar_sums, solve; of the incremental
+kernel: 0 warp+sample(+moment moves), 1 moment build (first evaluation), 2 scale, 3 A/b from moments, 6 solve."""
+import argparse
+import os
+import sys
+
+import numpy as np
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from vslam_b200 import capi, synth  # noqa: E402
+
+ap = argparse.ArgumentParser()
+ap.add_argument("--frames", type=int, default=257)
+ap.add_argument("--levels", type=int, default=4)
+ap.add_argument("--timing", type=int, default=1)
+args = ap.parse_args()
+W, H = 640, 480
+cam = synth.cam_for(W, H)
+gray, depth, _ = synth.make_sequence(args.frames, W, H, seed=1234, cam=cam)
+ctx = capi.Context(capi.make_config())
+ctx.upload(np.arange(args.frames), gray, depth, cam, args.levels)
+ident = np.array([0, 0, 0, 1, 0, 0, 0.0])
+jobs = [dict(to=i + 1, to_pose=ident, frm=[i], from_poses=ident, multi=False) for i in range(args.frames - 1)]
+ctx.align(jobs)
+capi.check(capi.lib().vslamb200_set_timing(ctx.h, args.timing))
+ctx.reset_stats()
+res = ctx.align(jobs)
+st = ctx.stats()
+print("INC", os.environ.get("VSLAMB200_INC"), "incremental launches", st["incremental_launches"], "ms_gn_level",
+      [round(x, 3) for x in st["ms_gn_level"][:args.levels]], "ms_lists", round(st["ms_lists"], 3))
+for l in range(args.levels):
+    pc = st["phase_clocks"][l]
+    tot = sum(pc[:7]) or 1
+    ev = st["pixel_iterations_level"][l] / (W * H / 4 ** l)
+    print(" level", l, "evals/job", round(ev / len(jobs), 2), "kclocks/job", [round(c / len(jobs) / 1e3, 1) for c in pc[:7]],
+          "share", [round(c / tot, 3) for c in pc[:7]])
+    if st["incremental_launches"] and st["point_iterations"]:
+        print("   slots 7-9 (incremental: flagged, changed, missed points; dense: scale sub-laps)", pc[7:10])
+ctx.close()

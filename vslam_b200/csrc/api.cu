@@ -716,6 +716,19 @@ int pick_cluster(int npx, int maxViewsPerJob)
   return 1;
 }
 
+// Which Gauss-Newton level kernel runs a level.  The incremental kernel (gn_inc.cu) keeps per-residual moments in shared
+// memory and needs one keyframe per job and a scaler without offset.  It is exact and parity-tested, but with one CTA per
+// job its scans are latency-bound and it is slower than the dense cluster kernel today, so it is
+// opt-in: VSLAMB200_INC=1 uses it on levels of at least 50 000 pixels, =2 wherever it is applicable (tests).
+bool use_incremental(const Problem & P, const vb::SolverParams & sp, int npx)
+{
+  int mode = 0;
+  if (const char * e = std::getenv("VSLAMB200_INC")) mode = std::atoi(e);
+  if (mode <= 0 || P.maxViews != 1 || npx > (1 << 20)) return false;
+  if (sp.scalerKind != VSLAMB200_SCALER_IDENTITY && sp.scalerKind != VSLAMB200_SCALER_TDIST) return false;
+  return mode >= 2 || npx >= 50000;
+}
+
 // One pyramid level for the jobs [job0, job0 + nJobs) (their views are contiguous: [view0, view0 + nViews)), queued on
 // `stream`.
 int run_level(vslamb200_ctx * c, Problem & P, int level, const vb::SolverParams & sp, int maxEvals, int job0, int nJobs,
@@ -738,8 +751,16 @@ int run_level(vslamb200_ctx * c, Problem & P, int level, const vb::SolverParams 
                          listChunks, stream);
   vb::launch_level_begin(dJobs, dViews, job0, nJobs, level, stream);
   if (c->timing) CK(cudaEventRecord(c->ev[1], stream));
-  CK(vb::launch_gn_level(dJobs, dViews, job0, nJobs, P.maxViews, cluster, sp, level, maxEvals, dTrace, traceJobStride,
-                         c->partials.as<double>(), stream));
+  if (use_incremental(P, sp, npx)) {
+    // VSLAMB200_INC_CHECK=1 (tests): every point is re-evaluated in every iteration and the points whose residual changed
+    // although their motion bound had not asked for them are counted (stats.phase_clocks[level][9], must stay 0)
+    const char * chk = std::getenv("VSLAMB200_INC_CHECK");
+    c->stats.incremental_launches++;
+    CK(vb::launch_gn_inc(dJobs, dViews, job0, nJobs, sp, level, maxEvals, dTrace, traceJobStride, chk && std::atoi(chk) > 0, stream));
+  } else {
+    CK(vb::launch_gn_level(dJobs, dViews, job0, nJobs, P.maxViews, cluster, sp, level, maxEvals, dTrace, traceJobStride,
+                           c->partials.as<double>(), stream));
+  }
   if (c->timing) CK(cudaEventRecord(c->ev[2], stream));
   c->stats.kernel_launches += 6;
   CK(cudaGetLastError());
@@ -759,17 +780,21 @@ int prepare_workspace(vslamb200_ctx * c, Problem & P, const vb::SolverParams & s
   const int nJobs = (int)P.jobs.size(), nViews = (int)P.views.size();
   const size_t npx0 = (size_t)P.W * P.H;
   const size_t listStride = align_up(npx0, vb::LIST_TILE);
-  // per view: list tiles (20 B per candidate pixel) | r u16   (22 bytes per candidate pixel)
+  // per view: list tiles (20 B per candidate pixel) | r u16 | lim f32 | 32 B per tile   (26.25 bytes per candidate pixel)
   const size_t tileBytes = listStride / vb::LIST_TILE * vb::LIST_TILE_BYTES;
-  CK(c->lists.ensure((tileBytes + listStride * 2) * nViews));
+  const size_t tileStateBytes = listStride / vb::LIST_TILE * 32;
+  const size_t viewBytes = tileBytes + listStride * 6 + tileStateBytes;
+  CK(c->lists.ensure(viewBytes * nViews));
   CK(c->chunkCounts.ensure((size_t)nViews * vb::list_chunks_for((int)npx0) * sizeof(int)));
   CK(c->partials.ensure((size_t)nViews * vb::NE_TERMS * sizeof(double)));
   uint8_t * base = c->lists.as<uint8_t>();
   for (int v = 0; v < nViews; v++) {
     vb::ViewState & V = P.views[v];
-    uint8_t * b = base + (size_t)v * (tileBytes + listStride * 2);
+    uint8_t * b = base + (size_t)v * viewBytes;
     V.tiles = b;
     V.r = (int16_t *)(b + tileBytes);
+    V.lim = (float *)(b + tileBytes + listStride * 2);
+    V.tileState = (float *)(b + tileBytes + listStride * 6);
   }
   CK(c->jobs.ensure(nJobs * sizeof(vb::JobState)));
   CK(c->views.ensure(nViews * sizeof(vb::ViewState)));

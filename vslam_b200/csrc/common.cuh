@@ -70,8 +70,10 @@ struct ViewState
   double xPred[6];          // MotionPrior::_xPred (SE3Alignment.cpp:32)
   double xCur[6];           // log(se3), kept in step with se3
   // robust weights of the current iteration
-  int * hist;               // HIST_BINS global bins
-  float * wlut;             // HIST_BINS weights
+  // incremental kernel (gn_inc.cu): per point the value of the tile's cumulative motion bound at which the point has to
+  // be re-evaluated; per LIST_TILE 8 floats: u, v, 1/depth ranges of the tile's points, cumulative motion bound, spare
+  float * lim;
+  float * tileState;
   double scale, offset;
 };
 
@@ -264,4 +266,7 @@ void launch_scatter_rcode(const ViewState * views, int view, int16_t * plane, cu
 size_t gn_level_static_smem();
 cudaError_t launch_gn_level(JobState * jobs, ViewState * views, int job0, int nJobs, int maxViewsPerJob, int clusterSize,
                             SolverParams p, int level, int maxEvals, double * trace, size_t traceJobStride, double * viewSums, cudaStream_t s);
+// gn_inc.cu (incremental level kernel: single keyframe, zero-offset scalers)
+cudaError_t launch_gn_inc(JobState * jobs, ViewState * views, int job0, int nJobs, SolverParams p, int level, int maxEvals,
+                          double * trace, size_t traceJobStride, int checkMode, cudaStream_t s);
 }  // namespace vb

@@ -22,7 +22,9 @@
 // aligner's iterates and stopping decisions needs ~1e-13 relative accuracy, not fp32's 1e-7.
 #include <cooperative_groups.h>
 
+#include "robust.cuh"
 #include "solve.cuh"
+#include "warp_filter.cuh"
 
 namespace cg = cooperative_groups;
 
@@ -45,42 +47,6 @@ __device__ __forceinline__ double block_sum(double v, double * sm /* >= GT/32 do
   return s;
 }
 
-__device__ __forceinline__ double loss_weight(const SolverParams & p, double r)
-{
-  switch (p.lossKind) {
-    case VSLAMB200_LOSS_TUKEY: {
-      const double C = 4.6851;
-      if (fabs(r) < C) {
-        const double rc = r / C;
-        const double q = 1.0 - rc * rc;
-        return q * q;
-      }
-      return 0.0;
-    }
-    case VSLAMB200_LOSS_HUBER:
-      if (fabs(r) < p.huberC) return 1.0;
-      return (p.huberC * r > 0.0 ? 1.0 : -1.0) / r;
-    case VSLAMB200_LOSS_TDIST:
-      return (p.lossV + 1.0) / (p.lossV + r * r);
-    default:
-      return 1.0;
-  }
-}
-
-// 1 / d for a positive, normal d: 20-bit seed refined by two Newton steps (relative error ~1e-16).  The scaler's
-// recurrence is a chain of dependent fp64 operations on one warp; the correctly rounded division's ~25
-// instruction sequence per term is what its latency is made of.
-__device__ __forceinline__ double rcp_newton(double d)
-{
-  double y;
-  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(d));
-  double e = fma(-d, y, 1.0);
-  y = fma(y, e, y);
-  e = fma(-d, y, 1.0);
-  y = fma(y, e, y);
-  e = fma(-d, y, 1.0);
-  return fma(y, e, y);
-}
 
 // bin b holds the residual value b - 255 (bin 511 is unused).  Thread t owns bins (t + j*GT + 192) mod 512:
 // j = 0 covers the central residuals -63..64, where nearly all the mass is, so the other j are skipped warp-wide
@@ -122,46 +88,7 @@ __device__ void compute_scale(
     // in r), slot m = 0..7; slots nobody populates are skipped warp-wide.
     // r^2 (nu+1) / (nu + r^2/sigma^2) == r^2 (nu+1) sigma^2 / (nu sigma^2 + r^2): one division per slot.
     __syncthreads();
-    if (tid < 32) {
-      double av[8], r2[8];
-      unsigned populated = 0;
-#pragma unroll
-      for (int m = 0; m < 8; m++) {
-        const int r = tid + 32 * m;  // 0..255
-        const int cnt = r == 0 ? h[255] : h[255 + r] + h[255 - r];
-        r2[m] = (double)(r * r);
-        av[m] = (double)cnt * (r2[m] * (p.scalerV + 1));
-        if (__any_sync(0xffffffffu, cnt > 0 && r > 0)) populated |= 1u << m;
-      }
-      // The recurrence is carried in x = sigma^2 (x' = mean(a x / (nu x + r^2))); sigma' = sqrt(x') only feeds the
-      // stopping test, so it is evaluated next to the following step's terms and the loop runs one step ahead
-      // (the look-ahead step is discarded on exit).
-      const double invn = 1.0 / (double)n;
-      auto next_x = [&](double x) {
-        const double vs2 = p.scalerV * x;
-        double t0 = 0.0, t1 = 0.0;
-#pragma unroll
-        for (int m = 0; m < 8; m += 2) {
-          if (populated & (1u << m)) t0 = fma(av[m] * x, rcp_newton(vs2 + r2[m]), t0);
-          if (populated & (2u << m)) t1 = fma(av[m + 1] * x, rcp_newton(vs2 + r2[m + 1]), t1);
-        }
-        double term = t0 + t1;
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) term += __shfl_xor_sync(0xffffffffu, term, o);
-        return term * invn;
-      };
-      double sigma = 1.0;
-      double x1 = next_x(1.0);  // sigma_1^2
-      for (int it = 0; it < 30; it++) {
-        const double x2 = next_x(x1);        // look-ahead: sigma_{it+2}^2
-        const double sg = sqrt(x1);          // sigma_{it+1}
-        const double step = fabs(sigma - sg);
-        sigma = sg;
-        x1 = x2;
-        if (!(step > 1e-5)) break;
-      }
-      scale = sigma;
-    }
+    if (tid < 32) scale = tdist_sigma_warp(h, 0, n, p.scalerV);
   } else if (p.scalerKind == VSLAMB200_SCALER_MEAN || p.scalerKind == VSLAMB200_SCALER_MEDIAN) {
     if (n > 0) {
       if (p.scalerKind == VSLAMB200_SCALER_MEAN) {
@@ -236,97 +163,6 @@ __device__ __forceinline__ double build_weights(
   return c2;
 }
 
-// Exact warp of one interest point, operation for operation the oracle's (fp64, explicit fma):
-// Camera::image2camera (Camera.cpp:32-35), se3 * p (Warp.cpp:160-161), Camera::camera2image
-// (Camera.cpp:23-30), visibility (InverseCompositional.cpp:115-116), std::round.
-__device__ __noinline__ int warp_exact(const ViewState & V, int u, int v, float df)
-{
-  const double d = (double)df;
-  const double X = __fma_rn(V.kx, d, __dmul_rn(V.ifx, __dmul_rn((double)u, d)));
-  const double Y = __fma_rn(V.ky, d, __dmul_rn(V.ify, __dmul_rn((double)v, d)));
-  const double qx = __fma_rn(V.R[2], d, __fma_rn(V.R[1], Y, __fma_rn(V.R[0], X, V.t[0])));
-  const double qy = __fma_rn(V.R[5], d, __fma_rn(V.R[4], Y, __fma_rn(V.R[3], X, V.t[1])));
-  const double qz = __fma_rn(V.R[8], d, __fma_rn(V.R[7], Y, __fma_rn(V.R[6], X, V.t[2])));
-  if (!(qz > 0.0)) return -1;
-  const double up = __ddiv_rn(__fma_rn(V.fx, qx, __dmul_rn(V.cx, qz)), qz);
-  const double vp = __ddiv_rn(__fma_rn(V.fy, qy, __dmul_rn(V.cy, qz)), qz);
-  if (!(1.0 < up && up < (double)(V.Wt - 1) && 1.0 < vp && vp < (double)(V.Ht - 1) && isfinite(up))) return -1;
-  // std::round (half away from zero) of a positive value == floor(x + 0.5)
-  return __double2int_rd(vp + 0.5) * V.Wt + __double2int_rd(up + 0.5);
-}
-
-struct WarpConsts
-{
-  float r00, r01, r02, r10, r11, r12, r20, r21, r22, t0, t1, t2, fx, fy, ifx, ify, kx, ky, epsA, epsB;
-  int Wt, Ht;
-};
-
-// Sampled target pixel index of one interest point, or -1 when it is not visible.  The index and the
-// visibility flag are integer decisions and must be the fp64 oracle's.  A filtered evaluation gets them
-// without fp64 in the common case: in exact arithmetic u' = u + fx*(Dx - xn*Dz)/(z + Dz) with
-// D = (R - I) p + t, because p was back-projected from the integer pixel (u, v).  The displacement du is
-// small, so fp32 carries it with an absolute error far below a pixel.  With iu = u + rint(du) and the exact
-// fp32 remainder fu = du - rint(du) in [-0.5, 0.5], u' = iu + fu, so
-//   - the rounded target round(u') is iu unless |fu| is within eps of 0.5,
-//   - visibility 1 < u' < W-1 is decided by iu alone, except on the ring iu == 1 (visible iff fu > 0) and
-//     iu == W-1 (visible iff fu < 0), where it is safe unless |fu| <= eps.
-// warp_eval() is branch-free (the four points of a thread interleave).  When every rounded target of the warp lies
-// strictly inside the ring (the common case, decided by two unsigned compares per point) warp_pick_interior()
-// finishes with the rounding distance alone; otherwise warp_pick_ring() adds the visibility logic.  Both report
-// `ok`; the few points within eps of a boundary are redone by warp_exact().
-struct WarpEval
-{
-  float fu, fv, eps;
-  int iu, iv;
-  bool okb;       // depth / magnitude guards of the fp32 evaluation
-  bool interior;  // 2 <= iu <= W-2 and 2 <= iv <= H-2
-};
-__device__ __forceinline__ WarpEval warp_eval(const WarpConsts & c, uint32_t pk, float d)
-{
-  WarpEval e;
-  const int u = pk & 0xfff, v = (pk >> 12) & 0xfff;
-  const float xn = fmaf((float)u, c.ifx, c.kx), yn = fmaf((float)v, c.ify, c.ky);
-  const float px = xn * d, py = yn * d;
-  const float Dx = fmaf(c.r02, d, fmaf(c.r01, py, fmaf(c.r00, px, c.t0)));
-  const float Dy = fmaf(c.r12, d, fmaf(c.r11, py, fmaf(c.r10, px, c.t1)));
-  const float Dz = fmaf(c.r22, d, fmaf(c.r21, py, fmaf(c.r20, px, c.t2)));
-  const float qz = d + Dz;
-  float iz;
-  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(iz) : "f"(qz));  // 1 ulp; covered by the 2^-18 (|du|+|dv|) term of eps
-  const float du = (c.fx * iz) * fmaf(-xn, Dz, Dx);
-  const float dv = (c.fy * iz) * fmaf(-yn, Dz, Dy);
-  // nearest integer of the displacement through the 1.5 * 2^23 trick (|du| < 4096 is part of okb)
-  const float MAGIC = 12582912.f;
-  const float mu = du + MAGIC, mv = dv + MAGIC;
-  e.fu = du - (mu - MAGIC);
-  e.fv = dv - (mv - MAGIC);
-  e.iu = u + (__float_as_int(mu) - 0x4B400000);
-  e.iv = v + (__float_as_int(mv) - 0x4B400000);
-  const float s = fabsf(du) + fabsf(dv);
-  e.eps = fmaf(fmaf(c.epsA, d, c.epsB), fabsf(iz), fmaf(3.8e-6f, s, 6.1e-5f));
-  e.okb = qz > 0.25f * d && s < 4096.f;
-  e.interior = (unsigned)(e.iu - 2) <= (unsigned)(c.Wt - 4) && (unsigned)(e.iv - 2) <= (unsigned)(c.Ht - 4);
-  return e;
-}
-__device__ __forceinline__ int warp_pick_interior(const WarpConsts & c, const WarpEval & e, bool & ok)
-{
-  ok = e.okb && 0.5f - fmaxf(fabsf(e.fu), fabsf(e.fv)) > e.eps;  // distance to the nearest rounding boundary
-  return e.iv * c.Wt + e.iu;
-}
-__device__ __forceinline__ int warp_pick_ring(const WarpConsts & c, const WarpEval & e, bool & ok)
-{
-  const int iu = e.iu, iv = e.iv;
-  const float au = fabsf(e.fu), av = fabsf(e.fv);
-  const bool ringu = iu == 1 || iu == c.Wt - 1, ringv = iv == 1 || iv == c.Ht - 1;
-  float dist = 0.5f - fmaxf(au, av);
-  dist = ringu ? fminf(dist, au) : dist;  // on the ring: distance to the visibility boundary as well
-  dist = ringv ? fminf(dist, av) : dist;
-  ok = e.okb && dist > e.eps;
-  bool vis = (unsigned)(iu - 1) <= (unsigned)(c.Wt - 2) && (unsigned)(iv - 1) <= (unsigned)(c.Ht - 2);
-  vis = vis && !(iu == 1 && e.fu < 0.f) && !(iu == c.Wt - 1 && e.fu > 0.f);
-  vis = vis && !(iv == 1 && e.fv < 0.f) && !(iv == c.Ht - 1 && e.fv > 0.f);
-  return vis ? iv * c.Wt + iu : -1;
-}
 
 // ------------------------------------------------------------------------------------------------
 // shared-memory ring fed by TMA bulk copies
