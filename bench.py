@@ -266,6 +266,22 @@ def main():
     h2d = F * W * H * 5
     d2h = (F - 1) * C.sizeof(capi.Result)
 
+    # p50 / p95 latency of ONE alignment (BASELINE.json metric, second half): batch size 1, the first pair
+    # of the sequence (frames resident), back-to-back calls, wall time from the host's submit to the result on the host
+    lat = None
+    if rank == 0:
+        one = (capi.Result * 1)()
+        for _ in range(50):
+            ctx.align_raw(jobs, 1, one)
+        ts = []
+        for _ in range(300):
+            t0 = time.perf_counter()
+            ctx.align_raw(jobs, 1, one)
+            ts.append((time.perf_counter() - t0) * 1e3)
+        assert list(one[0].pose) == list(resident_poses[0]), "single-pair call differs from the batched result"
+        lat = {"p50_ms": float(np.percentile(ts, 50)), "p95_ms": float(np.percentile(ts, 95)), "calls": len(ts),
+               "what": "one 640x480 pair, 4 levels, frames resident, host submit -> pose on host"}
+
     # per-kernel timing pass (events around every residual / accumulate launch; separate from the timed runs)
     capi.check(capi.lib().vslamb200_set_timing(ctx.h, 1))
     ctx.reset_stats()
@@ -330,7 +346,7 @@ def main():
                     "ms_per_step": ms_e2e / args.steps, "max_pose_diff_vs_resident": e2e_diff,
                     "pipeline": "upload of step s+1 (copy stream) overlaps the alignment of step s; all uploads timed"},
             "gpu_launches": int(st["kernel_launches"]),
-            "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
+            "latency": lat, "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
         }))
     ctx.close()
     if use_dist:

@@ -41,7 +41,8 @@ enum { VSLAMB200_SCALER_IDENTITY = 0, VSLAMB200_SCALER_MEDIAN = 1, VSLAMB200_SCA
 enum { VSLAMB200_STOP_MAXITER = 0, VSLAMB200_STOP_CONSTRAINTS = 1, VSLAMB200_STOP_HESSIAN = 2, VSLAMB200_STOP_CHI2 = 3, VSLAMB200_STOP_CONVERGED = 4, VSLAMB200_STOP_NAN = 5 };
 /* host image layouts / depth element types accepted by frame upload */
 enum { VSLAMB200_ROW_MAJOR = 0, VSLAMB200_COL_MAJOR = 1 };   /* COL_MAJOR == Eigen default (core/src/types.h:33-35) */
-enum { VSLAMB200_DEPTH_F32 = 0, VSLAMB200_DEPTH_F64 = 1 };
+enum { VSLAMB200_DEPTH_F32 = 0, VSLAMB200_DEPTH_F64 = 1, VSLAMB200_DEPTH_U16 = 2 /* frames_ingest_rgbd only */ };
+enum { VSLAMB200_RGB = 0, VSLAMB200_BGR = 1 };
 
 typedef struct vslamb200_ctx vslamb200_ctx;
 
@@ -128,6 +129,14 @@ int vslamb200_frames_upload_async(
 int vslamb200_frames_upload_device(
   vslamb200_ctx * ctx, int n, const uint64_t * ids, int W, int H, const uint8_t * d_gray, const float * d_depth,
   const double * cams, int n_levels);
+/* Frame ingestion as the node does it, fused into the upload (src/ros/nodes/NodeRgbdAlignment.cpp:177-199, replaces
+ * cv::cvtColor(RGB2GRAY) :182, the NaN -> 0 select :190 and, for 16-bit sensor depth, loadDepth(...) / 5000.0 of
+ * odometry/test/test_alignment_se3.cpp:99), followed by what vslamb200_frames_upload does.  rgb: n row-major H x W x 3
+ * interleaved 8-bit images in channel_order VSLAMB200_RGB / VSLAMB200_BGR; depth: n row-major planes of depth_type
+ * (F32, F64 or U16); every depth value is divided by depth_divisor in double (1.0: already metres) and NaN becomes 0. */
+int vslamb200_frames_ingest_rgbd(
+  vslamb200_ctx * ctx, int n, const uint64_t * ids, int W, int H, const uint8_t * rgb, int channel_order,
+  const void * depth, int depth_type, double depth_divisor, const double * cams, int n_levels);
 int vslamb200_frame_release(vslamb200_ctx * ctx, uint64_t id);
 int vslamb200_frame_release_all(vslamb200_ctx * ctx);
 /* dims4 = intensity W, H, depth W, H at that level (they differ at odd sizes: Frame.cpp:264 vs algorithm.h:93-94) */

@@ -87,6 +87,8 @@ def lib():
                                            C.c_void_p]
         for n in ("vo_pyr_down_u8", "vo_blur3_u8"):
             getattr(L, n).argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
+        L.vo_rgb_to_gray_u8.argtypes = [C.c_void_p, C.c_long, C.c_int, C.c_void_p]
+        L.vo_depth_ingest.argtypes = [C.c_void_p, C.c_long, C.c_double, C.c_void_p]
         L.vo_sobel3_s16.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
         for n in ("vo_se3_exp", "vo_se3_log", "vo_se3_inv", "vo_quat_to_R"):
             getattr(L, n).argtypes = [C.c_void_p, C.c_void_p]
@@ -100,6 +102,22 @@ def _p(a):
 
 
 IDENTITY = np.array([0, 0, 0, 1, 0, 0, 0], dtype=np.float64)
+
+
+def rgb_to_gray(rgb, bgr=False):
+    """cv::cvtColor(COLOR_RGB2GRAY / COLOR_BGR2GRAY) of an (H, W, 3) u8 image (NodeRgbdAlignment.cpp:182)."""
+    rgb = np.ascontiguousarray(rgb, np.uint8)
+    out = np.empty(rgb.shape[:-1], np.uint8)
+    lib().vo_rgb_to_gray_u8(_p(rgb), C.c_long(out.size), int(bgr), _p(out))
+    return out
+
+
+def depth_ingest(depth, divisor=1.0):
+    """NaN -> 0 and the dataset's depth factor (NodeRgbdAlignment.cpp:190, test_alignment_se3.cpp:99); -> f64."""
+    d = np.ascontiguousarray(depth, np.float64)
+    out = np.empty_like(d)
+    lib().vo_depth_ingest(_p(d), C.c_long(d.size), C.c_double(divisor), _p(out))
+    return out
 
 
 def pyr_down_u8(img):

@@ -293,6 +293,27 @@ static inline int reflect101(int i, int n)
   return i;
 }
 
+// Frame ingestion of the node (src/ros/nodes/NodeRgbdAlignment.cpp:177-199): cv::cvtColor(mat, mat, COLOR_RGB2GRAY)
+// on an 8UC3 image (:182).  OpenCV's 8-bit path is the integer formula below (15-bit coefficients 9798 / 19235 /
+// 3735, round to nearest); pinned against cv2 4.13.0 (tests/golden/cv_ops.npz).
+static void rgb_to_gray_u8(const uint8_t * rgb, size_t n, int bgr, uint8_t * gray)
+{
+  for (size_t i = 0; i < n; i++) {
+    const int c0 = rgb[3 * i], c1 = rgb[3 * i + 1], c2 = rgb[3 * i + 2];
+    const int r = bgr ? c2 : c0, b = bgr ? c0 : c2;
+    gray[i] = (uint8_t)((r * 9798 + c1 * 19235 + b * 3735 + (1 << 14)) >> 15);
+  }
+}
+// depth = depth.array().isNaN().select(0, depth) (NodeRgbdAlignment.cpp:190, utils.cpp:74); 16-bit sensor depth is
+// divided by the dataset's factor in double (loadDepth(...) / 5000.0, odometry/test/test_alignment_se3.cpp:99)
+static void depth_ingest(const double * in, size_t n, double divisor, double * out)
+{
+  for (size_t i = 0; i < n; i++) {
+    const double v = in[i] / divisor;
+    out[i] = std::isnan(v) ? 0.0 : v;
+  }
+}
+
 // cv::pyrDown as used by cv::buildPyramid (core/src/Frame.cpp:264):
 // 5x5 binomial [1 4 6 4 1]^2, reflect-101, (s+128)>>8, even rows/cols, size ((W+1)/2,(H+1)/2)
 static void pyr_down_u8(const uint8_t * src, int W, int H, uint8_t * dst)
@@ -1013,6 +1034,8 @@ static vo::SE3 to_se3(const double * p)
 }
 
 void vo_pyr_down_u8(const uint8_t * src, int W, int H, uint8_t * dst) { vo::pyr_down_u8(src, W, H, dst); }
+void vo_rgb_to_gray_u8(const uint8_t * rgb, long n, int bgr, uint8_t * gray) { vo::rgb_to_gray_u8(rgb, (size_t)n, bgr, gray); }
+void vo_depth_ingest(const double * in, long n, double divisor, double * out) { vo::depth_ingest(in, (size_t)n, divisor, out); }
 void vo_blur3_u8(const uint8_t * src, int W, int H, uint8_t * dst) { vo::blur3_u8(src, W, H, dst); }
 void vo_sobel3_s16(const uint8_t * g, int W, int H, int16_t * dx, int16_t * dy) { vo::sobel3_s16(g, W, H, dx, dy); }
 long vo_depth_down(const double * src, int W, int H, double * dst, int f32_storage)

@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Generates tests/golden/cv_ops.npz: OpenCV outputs for the image operations the reference delegates to OpenCV
 (core/src/Frame.cpp:264 cv::buildPyramid; :225 cv::GaussianBlur 3x3 sigma 0 BORDER_DEFAULT; :227-228 cv::Sobel
-CV_16S ksize 3).  Run in the build container (cv2 4.13 is importable there); the GPU box only reads the .npz.
+CV_16S ksize 3; src/ros/nodes/NodeRgbdAlignment.cpp:182 cv::cvtColor COLOR_RGB2GRAY).  Run in the build container (cv2 4.13 is importable there); the GPU box only reads the .npz.
 
     python tests/golden/make_golden.py
 """
@@ -39,6 +39,14 @@ def main():
         data[name + "/blur"] = blur
         data[name + "/dx"] = cv2.Sobel(blur, cv2.CV_16S, 1, 0, ksize=3)
         data[name + "/dy"] = cv2.Sobel(blur, cv2.CV_16S, 0, 1, ksize=3)
+    rng = np.random.default_rng(182)
+    rgb = rng.integers(0, 256, (40, 56, 3), dtype=np.uint8)
+    r = np.arange(0, 256, 5, dtype=np.uint8)
+    grid = np.stack(np.meshgrid(r, r, r, indexing="ij"), -1).reshape(-1, 52, 3)   # every 5th value of each channel
+    for name, img in (("rgb_noise_56x40", rgb), ("rgb_grid", np.ascontiguousarray(grid))):
+        data[name + "/img"] = img
+        data[name + "/gray_rgb"] = cv2.cvtColor(img, cv2.COLOR_RGB2GRAY)
+        data[name + "/gray_bgr"] = cv2.cvtColor(img, cv2.COLOR_BGR2GRAY)
     np.savez_compressed(os.path.join(HERE, "cv_ops.npz"), **data)
     print("wrote", os.path.join(HERE, "cv_ops.npz"), len(data), "arrays")
 

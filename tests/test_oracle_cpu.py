@@ -16,7 +16,7 @@ def golden():
 
 
 def _names(g):
-    return sorted({k.split("/")[0] for k in g.files if "/" in k})
+    return sorted({k.split("/")[0] for k in g.files if "/" in k and not k.startswith("rgb_")})
 
 
 # ---------------------------------------------------------------------------------------------------------
@@ -44,6 +44,23 @@ def test_blur_and_sobel_match_opencv_golden(oracle, golden):
         assert dx.dtype == np.int16
         assert np.array_equal(dx, golden[n + "/dx"]), n
         assert np.array_equal(dy, golden[n + "/dy"]), n
+
+
+def test_rgb_to_gray_matches_opencv_golden(oracle, golden):
+    """cv::cvtColor(COLOR_RGB2GRAY) of the node's ingestion (NodeRgbdAlignment.cpp:182), both channel orders."""
+    for name in ("rgb_noise_56x40", "rgb_grid"):
+        img = golden[name + "/img"]
+        assert np.array_equal(oracle.rgb_to_gray(img), golden[name + "/gray_rgb"]), name
+        assert np.array_equal(oracle.rgb_to_gray(img, bgr=True), golden[name + "/gray_bgr"]), name
+
+
+def test_depth_ingest_zeroes_nan_and_applies_the_dataset_factor(oracle):
+    """depth.array().isNaN().select(0, depth) (NodeRgbdAlignment.cpp:190); loadDepth / 5000.0 (test_alignment_se3.cpp:99)."""
+    d = np.array([[5000.0, np.nan, 0.0], [12345.0, 65535.0, np.inf]])
+    out = oracle.depth_ingest(d, 5000.0)
+    assert out[0, 0] == 1.0 and out[0, 1] == 0.0 and out[0, 2] == 0.0
+    assert out[1, 0] == 12345.0 / 5000.0 and out[1, 1] == 65535.0 / 5000.0 and np.isinf(out[1, 2])
+    assert np.array_equal(oracle.depth_ingest(np.array([1.5, np.nan])), np.array([1.5, 0.0]))
 
 
 def test_frame_pyramid_uses_the_same_ops(oracle, golden):

@@ -13,7 +13,8 @@ TRACE_STRIDE = 64
 LOSS_NONE, LOSS_QUADRATIC, LOSS_TUKEY, LOSS_HUBER, LOSS_TDIST = range(5)
 SCALER_IDENTITY, SCALER_MEDIAN, SCALER_MEAN, SCALER_TDIST = range(4)
 ROW_MAJOR, COL_MAJOR = 0, 1
-DEPTH_F32, DEPTH_F64 = 0, 1
+DEPTH_F32, DEPTH_F64, DEPTH_U16 = 0, 1, 2
+RGB, BGR = 0, 1
 R_NOT_INTEREST, R_INVISIBLE = -32768, -32767
 STOP_NAMES = ["maxiter", "constraints", "hessian", "chi2", "converged", "nan"]
 
@@ -45,7 +46,8 @@ class Stats(C.Structure):
 
 EXPORTS = [
     "vslamb200_last_error", "vslamb200_version", "vslamb200_create", "vslamb200_destroy", "vslamb200_set_config",
-    "vslamb200_set_stream", "vslamb200_frames_upload", "vslamb200_frames_upload_device", "vslamb200_frame_release",
+    "vslamb200_set_stream", "vslamb200_frames_upload", "vslamb200_frames_upload_device", "vslamb200_frames_ingest_rgbd",
+    "vslamb200_frame_release",
     "vslamb200_frame_release_all", "vslamb200_frame_dims", "vslamb200_frame_download", "vslamb200_align",
     "vslamb200_set_trace", "vslamb200_get_trace", "vslamb200_evaluate", "vslamb200_get_stats",
     "vslamb200_reset_stats", "vslamb200_set_timing", "vslamb200_synchronize",
@@ -77,6 +79,7 @@ def lib():
         L.vslamb200_frames_upload.argtypes = [vp, i, vp, i, i, vp, sz, vp, i, sz, i, vp, i]
         L.vslamb200_frames_upload_async.argtypes = [vp, i, vp, i, i, vp, sz, vp, i, sz, i, vp, i]
         L.vslamb200_frames_upload_device.argtypes = [vp, i, vp, i, i, vp, vp, vp, i]
+        L.vslamb200_frames_ingest_rgbd.argtypes = [vp, i, vp, i, i, vp, i, vp, i, C.c_double, vp, i]
         L.vslamb200_frame_release.argtypes = [vp, u64]
         L.vslamb200_frame_release_all.argtypes = [vp]
         L.vslamb200_frame_dims.argtypes = [vp, u64, i, vp]
@@ -153,6 +156,19 @@ class Context:
         cams = np.ascontiguousarray(np.broadcast_to(np.asarray(cams, np.float64).reshape(-1, 4), (n, 4)))
         check(lib().vslamb200_frames_upload_async(self.h, n, ptr(ids), W, H, C.c_void_p(gray_ptr), 0,
                                                   C.c_void_p(depth_ptr), DEPTH_F32, 0, ROW_MAJOR, ptr(cams), n_levels))
+
+    def ingest_rgbd(self, ids, rgb, depth, cams, n_levels, bgr=False, depth_divisor=1.0):
+        """Node-side ingestion (NodeRgbdAlignment.cpp:177-199): rgb (n,H,W,3) u8, depth (n,H,W) f32 / f64 / u16."""
+        ids = np.ascontiguousarray(np.atleast_1d(ids), np.uint64)
+        rgb = np.ascontiguousarray(rgb, np.uint8)
+        if rgb.ndim == 3:
+            rgb = rgb[None]
+        n, H, W, _ = rgb.shape
+        depth = np.ascontiguousarray(depth)
+        dt = {np.dtype(np.float32): DEPTH_F32, np.dtype(np.float64): DEPTH_F64, np.dtype(np.uint16): DEPTH_U16}[depth.dtype]
+        cams = np.ascontiguousarray(np.broadcast_to(np.asarray(cams, np.float64).reshape(-1, 4), (n, 4)))
+        check(lib().vslamb200_frames_ingest_rgbd(self.h, n, ptr(ids), W, H, ptr(rgb), BGR if bgr else RGB, ptr(depth), dt,
+                                                 float(depth_divisor), ptr(cams), n_levels))
 
     def upload_device(self, ids, d_gray_ptr, d_depth_ptr, n, W, H, cams, n_levels):
         ids = np.ascontiguousarray(np.atleast_1d(ids), np.uint64)

@@ -548,6 +548,39 @@ int vslamb200_frames_upload_device(
   return preprocess(c, slots, nLevels, true, c->stream);
 }
 
+int vslamb200_frames_ingest_rgbd(
+  vslamb200_ctx * c, int n, const uint64_t * ids, int W, int H, const uint8_t * rgb, int channelOrder, const void * depth,
+  int depthType, double depthDivisor, const double * cams, int nLevels)
+{
+  if (!c || !rgb || !depth) return fail(VSLAMB200_EINVAL, "frames_ingest_rgbd: null argument");
+  if (depthType != VSLAMB200_DEPTH_F32 && depthType != VSLAMB200_DEPTH_F64 && depthType != VSLAMB200_DEPTH_U16)
+    return fail(VSLAMB200_EINVAL, "frames_ingest_rgbd: bad depth_type");
+  if (channelOrder != VSLAMB200_RGB && channelOrder != VSLAMB200_BGR)
+    return fail(VSLAMB200_EINVAL, "frames_ingest_rgbd: bad channel_order");
+  if (!(depthDivisor > 0.0) || !std::isfinite(depthDivisor)) return fail(VSLAMB200_EINVAL, "frames_ingest_rgbd: bad depth_divisor");
+  CK(cudaSetDevice(c->device));
+  std::vector<int> slots;
+  if (int e = make_frames(c, n, ids, W, H, cams, nLevels, slots)) return e;
+  const size_t npx = (size_t)W * H;
+  const size_t dsz = depthType == VSLAMB200_DEPTH_F64 ? 8 : depthType == VSLAMB200_DEPTH_U16 ? 2 : 4;
+  const int sub = 32;  // frames per staging round
+  CK(c->stageGray.ensure(npx * 3 * sub));
+  CK(c->stageDepth.ensure(npx * dsz * sub));
+  CK(c->slotsBuf.ensure((size_t)n * sizeof(int)));
+  for (int b = 0; b < n; b += sub) {
+    const int m = std::min(sub, n - b);
+    CK(cudaMemcpyAsync(c->stageGray.p, rgb + npx * 3 * b, npx * 3 * m, cudaMemcpyHostToDevice, c->stream));
+    CK(cudaMemcpyAsync(c->stageDepth.p, (const uint8_t *)depth + npx * dsz * b, npx * dsz * m, cudaMemcpyHostToDevice, c->stream));
+    CK(cudaMemcpyAsync(c->slotsBuf.p, slots.data() + b, m * sizeof(int), cudaMemcpyHostToDevice, c->stream));
+    vb::launch_ingest_rgbd(c->stageGray.as<uint8_t>(), c->stageDepth.p, depthType, channelOrder == VSLAMB200_BGR, depthDivisor, W, H,
+                           c->dFrames.as<vb::FrameDev>(), c->slotsBuf.as<int>(), m, c->stream);
+    c->stats.kernel_launches++;
+    CK(cudaStreamSynchronize(c->stream));
+  }
+  c->stats.h2d_bytes += (uint64_t)n * npx * (3 + dsz);
+  return preprocess(c, slots, nLevels, true, c->stream);
+}
+
 int vslamb200_frame_release(vslamb200_ctx * c, uint64_t id)
 {
   if (!c) return fail(VSLAMB200_EINVAL, "ctx is null");

@@ -249,6 +249,8 @@ __device__ __forceinline__ int reflect101(int i, int n)
 // preprocess.cu
 void launch_ingest(const uint8_t * stagedGray, const void * stagedDepth, int depthType, int layout, int W, int H,
                    const FrameDev * frames, const int * slots, int n, cudaStream_t s);
+void launch_ingest_rgbd(const uint8_t * stagedRgb, const void * stagedDepth, int depthType, int bgr, double divisor, int W,
+                        int H, const FrameDev * frames, const int * slots, int n, cudaStream_t s);
 void launch_pyramid_level(const FrameDev * frames, const int * slots, int n, int level, int W, int H, int Wd, int Hd,
                           int Wp, int Hp, int Wdp, int Hdp, cudaStream_t s);
 void launch_gradients(const FrameDev * frames, const int * slots, int n, int level, int W, int H, cudaStream_t s);

@@ -1,5 +1,7 @@
 // Frame preprocessing on the device: ingest, image pyramid, depth pyramid, gradients.
 // Replaces Frame::computePyramid / computeDerivatives (core/src/Frame.cpp:215-275) for a batch of frames.
+#include <algorithm>
+
 #include "common.cuh"
 
 namespace vb
@@ -57,6 +59,55 @@ void launch_ingest(const uint8_t * stagedGray, const void * stagedDepth, int dep
     ingest_kernel<double><<<grid, 256, 0, s>>>(stagedGray, (const double *)stagedDepth, layout, W, H, frames, slots);
   else
     ingest_kernel<float><<<grid, 256, 0, s>>>(stagedGray, (const float *)stagedDepth, layout, W, H, frames, slots);
+}
+
+// Node-side ingestion fused into the upload (src/ros/nodes/NodeRgbdAlignment.cpp:177-199): cv::cvtColor(RGB2GRAY) of
+// the interleaved 8UC3 image (OpenCV's 8-bit integer formula, 15-bit coefficients), depth / divisor in double
+// (loadDepth(...) / 5000.0, odometry/test/test_alignment_se3.cpp:99), NaN -> 0 (:190), narrowed to the f32 plane.
+// Four pixels per thread: 12 colour bytes in, one 32-bit store of grey values and one 128-bit store of depths out.
+template <typename DepthT>
+__global__ void __launch_bounds__(256) ingest_rgbd_kernel(
+  const uint8_t * __restrict__ rgb, const DepthT * __restrict__ depth, int bgr, double divisor, size_t npx,
+  const FrameDev * __restrict__ frames, const int * __restrict__ slots)
+{
+  const FrameDev & f = frames[slots[blockIdx.y]];
+  const uint8_t * c = rgb + (size_t)blockIdx.y * npx * 3;
+  const DepthT * d = depth + (size_t)blockIdx.y * npx;
+  for (size_t i = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) * 4; i < npx; i += (size_t)gridDim.x * blockDim.x * 4) {
+    uint8_t g[4];
+    float z[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+      const size_t j = i + k < npx ? i + k : npx - 1;
+      const int c0 = c[3 * j], c1 = c[3 * j + 1], c2 = c[3 * j + 2];
+      const int r = bgr ? c2 : c0, b = bgr ? c0 : c2;
+      g[k] = (uint8_t)((r * 9798 + c1 * 19235 + b * 3735 + (1 << 14)) >> 15);
+      const double v = (double)d[j] / divisor;
+      z[k] = isnan(v) ? 0.f : (float)v;
+    }
+    if (i + 3 < npx && (npx & 3) == 0) {
+      *reinterpret_cast<uchar4 *>(f.I[0] + i) = make_uchar4(g[0], g[1], g[2], g[3]);
+      *reinterpret_cast<float4 *>(f.Z[0] + i) = make_float4(z[0], z[1], z[2], z[3]);
+    } else {
+      for (int k = 0; k < 4 && i + k < npx; k++) {
+        f.I[0][i + k] = g[k];
+        f.Z[0][i + k] = z[k];
+      }
+    }
+  }
+}
+
+void launch_ingest_rgbd(const uint8_t * stagedRgb, const void * stagedDepth, int depthType, int bgr, double divisor, int W, int H,
+                        const FrameDev * frames, const int * slots, int n, cudaStream_t s)
+{
+  const size_t npx = (size_t)W * H;
+  dim3 grid((unsigned)std::min<size_t>(148 * 4, (npx / 4 + 255) / 256), n);
+  if (depthType == VSLAMB200_DEPTH_F64)
+    ingest_rgbd_kernel<double><<<grid, 256, 0, s>>>(stagedRgb, (const double *)stagedDepth, bgr, divisor, npx, frames, slots);
+  else if (depthType == VSLAMB200_DEPTH_U16)
+    ingest_rgbd_kernel<uint16_t><<<grid, 256, 0, s>>>(stagedRgb, (const uint16_t *)stagedDepth, bgr, divisor, npx, frames, slots);
+  else
+    ingest_rgbd_kernel<float><<<grid, 256, 0, s>>>(stagedRgb, (const float *)stagedDepth, bgr, divisor, npx, frames, slots);
 }
 
 // ------------------------------------------------------------------------------------------------
