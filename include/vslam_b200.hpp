@@ -74,6 +74,7 @@ class PoseWithCovariance
 {
 public:
   typedef std::shared_ptr<PoseWithCovariance> ShPtr;
+  typedef std::shared_ptr<const PoseWithCovariance> ConstShPtr;
   typedef std::unique_ptr<PoseWithCovariance> UnPtr;
   PoseWithCovariance() { _cov.fill(0.0); for (int i = 0; i < 6; i++) _cov[7 * i] = 1.0; }
   PoseWithCovariance(const SE3d & pose, const Matd6 & cov) : _pose(pose), _cov(cov) {}

@@ -66,6 +66,16 @@ def test_pyramid_and_gradients_exact(ctx, oracle, synth, W, H, levels, holes):
         assert np.array_equal(got["Z"].astype(np.float64), ref["Z"]), f"depth level {l}"
 
 
+def test_single_frame_uploads(ctx, oracle, synth):
+    """One frame per call (what the odometry loop does), f32 row-major: the direct copy path with a one-row pitch."""
+    p = _pair(synth, 320, 240, 3)
+    f0, _ = _frames(oracle, p, 3)
+    ctx.upload(np.array([9]), p["gray0"][None], p["depth0"][None].astype(np.float32), p["cam"], 3)
+    for l in range(3):
+        ref, got = f0.level(l), ctx.download(9, l)
+        assert np.array_equal(got["I"], ref["I"]) and np.array_equal(got["Z"].astype(np.float64), ref["Z"]), l
+
+
 @pytest.mark.parametrize("depth_kind,bgr", [("u16", False), ("f32", True), ("f64", False)])
 def test_rgbd_ingestion_matches_the_node(ctx, oracle, synth, depth_kind, bgr):
     """RGB -> grey, depth factor and NaN -> 0 fused into the upload (NodeRgbdAlignment.cpp:177-199),
@@ -450,3 +460,39 @@ def test_large_batch_two_stream_path_matches_oracle(capi, oracle, synth, level_k
         for key in ("2", "5", "default"):
             assert np.array_equal(got[key][k]["pose"], got["1"][k]["pose"]), (key, k)
             assert list(got[key][k]["iters"]) == list(got["1"][k]["iters"]), (key, k)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("model,period", [("ConstantMotion", 3), ("NoMotion", 2)])
+def test_cpp_odometry_mirror_matches_the_oracle_loop(oracle, synth, capi, tmp_path, model, period):
+    """OdometryRgbd + Map rings + KeyFrameSelectionIdx + MotionPrediction of
+    include/vslam_b200_odometry.hpp, driven like NodeRgbdAlignment::processFrame over a rendered sequence; every
+    pose and speed equals oracle/odometry.py's on the same frames (single and stacked alignments, prior on)."""
+    import subprocess
+    from vslam_b200 import build
+    from oracle import odometry as OD
+    O = oracle
+    exe = build.build_odometry_mirror()
+    W, H, F, L = 320, 240, 9, 3
+    traj = tmp_path / "trajectory.txt"
+    r = subprocess.run([exe, str(W), str(H), str(F), str(L), str(period), model, str(traj)], capture_output=True, text=True,
+                       timeout=600)
+    assert r.returncode == 0, r.stderr
+    rows = [ln.split() for ln in r.stdout.strip().splitlines()]
+    assert rows[-1] == ["ok"]
+    got_pose = {int(x[1]): np.array([float(v) for v in x[2:]]) for x in rows if x[0] == "pose"}
+    got_speed = {int(x[1]): np.array([float(v) for v in x[2:]]) for x in rows if x[0] == "speed"}
+    got_kind = {int(x[1]): x[2] for x in rows if x[0] == "kind"}
+    cam = synth.cam_for(W, H)
+    gray, depth, _ = synth.make_sequence(F, W, H, seed=1234, cam=cam)
+    frames = [O.Frame(gray[k], depth[k].astype(np.float64), *cam, L) for k in range(F)]
+    stamps = [1000000000 + k * 33333333 for k in range(F)]
+    cfg = O.make_config(max_iterations=50, include_prior=True)
+    poses, speeds, kinds = OD.run(cfg, frames, stamps, prediction=model, kf_period=period)
+    assert [got_kind[k] for k in range(F)] == kinds and "stacked" in kinds and "single" in kinds
+    for k in range(F):
+        dt, dr = pose_err(O, got_pose[k], poses[k])
+        assert dt < POSE_TOL and dr < POSE_TOL, k
+        dt, dr = pose_err(O, got_speed[k], O.se3_exp(speeds[k]))
+        assert dt < 30 * POSE_TOL and dr < 30 * POSE_TOL, k       # speed = log(relative pose) / 0.0333 s
+    assert len(traj.read_text().splitlines()) == 3 + F

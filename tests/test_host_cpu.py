@@ -175,3 +175,47 @@ def test_cpp_host_mirror_builds_and_fails_loudly_without_a_gpu(capi):
     r = subprocess.run([exe, "160", "120", "5", "2"], capture_output=True, text=True, timeout=120)
     assert r.returncode == 3, (r.returncode, r.stderr)
     assert "no CPU fallback" in r.stderr
+
+
+def test_odometry_host_mirror_algebra_rings_prediction_and_trajectory_files(oracle, tmp_path):
+    """include/vslam_b200_odometry.hpp without a GPU (tests/cpp/host_algebra.cpp): SE3 closed forms against the
+    oracle's, Map rings (Map.cpp:19-33), KeyFrameSelectionIdx (KeyFrameSelection.h:36-51), constant-motion prediction
+    (MotionPrediction.cpp:38-55) against oracle/odometry.py, TUM trajectory files (utils.cpp:76-117,134-163)."""
+    import subprocess
+    from vslam_b200 import build
+    from oracle import odometry as OD
+    O = oracle
+    exe = build.build_host_algebra()
+    gt = tmp_path / "groundtruth.txt"
+    gt.write_text("# ground truth trajectory\n# timestamp tx ty tz qx qy qz qw\n"
+                  "1305031102.1758 1.3405 0.6266 1.6575 0.6574 0.6126 -0.2949 -0.3248\n"
+                  "1305031102.2758 1.5 -0.25 0.125 0 0 0 1\n")
+    out = tmp_path / "algo.txt"
+    x = np.array([0.01, -0.02, 0.03, 0.1, -0.2, 0.05])
+    y = np.array([-0.02, 0.01, 0.0, 0.0, 0.02, -0.01])
+    r = subprocess.run([exe, str(gt), str(out)] + [repr(float(v)) for v in np.concatenate([x, y])],
+                       capture_output=True, text=True, timeout=60)
+    assert r.returncode == 0, r.stderr
+    rows = [ln.split() for ln in r.stdout.strip().splitlines()]
+    val = {row[0]: np.array([float(v) for v in row[1:]]) for row in rows if row[0] != "stamp"}
+    X, Y = O.se3_exp(x), O.se3_exp(y)
+    assert np.allclose(val["expx"], X, atol=1e-14)
+    assert np.allclose(val["mul"], O.se3_mul(X, Y), atol=1e-14)
+    assert np.allclose(val["inv"], O.se3_inv(X), atol=1e-14)
+    assert np.allclose(val["rel"], O.se3_mul(Y, O.se3_inv(X)), atol=1e-14)     # algorithm.cpp:82-85: t1 * t0^-1
+    assert np.allclose(val["log"], O.se3_log(O.se3_mul(X, Y)), atol=1e-13)
+    assert list(val["kf"]) == [0, 0, 1] * 4                                      # period 3, counter starts at 1
+    assert list(val["rings"]) == [7, 4, 11, 11]                                 # 7 + 7 rings, newest first
+    pred = OD.MotionPredictionConstant()
+    pred.update(X, 1000000000)
+    pred.update(O.se3_mul(Y, X), 1500000000)
+    assert np.allclose(val["predict"], pred.predict(2500000000), atol=1e-13)
+    assert val["older"][0] == 1                                                  # "New timestamp is older than last one!"
+    stamps = [row for row in rows if row[0] == "stamp"]
+    assert [int(row[1]) for row in stamps] == [int(1305031102 * 1e9 + 1758 * 100000), int(1305031102 * 1e9 + 2758 * 100000)]
+    q = np.array([0.6574, 0.6126, -0.2949, -0.3248])
+    assert np.allclose([float(v) for v in stamps[0][2:6]], q / np.linalg.norm(q), atol=1e-15)
+    assert [float(v) for v in stamps[1][6:9]] == [1.5, -0.25, 0.125]
+    text = out.read_text().splitlines()
+    assert text[0] == "# Algorithm Trajectory" and text[2] == "# timestamp tx ty tz qx qy qz qw"
+    assert text[4].split()[1:] == ["1.5", "-0.25", "0.125", "0", "0", "0", "1"]

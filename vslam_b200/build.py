@@ -63,11 +63,44 @@ def build_host_mirror(force=False):
     return HOST_MIRROR
 
 
+ODOMETRY_MIRROR = os.path.join(LIBDIR, "odometry_mirror")
+
+
+def build_odometry_mirror(force=False):
+    """g++ build of tests/cpp/odometry_mirror.cpp: the C++ mirror of the odometry loop (include/vslam_b200_odometry.hpp)."""
+    root = os.path.join(_HERE, "..")
+    src = os.path.join(root, "tests", "cpp", "odometry_mirror.cpp")
+    inc = os.path.join(root, "include")
+    deps = [src] + [os.path.join(inc, h) for h in ("vslam_b200_odometry.hpp", "vslam_b200.hpp", "vslam_b200.h")]
+    if force or _stale(ODOMETRY_MIRROR, deps):
+        subprocess.check_call(["/usr/bin/g++", "-std=c++17", "-O2", "-Wall", "-Wextra", "-Werror", "-I", inc, src, "-o",
+                               ODOMETRY_MIRROR, "-L", LIBDIR, "-lvslam_b200", "-lvslam_synth", "-Wl,-rpath,$ORIGIN",
+                               "-lpthread"])
+    return ODOMETRY_MIRROR
+
+
+HOST_ALGEBRA = os.path.join(LIBDIR, "host_algebra")
+
+
+def build_host_algebra(force=False):
+    """g++ build of tests/cpp/host_algebra.cpp (host-only parts of include/vslam_b200_odometry.hpp; no GPU needed)."""
+    root = os.path.join(_HERE, "..")
+    src = os.path.join(root, "tests", "cpp", "host_algebra.cpp")
+    inc = os.path.join(root, "include")
+    deps = [src] + [os.path.join(inc, h) for h in ("vslam_b200_odometry.hpp", "vslam_b200.hpp", "vslam_b200.h")]
+    if force or _stale(HOST_ALGEBRA, deps):
+        subprocess.check_call(["/usr/bin/g++", "-std=c++17", "-O2", "-Wall", "-Wextra", "-Werror", "-I", inc, src, "-o",
+                               HOST_ALGEBRA, "-L", LIBDIR, "-lvslam_b200", "-Wl,-rpath,$ORIGIN", "-lpthread"])
+    return HOST_ALGEBRA
+
+
 def build_all(force=False):
     from . import synth
     synth.build(force)
     lib = build_cuda(force)
     build_host_mirror(force)
+    build_odometry_mirror(force)
+    build_host_algebra(force)
     return lib
 
 

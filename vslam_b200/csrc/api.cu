@@ -475,7 +475,7 @@ int vslamb200_frames_upload(
   if (!depthStride) depthStride = npx * dsz;
   // frames of one call live in one arena with a constant stride
   const vb::FrameDev & f0 = c->frames[slots[0]].dev;
-  const size_t frameStride = n > 1 ? (size_t)((uint8_t *)c->frames[slots[1]].dev.I[0] - (uint8_t *)f0.I[0]) : npx;
+  const size_t frameStride = n > 1 ? (size_t)((uint8_t *)c->frames[slots[1]].dev.I[0] - (uint8_t *)f0.I[0]) : npx * 4;  // one frame: any pitch >= the widest row copied
   const bool direct = layout == VSLAMB200_ROW_MAJOR && depthType == VSLAMB200_DEPTH_F32;
   if (direct) {
     CK(cudaMemcpy2DAsync(f0.I[0], frameStride, gray, grayStride, npx, n, cudaMemcpyHostToDevice, c->stream));
@@ -515,7 +515,7 @@ int vslamb200_frames_upload_async(
   if (!grayStride) grayStride = npx;
   if (!depthStride) depthStride = npx * 4;
   const vb::FrameDev & f0 = c->frames[slots[0]].dev;
-  const size_t frameStride = n > 1 ? (size_t)((uint8_t *)c->frames[slots[1]].dev.I[0] - (uint8_t *)f0.I[0]) : npx;
+  const size_t frameStride = n > 1 ? (size_t)((uint8_t *)c->frames[slots[1]].dev.I[0] - (uint8_t *)f0.I[0]) : npx * 4;  // one frame: any pitch >= the widest row copied
   // the copy may land in a recycled arena: order it after the compute work issued so far, not after what follows
   CK(cudaEventRecord(c->computeMark, c->stream));
   CK(cudaStreamWaitEvent(c->copyStream, c->computeMark, 0));
@@ -542,7 +542,7 @@ int vslamb200_frames_upload_device(
   if (int e = make_frames(c, n, ids, W, H, cams, nLevels, slots)) return e;
   const size_t npx = (size_t)W * H;
   const vb::FrameDev & f0 = c->frames[slots[0]].dev;
-  const size_t frameStride = n > 1 ? (size_t)((uint8_t *)c->frames[slots[1]].dev.I[0] - (uint8_t *)f0.I[0]) : npx;
+  const size_t frameStride = n > 1 ? (size_t)((uint8_t *)c->frames[slots[1]].dev.I[0] - (uint8_t *)f0.I[0]) : npx * 4;  // one frame: any pitch >= the widest row copied
   CK(cudaMemcpy2DAsync(f0.I[0], frameStride, dGray, npx, npx, n, cudaMemcpyDeviceToDevice, c->stream));
   CK(cudaMemcpy2DAsync(f0.Z[0], frameStride, dDepth, npx * 4, npx * 4, n, cudaMemcpyDeviceToDevice, c->stream));
   return preprocess(c, slots, nLevels, true, c->stream);
