@@ -496,3 +496,34 @@ def test_cpp_odometry_mirror_matches_the_oracle_loop(oracle, synth, capi, tmp_pa
         dt, dr = pose_err(O, got_speed[k], O.se3_exp(speeds[k]))
         assert dt < 30 * POSE_TOL and dr < 30 * POSE_TOL, k       # speed = log(relative pose) / 0.0333 s
     assert len(traj.read_text().splitlines()) == 3 + F
+
+
+@pytest.mark.gpu
+def test_sequence_trajectory_rpe_and_ate_against_ground_truth(capi, oracle, synth, tmp_path):
+    """BASELINE configs[1] in small, end to end on both sides of the path: a rendered 40-frame sequence, frame-to-frame
+    alignment of all pairs in one batched call, relative poses chained into a trajectory (vslam_b200/shard.py),
+    written as TUM files and scored with the RPE / ATE of the reference's evaluation scripts
+    (vslam_b200/evaluation.py).  The bounds are the CPU oracle's figures on the same sequence (RPE 4.6 mm / 1.9 mrad per
+    frame at 320x240 and 3 levels, ATE 25 mm over 40 frames) plus head-room; the reference's own tests ask < 0.01 per pair."""
+    from vslam_b200 import evaluation as E, shard
+    F, W, H, L = 40, 320, 240, 3
+    cam = synth.cam_for(W, H)
+    gray, depth, gt = synth.make_sequence(F, W, H, seed=1234, cam=cam)
+    ident = oracle.IDENTITY
+    ctx = capi.Context(capi.make_config())
+    try:
+        ctx.upload(np.arange(F), gray, depth, cam, L)
+        res = ctx.align([dict(to=i + 1, to_pose=ident, frm=[i], from_poses=ident, multi=False) for i in range(F - 1)])
+    finally:
+        ctx.close()
+    traj = shard.chain_trajectory(np.stack([r["pose"] for r in res]))
+    stamps = 1305031100.0 + np.arange(F) / 30.0
+    E.write_trajectory(str(tmp_path / "est.txt"), stamps, traj)
+    E.write_trajectory(str(tmp_path / "gt.txt"), stamps, gt)
+    tg, te = E.read_trajectory(str(tmp_path / "gt.txt")), E.read_trajectory(str(tmp_path / "est.txt"))
+    rpe = E.relative_pose_error(tg, te, 1, "f")
+    assert len(rpe) == F - 2                                         # the script leaves out pairs ending at the last pose
+    assert E.stats(rpe[:, 4])["rmse"] < 0.006 and E.stats(rpe[:, 5])["rmse"] < 0.003
+    assert E.stats(rpe[:, 4])["max"] < 0.01
+    ate = E.absolute_trajectory_error(tg, te)
+    assert len(ate["matches"]) == F and ate["rmse"] < 0.035
