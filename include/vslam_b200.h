@@ -43,6 +43,9 @@ enum { VSLAMB200_STOP_MAXITER = 0, VSLAMB200_STOP_CONSTRAINTS = 1, VSLAMB200_STO
 enum { VSLAMB200_ROW_MAJOR = 0, VSLAMB200_COL_MAJOR = 1 };   /* COL_MAJOR == Eigen default (core/src/types.h:33-35) */
 enum { VSLAMB200_DEPTH_F32 = 0, VSLAMB200_DEPTH_F64 = 1, VSLAMB200_DEPTH_U16 = 2 /* frames_ingest_rgbd only */ };
 enum { VSLAMB200_RGB = 0, VSLAMB200_BGR = 1 };
+/* solver_kind: Gauss-Newton is the reference's solver (least_squares/src/GaussNewton.cpp); Levenberg-Marquardt is an
+ * EXTENSION named by the benchmark configurations (no counterpart in the reference; defined by oracle/vslam_oracle.cpp) */
+enum { VSLAMB200_SOLVER_GN = 0, VSLAMB200_SOLVER_LM = 1 };
 
 typedef struct vslamb200_ctx vslamb200_ctx;
 
@@ -58,6 +61,10 @@ typedef struct vslamb200_config
   double min_step_size;  /* GaussNewton.cpp:24-29: also min gradient and min chi2 reduction */
   int max_iterations;    /* GaussNewton.h:35 */
   int include_prior;     /* MotionPrior (SE3Alignment.cpp:27-52) */
+  int solver_kind;       /* VSLAMB200_SOLVER_* */
+  double lm_lambda0;     /* LM only: initial damping of (A + lambda diag A) dx = b */
+  double lm_up;          /* LM only: lambda *= lm_up after a rejected step (> 1) */
+  double lm_down;        /* LM only: lambda *= lm_down after an accepted step (0 < lm_down <= 1) */
 } vslamb200_config;
 
 /* One alignment: SE3Alignment::align(from, to) (n_from == 1, multi == 0) or the vector overload (multi != 0).

@@ -262,6 +262,10 @@ public:
   virtual ~Solver() = default;
   virtual double minStepSize() const = 0;
   virtual size_t maxIterations() const = 0;
+  virtual int kind() const { return VSLAMB200_SOLVER_GN; }
+  virtual double lambda0() const { return 1e-3; }
+  virtual double up() const { return 10.0; }
+  virtual double down() const { return 0.1; }
 };
 class GaussNewton : public Solver
 {
@@ -273,6 +277,23 @@ public:
 private:
   double _minStepSize;
   size_t _maxIterations;
+};
+// EXTENSION (no counterpart in the reference): Levenberg-Marquardt damping on the same normal equations,
+// (A + lambda diag A) dx = b; lambda *= up after a rejected step, *= down after an accepted one.
+class LevenbergMarquardt : public GaussNewton
+{
+public:
+  LevenbergMarquardt(double minStepSize, size_t maxIterations, double lambda0 = 1e-3, double up = 10.0, double down = 0.1)
+  : GaussNewton(minStepSize, maxIterations), _lambda0(lambda0), _up(up), _down(down)
+  {
+  }
+  int kind() const override { return VSLAMB200_SOLVER_LM; }
+  double lambda0() const override { return _lambda0; }
+  double up() const override { return _up; }
+  double down() const override { return _down; }
+
+private:
+  double _lambda0, _up, _down;
 };
 }  // namespace least_squares
 
@@ -313,6 +334,10 @@ public:
     cfg.min_step_size = _solver->minStepSize();
     cfg.max_iterations = (int)_solver->maxIterations();
     cfg.include_prior = includePrior ? 1 : 0;
+    cfg.solver_kind = _solver->kind();
+    cfg.lm_lambda0 = _solver->lambda0();
+    cfg.lm_up = _solver->up();
+    cfg.lm_down = _solver->down();
     check(vslamb200_create(&cfg, device, &_ctx));
   }
   ~SE3Alignment() override { vslamb200_destroy(_ctx); }

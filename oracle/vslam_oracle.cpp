@@ -561,6 +561,10 @@ struct Config
   int maxIterations;
   int includePrior;
   int f32Storage;
+  // EXTENSION (no counterpart in the reference): solver 0 = Gauss-Newton (GaussNewton.cpp),
+  // 1 = Levenberg-Marquardt damping on the same normal equations
+  int solverKind;
+  double lmLambda0, lmUp, lmDown;
 };
 
 struct Scale
@@ -955,6 +959,100 @@ static SolveResult gauss_newton(
 }
 
 // ------------------------------------------------------------------------------------------
+// EXTENSION: Levenberg-Marquardt on the same problem (named by BASELINE.json's configs[3]; the reference has no LM
+// solver, so this restatement IS the definition - parity unpinned).  Per evaluation i:
+//   ne = normal equations at the current pose (normalised, prior-augmented, exactly as for Gauss-Newton)
+//   worse than the accepted state (chi2 > chi2_acc):  reject - pose <- accepted pose, lambda *= up (stop at 1e12)
+//   else: accept - (A, b, chi2, pose)_acc <- current, lambda <- max(lambda * down, 1e-12) from the second accept on;
+//         converged when |chi2 - chi2_acc_before| < minStepSize
+//   dx = ldlt(A_acc + lambda diag(A_acc))^-1 b_acc;  se3 <- se3_acc * exp(-dx);  converged when |dx| < minStepSize
+// The covariance is the inverse of the last accepted, undamped A (as SE3Alignment.cpp:101 does for Gauss-Newton).
+// trace slot 60 holds lambda.
+// ------------------------------------------------------------------------------------------
+static SolveResult levenberg_marquardt(std::vector<View> & views, const Config & cfg, bool stacked, double * trace)
+{
+  SolveResult res;
+  double lambda = cfg.lmLambda0, chi2Acc = 0.0;
+  bool accepted = false;
+  Mat6 Aacc;
+  Vec6 bacc;
+  NE neAcc;
+  std::vector<SE3> se3Acc(views.size());
+  for (int i = 0; i < cfg.maxIterations; i++) {
+    NE ne = stacked_normal_equations(views, cfg, stacked);
+    if (ne.n < 6) {
+      res.stop = STOP_CONSTRAINTS;
+      break;
+    }
+    if (accepted && ne.chi2 > chi2Acc) {
+      for (size_t k = 0; k < views.size(); k++) views[k].se3 = se3Acc[k];
+      lambda *= cfg.lmUp;
+      if (lambda > 1e12) {
+        res.stop = STOP_CONVERGED;
+        break;
+      }
+    } else {
+      const bool converged = accepted && std::fabs(ne.chi2 - chi2Acc) < cfg.minStepSize;
+      if (accepted) lambda = std::max(lambda * cfg.lmDown, 1e-12);
+      Aacc = ne.A;
+      bacc = ne.b;
+      chi2Acc = ne.chi2;
+      neAcc = ne;
+      for (size_t k = 0; k < views.size(); k++) se3Acc[k] = views[k].se3;
+      accepted = true;
+      res.last = ne;
+      if (converged) {
+        res.iteration = std::max(res.iteration, 0);
+        res.stop = STOP_CONVERGED;
+        break;
+      }
+    }
+    Mat6 D = Aacc;
+    for (int k = 0; k < 6; k++) D(k, k) += lambda * Aacc(k, k);
+    const double det = det6(D);
+    if (!std::isfinite(det) || std::fabs(det) < 1e-6) {
+      res.stop = STOP_HESSIAN;
+      break;
+    }
+    const Vec6 dx = ldlt_solve(D, bacc);
+    Vec6 mdx;
+    for (int k = 0; k < 6; k++) mdx[k] = -dx[k];
+    const SE3 inc = se3_exp(mdx);
+    for (size_t k = 0; k < views.size(); k++) views[k].se3 = se3_mul(se3Acc[k], inc);
+    double nrm = 0;
+    for (int k = 0; k < 6; k++) nrm += dx[k] * dx[k];
+    const double step = std::sqrt(nrm);
+    res.iteration = i;
+    res.nPushed++;
+    if (trace) {
+      double * t = trace + (size_t)i * TRACE_STRIDE;
+      const Vec6 x = se3_log(views[0].se3);
+      t[0] = 1;
+      t[1] = (double)neAcc.n;
+      t[2] = chi2Acc;
+      t[3] = step;
+      t[4] = neAcc.scale;
+      t[5] = neAcc.offset;
+      for (int k = 0; k < 6; k++) t[6 + k] = x[k];
+      for (int k = 0; k < 6; k++) t[12 + k] = bacc[k];
+      for (int k = 0; k < 36; k++) t[18 + k] = Aacc.a[k];
+      for (int k = 0; k < 6; k++) t[54 + k] = dx[k];
+      t[60] = lambda;
+    }
+    if (!std::isfinite(step)) {
+      for (size_t k = 0; k < views.size(); k++) views[k].se3 = se3Acc[k];
+      res.stop = STOP_NAN;
+      break;
+    }
+    if (step < cfg.minStepSize) {
+      res.stop = STOP_CONVERGED;
+      break;
+    }
+  }
+  return res;
+}
+
+// ------------------------------------------------------------------------------------------
 // SE3Alignment::align, single (SE3Alignment.cpp:64-105) and multi keyframe (:106-146)
 // ------------------------------------------------------------------------------------------
 struct AlignOut
@@ -984,7 +1082,8 @@ static AlignOut align(
       views[k].hasPrior = cfg.includePrior != 0;
       views[k].xPred = xPred[k];
     }
-    SolveResult r = gauss_newton(views, cfg, multi, trace ? trace + (size_t)level * cfg.maxIterations * TRACE_STRIDE : nullptr);
+    double * tr = trace ? trace + (size_t)level * cfg.maxIterations * TRACE_STRIDE : nullptr;
+    SolveResult r = cfg.solverKind == 1 ? levenberg_marquardt(views, cfg, multi, tr) : gauss_newton(views, cfg, multi, tr);
     out.iters[level] = r.nPushed;
     out.stop[level] = r.stop;
     if (r.iteration < 0) {
@@ -1018,12 +1117,15 @@ struct vo_config
   int max_iterations;
   int include_prior;
   int f32_storage;
+  int solver_kind;
+  double lm_lambda0, lm_up, lm_down;
 };
 
 static vo::Config to_cfg(const vo_config * c)
 {
   return {c->min_gradient, c->loss_kind, c->huber_c, c->loss_v, c->scaler_kind, c->scaler_v,
-          c->min_step_size, c->max_iterations, c->include_prior, c->f32_storage};
+          c->min_step_size, c->max_iterations, c->include_prior, c->f32_storage, c->solver_kind, c->lm_lambda0, c->lm_up,
+          c->lm_down};
 }
 static vo::SE3 to_se3(const double * p)
 {

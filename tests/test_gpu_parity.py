@@ -527,3 +527,53 @@ def test_sequence_trajectory_rpe_and_ate_against_ground_truth(capi, oracle, synt
     assert E.stats(rpe[:, 4])["max"] < 0.01
     ate = E.absolute_trajectory_error(tg, te)
     assert len(ate["matches"]) == F and ate["rmse"] < 0.035
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("W,H,L,K,prior", [(640, 480, 4, 1, False), (1232, 368, 5, 1, False), (320, 240, 3, 2, True)])
+def test_levenberg_marquardt_extension_matches_oracle(ctx, capi, oracle, synth, W, H, L, K, prior):
+    """SURVEY 8(f)-3 / BASELINE configs[3] ("LM solver"): Levenberg-Marquardt damping on the reference's normal
+    equations.  The reference has no LM solver: oracle/vslam_oracle.cpp (levenberg_marquardt) is the definition, parity
+    is GPU <-> that restatement - every evaluation's accepted A, b, lambda and step, the stop reasons and the pose."""
+    O, A = oracle, capi
+    cam = synth.cam_for(W, H)
+    rng = np.random.default_rng(11)
+    xis = [np.zeros(6)] + [np.concatenate([rng.uniform(-0.02, 0.02, 3), rng.uniform(-0.01, 0.01, 3)]) for _ in range(K)]
+    frames, poses, raw = [], [], []
+    for xi in xis:
+        R, t = synth.se3_exp(xi)
+        g, d = synth.render(W, H, cam, R, t, scene_seed=4004)
+        raw.append((g, d))
+        frames.append(O.Frame(g, d.astype(np.float64), *cam, L))
+        poses.append(synth.pose7(R, t))
+    ctx.upload(np.arange(K + 1), np.stack([g for g, _ in raw]), np.stack([d for _, d in raw]), cam, L)
+    kw = dict(max_iterations=40, include_prior=prior, lm_lambda0=1e-2, lm_up=8.0, lm_down=0.25)
+    ocfg = O.make_config(solver=O.SOLVER_LM, **kw)
+    ctx.set_config(A.make_config(solver=A.SOLVER_LM, **kw))
+    ctx.set_trace(True)
+    multi = K > 1
+    # keyframes 0..K-1 at their true poses, the last frame is the target and starts at keyframe 0's pose
+    ref = O.align(ocfg, frames[:K] if multi else frames[0], poses[:K] if multi else poses[0], frames[K], poses[0],
+                  multi=multi, want_trace=True)
+    got = ctx.align([dict(to=K, to_pose=poses[0], frm=list(range(K)), from_poses=np.stack(poses[:K]), multi=multi)])[0]
+    tr = ctx.get_trace(0, L)
+    assert got["status"] == ref["status"] == 0
+    assert list(got["iters"][:L]) == list(ref["iters"]), (got["iters"], ref["iters"])
+    assert list(got["stop"][:L]) == list(ref["stop"])
+    rejected = 0
+    for l in range(L):
+        for i in range(ref["iters"][l]):
+            a, b = tr[l, i], ref["trace"][l, i]
+            assert a[0] == b[0] == 1
+            assert rel_fro(a[18:54], b[18:54]) < NE_TOL and rel_fro(a[12:18], b[12:18]) < NE_TOL, (l, i)
+            assert abs(a[60] - b[60]) <= 1e-12 * b[60], (l, i)                      # lambda
+            assert np.allclose(a[54:60], b[54:60], rtol=1e-6, atol=1e-12), (l, i)     # the damped step
+            if i > 0 and b[60] > ref["trace"][l, i - 1][60]:
+                rejected += 1
+    assert rejected > 0, "the case never exercised a rejected step"
+    dt, dr = pose_err(O, got["pose"], ref["pose"])
+    assert dt < POSE_TOL and dr < POSE_TOL
+    assert rel_fro(got["cov"], ref["cov"]) < 1e-3
+    if not prior:
+        dt, dr = pose_err(O, got["pose"], poses[K])
+        assert dt < 0.01 and dr < 0.01

@@ -209,3 +209,41 @@ def test_trace_is_consistent_with_evaluate(oracle, synth):
         assert sum(res["iters"]) >= 4
         _teacher_forced_check(oracle, cfg, [f0], [oracle.IDENTITY], f1, oracle.IDENTITY, False, res["trace"],
                               res["iters"], prior, L)
+
+
+def test_levenberg_marquardt_extension(oracle, synth):
+    """The LM extension's own contract (oracle/vslam_oracle.cpp, levenberg_marquardt): accepted chi2 never increases
+    within a level, lambda grows by `up` exactly when a step is rejected and shrinks by `down` otherwise, the damped
+    step solves (A + lambda diag A) dx = b, and the alignment still recovers the rendered motion."""
+    O = oracle
+    p = synth.make_pair(320, 240, 1234)
+    L = 3
+    f0 = O.Frame(p["gray0"], p["depth0"].astype(np.float64), *p["cam"], L)
+    f1 = O.Frame(p["gray1"], p["depth1"].astype(np.float64), *p["cam"], L)
+    cfg = O.make_config(solver=O.SOLVER_LM, max_iterations=40, lm_lambda0=1e-2, lm_up=8.0, lm_down=0.25)
+    r = O.align(cfg, f0, O.IDENTITY, f1, O.IDENTITY, want_trace=True)
+    assert r["status"] == 0
+    ups = downs = 0
+    for l in range(L):
+        n = r["iters"][l]
+        assert n > 0
+        chi2, lam = r["trace"][l, :n, 2], r["trace"][l, :n, 60]
+        assert np.all(np.diff(chi2) <= 0)                       # chi2 of the accepted state
+        assert lam[0] == 1e-2
+        for i in range(1, n):
+            if chi2[i] == chi2[i - 1] and lam[i] > lam[i - 1]:
+                assert np.isclose(lam[i], lam[i - 1] * 8.0)
+                ups += 1
+            else:
+                assert np.isclose(lam[i], max(lam[i - 1] * 0.25, 1e-12))
+                downs += 1
+        for i in range(n):
+            t = r["trace"][l, i]
+            A, b, dx = t[18:54].reshape(6, 6), t[12:18], t[54:60]
+            assert np.allclose((A + t[60] * np.diag(np.diag(A))) @ dx, b, rtol=1e-9, atol=1e-12)
+    assert ups > 0 and downs > 0
+    d = O.se3_log(O.se3_mul(r["pose"], O.se3_inv(p["pose1"])))
+    assert np.linalg.norm(d[:3]) < 0.01 and np.linalg.norm(d[3:]) < 0.01
+    gn = O.align(O.make_config(max_iterations=40), f0, O.IDENTITY, f1, O.IDENTITY)
+    d = O.se3_log(O.se3_mul(r["pose"], O.se3_inv(gn["pose"])))
+    assert np.linalg.norm(d) < 5e-3                             # both solvers end in the same basin

@@ -15,6 +15,7 @@ SCALER_IDENTITY, SCALER_MEDIAN, SCALER_MEAN, SCALER_TDIST = range(4)
 ROW_MAJOR, COL_MAJOR = 0, 1
 DEPTH_F32, DEPTH_F64, DEPTH_U16 = 0, 1, 2
 RGB, BGR = 0, 1
+SOLVER_GN, SOLVER_LM = 0, 1
 R_NOT_INTEREST, R_INVISIBLE = -32768, -32767
 STOP_NAMES = ["maxiter", "constraints", "hessian", "chi2", "converged", "nan"]
 
@@ -22,7 +23,8 @@ STOP_NAMES = ["maxiter", "constraints", "hessian", "chi2", "converged", "nan"]
 class Config(C.Structure):
     _fields_ = [("min_gradient", C.c_double), ("loss_kind", C.c_int), ("huber_c", C.c_double),
                 ("loss_v", C.c_double), ("scaler_kind", C.c_int), ("scaler_v", C.c_double),
-                ("min_step_size", C.c_double), ("max_iterations", C.c_int), ("include_prior", C.c_int)]
+                ("min_step_size", C.c_double), ("max_iterations", C.c_int), ("include_prior", C.c_int),
+                ("solver_kind", C.c_int), ("lm_lambda0", C.c_double), ("lm_up", C.c_double), ("lm_down", C.c_double)]
 
 
 class Job(C.Structure):
@@ -106,8 +108,10 @@ def ptr(a):
 
 
 def make_config(min_gradient=30.0, loss=LOSS_TDIST, scaler=SCALER_TDIST, huber_c=1.345, v=5.0,
-                min_step_size=1e-7, max_iterations=100, include_prior=False):
-    return Config(min_gradient, loss, huber_c, v, scaler, v, min_step_size, max_iterations, int(include_prior))
+                min_step_size=1e-7, max_iterations=100, include_prior=False, solver=SOLVER_GN, lm_lambda0=1e-3,
+                lm_up=10.0, lm_down=0.1):
+    return Config(min_gradient, loss, huber_c, v, scaler, v, min_step_size, max_iterations, int(include_prior), solver,
+                  lm_lambda0, lm_up, lm_down)
 
 
 class Context:

@@ -349,6 +349,11 @@ static int check_cfg(const vslamb200_config * cfg)
   if (cfg->loss_kind < 0 || cfg->loss_kind > VSLAMB200_LOSS_TDIST) return fail(VSLAMB200_EINVAL, "bad loss_kind");
   if (cfg->scaler_kind < 0 || cfg->scaler_kind > VSLAMB200_SCALER_TDIST) return fail(VSLAMB200_EINVAL, "bad scaler_kind");
   if (cfg->max_iterations < 1 || cfg->max_iterations > 100000) return fail(VSLAMB200_EINVAL, "bad max_iterations");
+  if (cfg->solver_kind != VSLAMB200_SOLVER_GN && cfg->solver_kind != VSLAMB200_SOLVER_LM)
+    return fail(VSLAMB200_EINVAL, "bad solver_kind");
+  if (cfg->solver_kind == VSLAMB200_SOLVER_LM &&
+      !(cfg->lm_lambda0 > 0.0 && cfg->lm_up > 1.0 && cfg->lm_down > 0.0 && cfg->lm_down <= 1.0))
+    return fail(VSLAMB200_EINVAL, "bad Levenberg-Marquardt parameters (lambda0 > 0, up > 1, 0 < down <= 1)");
   return 0;
 }
 
@@ -664,6 +669,10 @@ vb::SolverParams solver_params(const vslamb200_config & cfg)
   p.minStepSize = cfg.min_step_size;
   p.maxIterations = cfg.max_iterations;
   p.includePrior = cfg.include_prior;
+  p.solverKind = cfg.solver_kind;
+  p.lmLambda0 = cfg.lm_lambda0;
+  p.lmUp = cfg.lm_up;
+  p.lmDown = cfg.lm_down;
   return p;
 }
 
@@ -757,7 +766,7 @@ bool use_incremental(const Problem & P, const vb::SolverParams & sp, int npx)
 {
   int mode = 0;
   if (const char * e = std::getenv("VSLAMB200_INC")) mode = std::atoi(e);
-  if (mode <= 0 || P.maxViews != 1 || npx > (1 << 20)) return false;
+  if (mode <= 0 || P.maxViews != 1 || npx > (1 << 20) || sp.solverKind != VSLAMB200_SOLVER_GN) return false;
   if (sp.scalerKind != VSLAMB200_SCALER_IDENTITY && sp.scalerKind != VSLAMB200_SCALER_TDIST) return false;
   return mode >= 2 || npx >= 50000;
 }

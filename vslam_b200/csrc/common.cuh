@@ -69,6 +69,7 @@ struct ViewState
   float epsA, epsB;         // per-view terms of the fast-path error bound
   double xPred[6];          // MotionPrior::_xPred (SE3Alignment.cpp:32)
   double xCur[6];           // log(se3), kept in step with se3
+  Pose se3Acc;              // Levenberg-Marquardt: se3 at the last accepted evaluation
   // robust weights of the current iteration
   // incremental kernel (gn_inc.cu): per point the value of the tile's cumulative motion bound at which the point has to
   // be re-evaluated; per LIST_TILE 8 floats: u, v, 1/depth ranges of the tile's points, cumulative motion bound, spare
@@ -89,6 +90,9 @@ struct JobState
   double lastA[36];
   double xPrev[6];
   double chi2Prev;
+  // Levenberg-Marquardt (extension): damping, b and chi2 of the last accepted evaluation (its A is lastA)
+  double lambda, bAcc[6], chi2Acc;
+  int accepted, lmPad;
   int iter;                 // Gauss-Newton iteration index within the level
   int nPushed;              // completed steps within the level
   int active;               // 1 while the level's solve is running
@@ -114,6 +118,8 @@ struct SolverParams
   double minStepSize;
   int maxIterations;
   int includePrior;
+  int solverKind;            // VSLAMB200_SOLVER_*
+  double lmLambda0, lmUp, lmDown;
 };
 
 // ------------------------------------------------------------------------------------------------

@@ -573,7 +573,7 @@ __global__ void __launch_bounds__(NT, CTAS_PER_SM) gn_inc_kernel(
       S.J.evals[level]++;
       S.J.pointIters += (unsigned long long)S.J.totalPoints;
     }
-    gn_step_block(S.J, &S.V, S.sums, S.X, p, level, trace ? trace + (size_t)job * traceJobStride : nullptr, evals >= maxEvals);
+    solver_step_block(S.J, &S.V, S.sums, S.X, p, level, trace ? trace + (size_t)job * traceJobStride : nullptr, evals >= maxEvals);
     if (!S.J.active) break;
     if (tid == 0) {
       double Rinc[9];

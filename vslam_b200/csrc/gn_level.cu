@@ -601,7 +601,7 @@ __global__ void __launch_bounds__(GT, CTAS_PER_SM) gn_level_kernel(
       S.J.evals[level]++;
       S.J.pointIters += (unsigned long long)S.J.totalPoints;
     }
-    gn_step_block(S.J, Vs, sums, S.X, p, level, (trace && rank == 0) ? trace + (size_t)job * traceJobStride : nullptr,
+    solver_step_block(S.J, Vs, sums, S.X, p, level, (trace && rank == 0) ? trace + (size_t)job * traceJobStride : nullptr,
                   evals >= maxEvals);
     lap(6);
     if (!S.J.active) break;

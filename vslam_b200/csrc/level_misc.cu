@@ -57,6 +57,8 @@ __global__ void level_setup_kernel(
     J.iter = 0;
     J.nPushed = 0;
     J.chi2Prev = 0.0;
+    J.accepted = 0;
+    J.chi2Acc = 0.0;
     J.active = J.dead ? 0 : 1;
     for (int k = 0; k < 6; k++) J.xPrev[k] = 0.0;
     J.evals[level] = 0;

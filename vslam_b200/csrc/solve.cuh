@@ -326,4 +326,174 @@ __device__ __forceinline__ void gn_step_block(
   }
   __syncthreads();
 }
+// ------------------------------------------------------------------------------------------------
+// EXTENSION: one Levenberg-Marquardt evaluation on the same stacked, normalised, prior-augmented normal equations
+// (oracle/vslam_oracle.cpp: levenberg_marquardt is the definition; the reference has no LM solver).  Same calling
+// convention as gn_step_block.  J.lastA / J.bAcc / J.chi2Acc / jv[k].se3Acc hold the last accepted evaluation.
+//   worse than the accepted state: reject (pose <- accepted pose, lambda *= up); else accept (lambda *= down from the
+//   second accept on); then dx = ldlt(A_acc + lambda diag A_acc)^-1 b_acc, se3 <- se3_acc * exp(-dx).
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void lm_step_block(
+  JobState & J, ViewState * jv, const double * sums, SolveScratch & X, const SolverParams & p, int level,
+  double * trace, bool forceStop)
+{
+  const int tid = threadIdx.x;
+  const int K = J.nViews;
+  // ---- 1. assemble (as gn_step_block)
+  if (tid < NE_TERMS) {
+    int di = -1, bi = -1;
+    {
+      int idx = 0;
+      for (int i = 0; i < 6; i++)
+        for (int j = i; j < 6; j++) {
+          if (idx == tid && i == j) di = i;
+          idx++;
+        }
+      if (tid >= 21 && tid < 27) bi = tid - 21;
+    }
+    double acc = 0.0;
+    long nTotal = 0;
+    for (int k = 0; k < K; k++) {
+      const ViewState & V = jv[k];
+      double v = sums[k * NE_TERMS + tid];
+      const long n = V.nIp;
+      if (n > 1) v /= (double)n;
+      if (p.includePrior && tid < 27) {
+        v *= 1.0 / (255.0 * 255.0);
+        if (di >= 0) v += 1.0;
+        if (bi >= 0) v += V.xPred[bi] - V.xCur[bi];
+      }
+      acc += v;
+      nTotal += n;
+    }
+    X.ne[tid] = acc;
+    if (tid == 0) X.nTotal = nTotal;
+  }
+  __syncthreads();
+  // ---- 2. accept / reject
+  const int it = J.iter;
+  if (tid == 0) {
+    if (it == 0) {
+      J.lambda = p.lmLambda0;
+      J.accepted = 0;
+    }
+    const double chi2 = X.ne[27];
+    int dec = -1, rej = 0;
+    if (X.nTotal < 6) {
+      dec = VSLAMB200_STOP_CONSTRAINTS;
+    } else if (J.accepted && chi2 > J.chi2Acc) {
+      rej = 1;
+      J.lambda *= p.lmUp;
+      if (J.lambda > 1e12) dec = VSLAMB200_STOP_CONVERGED;
+    } else {
+      const bool converged = J.accepted && fabs(chi2 - J.chi2Acc) < p.minStepSize;
+      if (J.accepted) J.lambda = fmax(J.lambda * p.lmDown, 1e-12);
+      int idx = 0;
+      for (int i = 0; i < 6; i++)
+        for (int j = i; j < 6; j++) {
+          J.lastA[i * 6 + j] = X.ne[idx];
+          J.lastA[j * 6 + i] = X.ne[idx];
+          idx++;
+        }
+      for (int i = 0; i < 6; i++) J.bAcc[i] = X.ne[21 + i];
+      J.chi2Acc = chi2;
+      J.accepted = 1;
+      if (converged) dec = VSLAMB200_STOP_CONVERGED;  // (a previous step exists: nPushed >= 1)
+    }
+    X.decision = dec;
+    X.dChi2 = (double)rej;
+  }
+  __syncthreads();
+  const bool rejected = X.dChi2 != 0.0;
+  if (tid < K) {
+    if (rejected)
+      jv[tid].se3 = jv[tid].se3Acc;
+    else
+      jv[tid].se3Acc = jv[tid].se3;
+  }
+  __syncthreads();
+  // ---- 3. damped solve (thread 0: determinant, thread 32: step)
+  if (X.decision < 0 && (tid == 0 || tid == 32)) {
+    double A[36];
+#pragma unroll
+    for (int i = 0; i < 36; i++) A[i] = J.lastA[i];
+#pragma unroll
+    for (int i = 0; i < 6; i++) A[i * 7] += J.lambda * J.lastA[i * 7];
+    if (tid == 0) {
+#pragma unroll
+      for (int i = 0; i < 36; i++) X.A[i] = J.lastA[i];
+      X.det = det6(A);
+    } else {
+      double b[6], dx[6], mdx[6];
+#pragma unroll
+      for (int i = 0; i < 6; i++) b[i] = J.bAcc[i];
+      ldlt_solve(A, b, dx);
+#pragma unroll
+      for (int i = 0; i < 6; i++) {
+        X.dx[i] = dx[i];
+        mdx[i] = -dx[i];
+      }
+      X.inc = se3_exp(mdx);
+    }
+  }
+  __syncthreads();
+  if (tid == 0 && X.decision < 0 && (!isfinite(X.det) || fabs(X.det) < 1e-6)) X.decision = VSLAMB200_STOP_HESSIAN;
+  __syncthreads();
+  if (X.decision < 0) {
+    if (tid < K) jv[tid].se3 = se3_mul(jv[tid].se3Acc, X.inc);
+    __syncthreads();
+  }
+  if (X.decision < 0 || rejected) {  // the pose changed (a step, or the roll-back of a rejected one that ends the level)
+    if (tid < K) se3_log(jv[tid].se3, jv[tid].xCur);
+    if (tid >= 32 && tid < 32 + K) view_set_warp(jv[tid - 32]);
+    __syncthreads();
+  }
+  // ---- 4. bookkeeping and stop rules
+  if (tid == 0) {
+    int stop = X.decision;
+    if (stop < 0) {
+      double nrm = 0;
+#pragma unroll
+      for (int k = 0; k < 6; k++) nrm += X.dx[k] * X.dx[k];
+      const double step = sqrt(nrm);
+      J.nPushed++;
+      if (trace) {
+        double * t = trace + ((size_t)level * p.maxIterations + it) * TRACE_STRIDE;
+        t[0] = 1;
+        t[1] = (double)X.nTotal;
+        t[2] = J.chi2Acc;
+        t[3] = step;
+        t[4] = jv[0].scale;
+        t[5] = jv[0].offset;
+        for (int k = 0; k < 6; k++) t[6 + k] = jv[0].xCur[k];
+        for (int k = 0; k < 6; k++) t[12 + k] = J.bAcc[k];
+        for (int k = 0; k < 36; k++) t[18 + k] = J.lastA[k];
+        for (int k = 0; k < 6; k++) t[54 + k] = X.dx[k];
+        t[60] = J.lambda;
+      }
+      if (!isfinite(step)) {
+        for (int k = 0; k < K; k++) jv[k].se3 = jv[k].se3Acc;
+        stop = VSLAMB200_STOP_NAN;
+      } else if (step < p.minStepSize) {
+        stop = VSLAMB200_STOP_CONVERGED;
+      } else {
+        J.iter = it + 1;
+        if (J.iter >= p.maxIterations || forceStop) stop = VSLAMB200_STOP_MAXITER;
+      }
+    }
+    if (stop >= 0) finish_level(J, jv, level, stop);
+  }
+  __syncthreads();
+}
+
+// the level kernels' single entry point
+__device__ __forceinline__ void solver_step_block(
+  JobState & J, ViewState * jv, const double * sums, SolveScratch & X, const SolverParams & p, int level,
+  double * trace, bool forceStop)
+{
+  if (p.solverKind == VSLAMB200_SOLVER_LM)
+    lm_step_block(J, jv, sums, X, p, level, trace, forceStop);
+  else
+    gn_step_block(J, jv, sums, X, p, level, trace, forceStop);
+}
 }  // namespace vb
