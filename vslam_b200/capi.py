@@ -6,7 +6,8 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libvslam_b200.so")
+# VSLAMB200_LIB: another build of the same library (A/B kernel experiments, tools/ab.sh)
+LIB_PATH = os.environ.get("VSLAMB200_LIB") or os.path.join(_HERE, "lib", "libvslam_b200.so")
 
 MAX_LEVELS = 8
 TRACE_STRIDE = 64

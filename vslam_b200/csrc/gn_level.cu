@@ -267,7 +267,8 @@ __device__ __forceinline__ void slice_of(int n, unsigned C, unsigned rank, int &
 // (item % NS) of that ring.  A warp refills a stage right after it has copied it into registers, so no warp ever
 // waits for another one (no "empty" barriers, no producer thread that can fall behind).
 __device__ __forceinline__ void issue_chunk(
-  LevelShared & S, unsigned char * ring, const ViewState & V, bool phaseC, int p0, int p1, int c, uint32_t item, int warp)
+  LevelShared & S, unsigned char * ring, const ViewState & V, bool phaseC, int p0, int p1, int c, uint32_t item, int warp,
+  uint64_t pol)
 {
   const int start = p0 + c * CH + warp * WCH;
   uint64_t * bar = &S.full[warp][item % NS];
@@ -277,7 +278,6 @@ __device__ __forceinline__ void issue_chunk(
   }
   unsigned char * st = ring + (size_t)(warp * NS + item % NS) * WSTAGE_BYTES;
   const unsigned char * tile = V.tiles + (size_t)(start / LIST_TILE) * LIST_TILE_BYTES;
-  const uint64_t pol = l2_evict_first_policy();
   if (phaseC) {
     mbar_expect_tx(bar, C_TILE_BYTES + C_R_BYTES);
     bulk_g2s_stream(st, tile + TILE_OFF_UVT, C_TILE_BYTES, bar, pol);
@@ -314,6 +314,7 @@ __global__ void __launch_bounds__(GT, CTAS_PER_SM) gn_level_kernel(
   }
   __syncthreads();
   int hb = 0, evals = 0;
+  const uint64_t pol = l2_evict_first_policy();
   uint32_t item = 0;  // chunks consumed so far == ring position of the next chunk (uniform over the CTA)
 
   // prologue of the very first phase A
@@ -322,7 +323,7 @@ __global__ void __launch_bounds__(GT, CTAS_PER_SM) gn_level_kernel(
     slice_of(Vs[0].nIp, C, rank, p0, p1);
     const int nCh = (p1 - p0 + CH - 1) / CH;
     if (lane == 0)
-      for (int c = 0; c < min(NS, nCh); c++) issue_chunk(S, ring, Vs[0], false, p0, p1, c, item + c, warp);
+      for (int c = 0; c < min(NS, nCh); c++) issue_chunk(S, ring, Vs[0], false, p0, p1, c, item + c, warp, pol);
   }
 
   long long tc = clock64();
@@ -376,7 +377,7 @@ __global__ void __launch_bounds__(GT, CTAS_PER_SM) gn_level_kernel(
           const unsigned char * st = ring + (size_t)(warp * NS + it % NS) * WSTAGE_BYTES;
           mbar_wait(&S.full[warp][it % NS], (it / NS) & 1);
           if (p0 + ch * CH + warp * WCH >= p1) {  // warp-uniform: nothing of this chunk belongs to the warp
-            if (lane == 0 && ch + NS < nCh) issue_chunk(S, ring, V, false, p0, p1, ch + NS, it + NS, warp);
+            if (lane == 0 && ch + NS < nCh) issue_chunk(S, ring, V, false, p0, p1, ch + NS, it + NS, warp, pol);
 #pragma unroll
             for (int q = 0; q < 4; q++) P.pix[q] = -1, P.val[q] = 0, P.T[q] = 0;
             return;
@@ -384,7 +385,7 @@ __global__ void __launch_bounds__(GT, CTAS_PER_SM) gn_level_kernel(
           const uint4 pk4 = *reinterpret_cast<const uint4 *>(st + A_OFF_UVT + lane * 16);
           const float4 dd4 = *reinterpret_cast<const float4 *>(st + A_OFF_D + lane * 16);
           __syncwarp();
-          if (lane == 0 && ch + NS < nCh) issue_chunk(S, ring, V, false, p0, p1, ch + NS, it + NS, warp);
+          if (lane == 0 && ch + NS < nCh) issue_chunk(S, ring, V, false, p0, p1, ch + NS, it + NS, warp, pol);
           const uint32_t pk[4] = {pk4.x, pk4.y, pk4.z, pk4.w};
           const float dd[4] = {dd4.x, dd4.y, dd4.z, dd4.w};
           bool good[4];
@@ -406,8 +407,10 @@ __global__ void __launch_bounds__(GT, CTAS_PER_SM) gn_level_kernel(
             for (int q = 0; q < 4; q++)
               if (!good[q]) P.pix[q] = warp_exact(V, pk[q] & 0xfff, (pk[q] >> 12) & 0xfff, dd[q]);
           }
+          if (P.g + 3 >= p1) {  // only in the last tile of the slice: entries past the end of the list take no part
 #pragma unroll
-          for (int q = 0; q < 4; q++) P.pix[q] = P.g + q < p1 ? P.pix[q] : -1;
+            for (int q = 0; q < 4; q++) P.pix[q] = P.g + q < p1 ? P.pix[q] : -1;
+          }
 #pragma unroll
           for (int q = 0; q < 4; q++) P.val[q] = P.pix[q] >= 0 ? (int)__ldg(I + P.pix[q]) : 0;
         };
@@ -417,7 +420,7 @@ __global__ void __launch_bounds__(GT, CTAS_PER_SM) gn_level_kernel(
           for (int q = 0; q < 4; q++) {
             const int r = P.val[q] - (int)P.T[q];
             rr[q] = P.pix[q] >= 0 ? (uint32_t)(r + 255) : (uint32_t)R_CODE_INVISIBLE;  // residual code
-            if (P.pix[q] >= 0) atomicAdd(&hist[r + 255], 1);
+            atomicAdd(&hist[rr[q]], 1);  // branch-free: invisible points land in bin 511, which nobody reads
           }
           if (P.g < p1) r4[P.g >> 2] = make_uint2(rr[0] | (rr[1] << 16), rr[2] | (rr[3] << 16));
         };
@@ -444,7 +447,7 @@ __global__ void __launch_bounds__(GT, CTAS_PER_SM) gn_level_kernel(
       asm volatile("fence.proxy.async;" ::: "memory");
       __syncwarp();
       if (lane == 0)
-        for (int c = 0; c < min(NS, nCh); c++) issue_chunk(S, ring, V, true, p0, p1, c, item + c, warp);
+        for (int c = 0; c < min(NS, nCh); c++) issue_chunk(S, ring, V, true, p0, p1, c, item + c, warp, pol);
       lap(0);
       // ---------------------------------------------------------------- scale + weight table
       // The leading CTA sums the cluster's histograms, runs the scaler and publishes {scale, offset} into every
@@ -470,7 +473,7 @@ __global__ void __launch_bounds__(GT, CTAS_PER_SM) gn_level_kernel(
           // the other histogram buffer is idle (its last remote readers passed a cluster barrier since)
           int * tot = S.hist[hb ^ 1];
 #pragma unroll
-          for (int j = 0; j < BPT; j++) tot[tid + j * GT] = a[j];
+          for (int j = 0; j < BPT; j++) tot[tid + j * GT] = tid + j * GT == R_CODE_INVISIBLE ? 0 : a[j];
           __syncthreads();
           double sc, of;
           compute_scale(V, p, tot, S.red, nvis, sc, of);
@@ -502,35 +505,39 @@ __global__ void __launch_bounds__(GT, CTAS_PER_SM) gn_level_kernel(
           const unsigned char * st = ring + (size_t)(warp * NS + item % NS) * WSTAGE_BYTES;
           mbar_wait(&S.full[warp][item % NS], (item / NS) & 1);
           if (p0 + ch * CH + warp * WCH >= p1) {  // warp-uniform: nothing of this chunk belongs to the warp
-            if (lane == 0 && ch + NS < nCh) issue_chunk(S, ring, V, true, p0, p1, ch + NS, item + NS, warp);
+            if (lane == 0 && ch + NS < nCh) issue_chunk(S, ring, V, true, p0, p1, ch + NS, item + NS, warp, pol);
             continue;
           }
-          const int g = p0 + ch * CH + 4 * tid;
           const uint4 pk4 = *reinterpret_cast<const uint4 *>(st + C_OFF_UVT + lane * 16);
           const uint4 gg4 = *reinterpret_cast<const uint4 *>(st + C_OFF_G + lane * 16);
           const double2 za = *reinterpret_cast<const double2 *>(st + C_OFF_ZI + lane * 32);
           const double2 zb = *reinterpret_cast<const double2 *>(st + C_OFF_ZI + lane * 32 + 16);
           const uint2 packed = *reinterpret_cast<const uint2 *>(st + C_OFF_R + lane * 8);
           __syncwarp();
-          if (lane == 0 && ch + NS < nCh) issue_chunk(S, ring, V, true, p0, p1, ch + NS, item + NS, warp);
+          if (lane == 0 && ch + NS < nCh) issue_chunk(S, ring, V, true, p0, p1, ch + NS, item + NS, warp, pol);
           const uint32_t pk[4] = {pk4.x, pk4.y, pk4.z, pk4.w};
           const uint32_t gg[4] = {gg4.x, gg4.y, gg4.z, gg4.w};
           const double zz[4] = {za.x, za.y, zb.x, zb.y};
-          const int rq[4] = {(int)(packed.x & 0xffff), (int)(packed.x >> 16), (int)(packed.y & 0xffff),
-                             (int)(packed.y >> 16)};  // residual codes: r + 255, or 511 when not visible
+          // residual codes: r + 255, or 511 when not visible.  Entries past the end of the list (padding of the last
+          // tile) may hold anything: masked to a valid table index, and their Jacobian is exactly zero (lists.cu)
+          const int rq[4] = {(int)(packed.x & 0x1ff), (int)((packed.x >> 16) & 0x1ff), (int)(packed.y & 0x1ff),
+                             (int)((packed.y >> 16) & 0x1ff)};
 #pragma unroll
           for (int q = 0; q < 4; q++) {
-            // branch-free: a point outside the slice or not visible gets weight 0 (and a zero Jacobian when its
-            // list entry is padding), which adds exact zeros - the oracle skips w == 0 points the same way.
+            // branch-free: a point that is not visible gets weight 0, a padding entry has a zero Jacobian; both add
+            // exact zeros - the oracle skips w == 0 points the same way.
             // WarpSE3::J rows (Warp.cpp:184-199) contracted with the template gradient
-            // (InverseCompositional.cpp:79-80), in normalised coordinates xn = x/z, yn = y/z
-            const bool inside = g + q < p1;
-            const double u = (double)(int)(pk[q] & 0xfff), v = (double)(int)((pk[q] >> 12) & 0xfff);
-            const double a = inside ? (double)(int)(int16_t)(gg[q] & 0xffff) * fxJ : 0.0;  // dIx * fx
-            const double b = inside ? (double)(int)(int16_t)(gg[q] >> 16) * fyJ : 0.0;     // dIy * fy
-            const double2 wwr = lut[inside ? rq[q] : R_CODE_INVISIBLE];                    // {w, w r}
+            // (InverseCompositional.cpp:79-80), in normalised coordinates xn = x/z, yn = y/z.
+            // Integer -> double through the 2^52 trick (one full-rate add instead of a quarter-rate conversion):
+            // the low word of 2^52 + k is k, and the gradients are biased by 2^15 to make them non-negative.
+            const uint32_t gb = gg[q] ^ 0x80008000u;
+            const double u = __hiloint2double(0x43300000, (int)(pk[q] & 0xfff)) - 4503599627370496.0;
+            const double v = __hiloint2double(0x43300000, (int)((pk[q] >> 12) & 0xfff)) - 4503599627370496.0;
+            const double a = (__hiloint2double(0x43300000, (int)(gb & 0xffff)) - 4503599627403264.0) * fxJ;  // dIx * fx
+            const double b = (__hiloint2double(0x43300000, (int)(gb >> 16)) - 4503599627403264.0) * fyJ;     // dIy * fy
+            const double2 wwr = lut[rq[q]];                                                                  // {w, w r}
             const double w = wwr.x, wr = wwr.y;
-            const double zi = inside ? zz[q] : 0.0;
+            const double zi = zz[q];
             const double xn = fma(ifx, u, kx), yn = fma(ify, v, ky);
             const double cc = fma(a, xn, b * yn);
             double J[6];
@@ -563,7 +570,7 @@ __global__ void __launch_bounds__(GT, CTAS_PER_SM) gn_level_kernel(
         slice_of(Vn.nIp, C, rank, q0, q1);
         const int nChN = (q1 - q0 + CH - 1) / CH;
         if (lane == 0)  // the warp's own ring is free as soon as the warp leaves phase C
-          for (int c = 0; c < min(NS, nChN); c++) issue_chunk(S, ring, Vn, false, q0, q1, c, item + c, warp);
+          for (int c = 0; c < min(NS, nChN); c++) issue_chunk(S, ring, Vn, false, q0, q1, c, item + c, warp, pol);
       }
       // fixed-order block reduction: lanes (xor tree), then warps in order
 #pragma unroll

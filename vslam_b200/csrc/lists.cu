@@ -84,6 +84,17 @@ __global__ void __launch_bounds__(256) list_scan_kernel(
     __syncthreads();
   }
   if (threadIdx.x == 0) V.nIp = carry;
+  // Padding of the last tile: zero gradient (hence a zero Jacobian row, which adds exact zeros whatever the weight),
+  // finite 1/depth, depth 1.  The Jacobian phase of the level kernel then needs no "is this entry real" test.
+  const int nIp = carry, padEnd = (nIp + LIST_TILE - 1) / LIST_TILE * LIST_TILE;
+  for (int o = nIp + (int)threadIdx.x; o < padEnd; o += 256) {
+    unsigned char * tile = V.tiles + (size_t)(o / LIST_TILE) * LIST_TILE_BYTES;
+    const int j = o % LIST_TILE;
+    reinterpret_cast<float *>(tile + TILE_OFF_D)[j] = 1.f;
+    reinterpret_cast<uint32_t *>(tile + TILE_OFF_UVT)[j] = 0u;
+    reinterpret_cast<uint32_t *>(tile + TILE_OFF_G)[j] = 0u;
+    reinterpret_cast<double *>(tile + TILE_OFF_ZI)[j] = 0.0;
+  }
 }
 
 __global__ void __launch_bounds__(LTHREADS) list_write_kernel(
