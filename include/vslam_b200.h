@@ -46,6 +46,10 @@ enum { VSLAMB200_RGB = 0, VSLAMB200_BGR = 1 };
 /* solver_kind: Gauss-Newton is the reference's solver (least_squares/src/GaussNewton.cpp); Levenberg-Marquardt is an
  * EXTENSION named by the benchmark configurations (no counterpart in the reference; defined by oracle/vslam_oracle.cpp) */
 enum { VSLAMB200_SOLVER_GN = 0, VSLAMB200_SOLVER_LM = 1 };
+/* sampling: NEAREST is the reference's aligner (inverse compositional, InverseCompositional.cpp:119-120).  BILINEAR is an
+ * EXTENSION (forward formulation: bilinear sampling, Jacobians at the warped point every iteration, optional depth
+ * residual; semantics of lukas_kanade/src/ForwardAdditive.cpp:52-137, defined by oracle/vslam_oracle.cpp) */
+enum { VSLAMB200_SAMPLING_NEAREST = 0, VSLAMB200_SAMPLING_BILINEAR = 1 };
 
 typedef struct vslamb200_ctx vslamb200_ctx;
 
@@ -65,6 +69,8 @@ typedef struct vslamb200_config
   double lm_lambda0;     /* LM only: initial damping of (A + lambda diag A) dx = b */
   double lm_up;          /* LM only: lambda *= lm_up after a rejected step (> 1) */
   double lm_down;        /* LM only: lambda *= lm_down after an accepted step (0 < lm_down <= 1) */
+  int sampling;          /* VSLAMB200_SAMPLING_* */
+  double depth_weight;   /* BILINEAR only: weight of the depth residual Z_to(u',v') - q_z against the photometric one; 0 = off */
 } vslamb200_config;
 
 /* One alignment: SE3Alignment::align(from, to) (n_from == 1, multi == 0) or the vector overload (multi != 0).

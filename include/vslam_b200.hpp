@@ -320,7 +320,8 @@ public:
   };
 
   SE3Alignment(double minGradient, least_squares::Solver::ShPtr solver, least_squares::Loss::ShPtr loss,
-               bool includePrior = false, int device = 0)
+               bool includePrior = false, int device = 0, int sampling = VSLAMB200_SAMPLING_NEAREST,
+               double depthWeight = 0.0)  // the last two: extension (bilinear sampling, depth residual), see vslam_b200.h
   : _solver(std::move(solver)), _loss(std::move(loss))
   {
     if (!_solver) throw Exception("SE3Alignment: solver is null");
@@ -338,6 +339,8 @@ public:
     cfg.lm_lambda0 = _solver->lambda0();
     cfg.lm_up = _solver->up();
     cfg.lm_down = _solver->down();
+    cfg.sampling = sampling;
+    cfg.depth_weight = depthWeight;
     check(vslamb200_create(&cfg, device, &_ctx));
   }
   ~SE3Alignment() override { vslamb200_destroy(_ctx); }

@@ -15,6 +15,7 @@ _SO = os.path.join(_HERE, "_build", "libvslam_oracle.so")
 LOSS_NONE, LOSS_QUADRATIC, LOSS_TUKEY, LOSS_HUBER, LOSS_TDIST = range(5)
 SCALER_IDENTITY, SCALER_MEDIAN, SCALER_MEAN, SCALER_TDIST = range(4)
 SOLVER_GN, SOLVER_LM = range(2)
+SAMPLING_NEAREST, SAMPLING_BILINEAR = range(2)
 R_NOT_INTEREST, R_INVISIBLE = -32768, -32767
 TRACE_STRIDE = 64
 STOP_NAMES = ["maxiter", "constraints", "hessian", "chi2", "converged", "nan"]
@@ -36,14 +37,16 @@ class Config(C.Structure):
         ("lm_lambda0", C.c_double),
         ("lm_up", C.c_double),
         ("lm_down", C.c_double),
+        ("sampling", C.c_int),
+        ("depth_weight", C.c_double),
     ]
 
 
 def make_config(min_gradient=30.0, loss=LOSS_TDIST, scaler=SCALER_TDIST, huber_c=1.345, v=5.0,
                 min_step_size=1e-7, max_iterations=100, include_prior=False, f32_storage=True, solver=SOLVER_GN,
-                lm_lambda0=1e-3, lm_up=10.0, lm_down=0.1):
+                lm_lambda0=1e-3, lm_up=10.0, lm_down=0.1, sampling=SAMPLING_NEAREST, depth_weight=0.0):
     return Config(min_gradient, loss, huber_c, v, scaler, v, min_step_size, max_iterations,
-                  int(include_prior), int(f32_storage), solver, lm_lambda0, lm_up, lm_down)
+                  int(include_prior), int(f32_storage), solver, lm_lambda0, lm_up, lm_down, sampling, depth_weight)
 
 
 def build(force=False):

@@ -565,6 +565,10 @@ struct Config
   // 1 = Levenberg-Marquardt damping on the same normal equations
   int solverKind;
   double lmLambda0, lmUp, lmDown;
+  // EXTENSION: sampling 0 = nearest pixel, inverse compositional (the reference's aligner); 1 = bilinear sampling with
+  // per-iteration Jacobians at the warped point, optionally with a depth residual weighted by depthWeight
+  int sampling;
+  double depthWeight;
 };
 
 struct Scale
@@ -835,6 +839,122 @@ static NE view_normal_equations(View & V, const Config & cfg, int16_t * rcode)
   return ne;
 }
 
+// ------------------------------------------------------------------------------------------
+// EXTENSION (named by BASELINE.json's north_star, absent from the reference's aligner): forward
+// formulation with BILINEAR sampling, per-iteration Jacobians and an optional DEPTH residual.  Semantics follow
+// lukas_kanade/src/ForwardAdditive.cpp:52-137 (gradients of the target sampled at the warped position, visibility
+// 1 < u' < W-1, scale over the visible residuals) and the dense RGB-D odometry literature odometry/README.md:3-6
+// cites (Kerl et al.: geometric residual Z_to(u', v') - q_z).  This restatement is the definition: parity unpinned.
+//   q = R p + t, (u', v') = pi(q), S(f) = true bilinear interpolation of plane f at (u', v')
+//   r_I = S(I_to) - T(u, v);   g = (S(dIx_to), S(dIy_to)) / 8   (the Sobel planes are 8 x the derivative)
+//   right perturbation se3 * exp(xi) (the solvers update se3 <- se3 * exp(-dx)):  dq/dxi = R [I | -p^]
+//   J_I = G R, (p x (G R)) with G = g^T dpi/dq = (g_x fx / q_z, g_y fy / q_z, -(g_x fx q_x + g_y fy q_y) / q_z^2)
+//   r_Z = S(Z_to) - q_z (all four neighbours valid), gradient of the bilinear interpolant itself,
+//   J_Z = G_Z R, (p x (G_Z R)),  G_Z = g_Z^T dpi/dq - (0, 0, 1)
+//   A = (sum w_I J_I^T J_I + depthWeight sum w_Z J_Z^T J_Z) / n, b and chi2 alike, n = all interest points
+// ------------------------------------------------------------------------------------------
+static inline double bilinear_true(const double f00, const double f10, const double f01, const double f11, double a, double b)
+{
+  return (1.0 - b) * ((1.0 - a) * f00 + a * f10) + b * ((1.0 - a) * f01 + a * f11);
+}
+
+static NE view_normal_equations_ext(View & V, const Config & cfg)
+{
+  const size_t N = V.ipU.size();
+  double R[9];
+  quat_to_R(V.se3.q, R);
+  const int W = V.W, l = V.level;
+  const int Wt = V.to->W[l], Ht = V.to->H[l];
+  const uint8_t * I = V.to->I[l].data();
+  const uint8_t * T = V.from->I[l].data();
+  const int16_t * gxT = V.to->dIx[l].data();
+  const int16_t * gyT = V.to->dIy[l].data();
+  const double * Zt = V.to->Z[l].data();
+  const double * pcl = V.from->pcl[l].data();
+  const double fx = V.camProj.fx, fy = V.camProj.fy;
+  const double NaN = std::numeric_limits<double>::quiet_NaN();
+  std::vector<double> rI(N, NaN), rZ(N, NaN), JI(6 * N, 0.0), JZ(6 * N, 0.0);
+  std::vector<double> visI, visZ;
+  for (size_t k = 0; k < N; k++) {
+    const int u = V.ipU[k], v = V.ipV[k];
+    const double * p = pcl + 3 * ((size_t)v * W + u);
+    double up, vp;
+    if (!warp_apply(R, V.se3.t, V.camProj, p, up, vp)) continue;
+    if (!(1 < up && up < Wt - 1 && 1 < vp && vp < Ht - 1)) continue;
+    const double qx = std::fma(R[2], p[2], std::fma(R[1], p[1], std::fma(R[0], p[0], V.se3.t[0])));
+    const double qy = std::fma(R[5], p[2], std::fma(R[4], p[1], std::fma(R[3], p[0], V.se3.t[1])));
+    const double qz = std::fma(R[8], p[2], std::fma(R[7], p[1], std::fma(R[6], p[0], V.se3.t[2])));
+    const int x0 = (int)std::floor(up), y0 = (int)std::floor(vp);
+    const double a = up - x0, b = vp - y0;
+    const size_t i00 = (size_t)y0 * Wt + x0, i10 = i00 + 1, i01 = i00 + Wt, i11 = i01 + 1;
+    rI[k] = bilinear_true(I[i00], I[i10], I[i01], I[i11], a, b) - (double)T[(size_t)v * W + u];
+    visI.push_back(rI[k]);
+    const double gx = bilinear_true(gxT[i00], gxT[i10], gxT[i01], gxT[i11], a, b) / 8.0;
+    const double gy = bilinear_true(gyT[i00], gyT[i10], gyT[i01], gyT[i11], a, b) / 8.0;
+    const double iz = 1.0 / qz;
+    auto jac = [&](double g0, double g1, double g2, double * J) {
+      const double H[3] = {g0 * R[0] + g1 * R[3] + g2 * R[6], g0 * R[1] + g1 * R[4] + g2 * R[7], g0 * R[2] + g1 * R[5] + g2 * R[8]};
+      J[0] = H[0];
+      J[1] = H[1];
+      J[2] = H[2];
+      J[3] = p[1] * H[2] - p[2] * H[1];
+      J[4] = p[2] * H[0] - p[0] * H[2];
+      J[5] = p[0] * H[1] - p[1] * H[0];
+    };
+    jac(gx * fx * iz, gy * fy * iz, -(gx * fx * qx + gy * fy * qy) * iz * iz, &JI[6 * k]);
+    if (cfg.depthWeight > 0.0) {
+      const double z00 = Zt[i00], z10 = Zt[i10], z01 = Zt[i01], z11 = Zt[i11];
+      if (z00 > 0 && z10 > 0 && z01 > 0 && z11 > 0 && std::isfinite(z00 + z10 + z01 + z11)) {
+        rZ[k] = bilinear_true(z00, z10, z01, z11, a, b) - qz;
+        visZ.push_back(rZ[k]);
+        const double gzx = (1.0 - b) * (z10 - z00) + b * (z11 - z01), gzy = (1.0 - a) * (z01 - z00) + a * (z11 - z10);
+        jac(gzx * fx * iz, gzy * fy * iz, -(gzx * fx * qx + gzy * fy * qy) * iz * iz - 1.0, &JZ[6 * k]);
+      }
+    }
+  }
+  NE ne;
+  Scale sI{0.0, 1.0}, sZ{0.0, 1.0};
+  if (cfg.lossKind != LOSS_NONE) {
+    sI = compute_scale(cfg, visI);
+    if (!visZ.empty()) sZ = compute_scale(cfg, visZ);
+  }
+  ne.scale = sI.scale;
+  ne.offset = sI.offset;
+  double A[21] = {0}, b[6] = {0}, chi2 = 0;
+  auto add = [&](const double * Jk, double rk, double wk) {
+    int idx = 0;
+    for (int i = 0; i < 6; i++) {
+      const double wj = wk * Jk[i];
+      for (int j = i; j < 6; j++) A[idx++] += wj * Jk[j];
+      b[i] += wj * rk;
+    }
+    chi2 += rk * wk * rk;
+  };
+  for (size_t k = 0; k < N; k++) {
+    if (!std::isnan(rI[k]))
+      add(&JI[6 * k], rI[k], cfg.lossKind == LOSS_NONE ? 1.0 : compute_weight(cfg, (rI[k] - sI.offset) / sI.scale));
+    if (!std::isnan(rZ[k]))
+      add(&JZ[6 * k], rZ[k],
+          cfg.depthWeight * (cfg.lossKind == LOSS_NONE ? 1.0 : compute_weight(cfg, (rZ[k] - sZ.offset) / sZ.scale)));
+  }
+  int idx = 0;
+  for (int i = 0; i < 6; i++)
+    for (int j = i; j < 6; j++) {
+      ne.A(i, j) = A[idx];
+      ne.A(j, i) = A[idx++];
+    }
+  for (int i = 0; i < 6; i++) ne.b[i] = b[i];
+  ne.chi2 = chi2;
+  ne.n = (long)N;
+  if (ne.n > 1) {
+    const double inv = (double)ne.n;
+    for (double & x : ne.A.a) x /= inv;
+    for (double & x : ne.b.v) x /= inv;
+    ne.chi2 /= inv;
+  }
+  return ne;
+}
+
 // MotionPrior::apply (odometry/src/direct_image_alignment/SE3Alignment.cpp:37-47)
 static void prior_apply(NE & ne, const Vec6 & xPred, const Vec6 & x)
 {
@@ -867,14 +987,14 @@ struct SolveResult
 static NE stacked_normal_equations(std::vector<View> & views, const Config & cfg, bool stacked)
 {
   if (!stacked) {
-    NE ne = view_normal_equations(views[0], cfg, nullptr);
+    NE ne = cfg.sampling == 1 ? view_normal_equations_ext(views[0], cfg) : view_normal_equations(views[0], cfg, nullptr);
     if (views[0].hasPrior) prior_apply(ne, views[0].xPred, se3_log(views[0].se3));
     return ne;
   }
   NE sum;  // NormalEquations(nParameters) zero, then combine (InverseCompositionalStacked.cpp:44-46)
   bool first = true;
   for (auto & V : views) {
-    NE ne = view_normal_equations(V, cfg, nullptr);
+    NE ne = cfg.sampling == 1 ? view_normal_equations_ext(V, cfg) : view_normal_equations(V, cfg, nullptr);
     if (V.hasPrior) prior_apply(ne, V.xPred, se3_log(V.se3));
     for (int i = 0; i < 36; i++) sum.A.a[i] += ne.A.a[i];
     for (int i = 0; i < 6; i++) sum.b[i] += ne.b[i];
@@ -1119,13 +1239,15 @@ struct vo_config
   int f32_storage;
   int solver_kind;
   double lm_lambda0, lm_up, lm_down;
+  int sampling;
+  double depth_weight;
 };
 
 static vo::Config to_cfg(const vo_config * c)
 {
   return {c->min_gradient, c->loss_kind, c->huber_c, c->loss_v, c->scaler_kind, c->scaler_v,
           c->min_step_size, c->max_iterations, c->include_prior, c->f32_storage, c->solver_kind, c->lm_lambda0, c->lm_up,
-          c->lm_down};
+          c->lm_down, c->sampling, c->depth_weight};
 }
 static vo::SE3 to_se3(const double * p)
 {

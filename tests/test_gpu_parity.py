@@ -577,3 +577,93 @@ def test_levenberg_marquardt_extension_matches_oracle(ctx, capi, oracle, synth, 
     if not prior:
         dt, dr = pose_err(O, got["pose"], poses[K])
         assert dt < 0.01 and dr < 0.01
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("W,H,L,K,prior,dw,solver,loss", [
+    (640, 480, 4, 1, False, 0.0, "GN", "TDIST"),
+    (640, 480, 4, 1, False, 1e6, "GN", "TDIST"),
+    (320, 240, 3, 2, True, 1e6, "GN", "TDIST"),
+    (320, 240, 3, 1, False, 1e6, "LM", "TDIST"),
+    (320, 240, 3, 1, False, 50.0, "GN", "NONE"),
+    (1232, 368, 5, 1, False, 0.0, "GN", "TDIST"),
+])
+def test_bilinear_depth_extension_matches_oracle(ctx, capi, oracle, synth, W, H, L, K, prior, dw, solver, loss):
+    """bilinear sampling with per-iteration Jacobians and the optional depth residual (ext.cu).  The
+    reference's shipped aligner is nearest-pixel inverse compositional; this mode is defined by
+    oracle/vslam_oracle.cpp (view_normal_equations_ext), parity is GPU <-> that restatement: every evaluation's A, b,
+    chi2, scale and step, the iteration counts, stop reasons, pose and covariance."""
+    O, A = oracle, capi
+    cam = synth.cam_for(W, H)
+    rng = np.random.default_rng(23)
+    xis = [np.zeros(6)] + [np.concatenate([rng.uniform(-0.02, 0.02, 3), rng.uniform(-0.01, 0.01, 3)]) for _ in range(K)]
+    frames, poses, raw = [], [], []
+    for xi in xis:
+        R, t = synth.se3_exp(xi)
+        g, d = synth.render(W, H, cam, R, t, scene_seed=5005)
+        raw.append((g, d))
+        frames.append(O.Frame(g, d.astype(np.float64), *cam, L))
+        poses.append(synth.pose7(R, t))
+    ctx.upload(np.arange(K + 1), np.stack([g for g, _ in raw]), np.stack([d for _, d in raw]), cam, L)
+    kw = dict(max_iterations=30, include_prior=prior, depth_weight=dw)
+    if loss == "NONE":
+        okw, akw = dict(loss=O.LOSS_NONE, scaler=O.SCALER_IDENTITY), dict(loss=A.LOSS_NONE, scaler=A.SCALER_IDENTITY)
+    else:
+        okw, akw = {}, {}
+    ocfg = O.make_config(sampling=O.SAMPLING_BILINEAR, solver=O.SOLVER_LM if solver == "LM" else O.SOLVER_GN, **kw, **okw)
+    ctx.set_config(A.make_config(sampling=A.SAMPLING_BILINEAR, solver=A.SOLVER_LM if solver == "LM" else A.SOLVER_GN,
+                                 **kw, **akw))
+    ctx.set_trace(True)
+    multi = K > 1
+    ref = O.align(ocfg, frames[:K] if multi else frames[0], poses[:K] if multi else poses[0], frames[K], poses[0],
+                  multi=multi, want_trace=True)
+    got = ctx.align([dict(to=K, to_pose=poses[0], frm=list(range(K)), from_poses=np.stack(poses[:K]), multi=multi)])[0]
+    tr = ctx.get_trace(0, L)
+    assert got["status"] == ref["status"] == 0
+    assert list(got["iters"][:L]) == list(ref["iters"]), (got["iters"], ref["iters"])
+    assert list(got["stop"][:L]) == list(ref["stop"])
+    for l in range(L):
+        for i in range(ref["iters"][l]):
+            a, b = tr[l, i], ref["trace"][l, i]
+            assert a[0] == b[0] == 1 and a[1] == b[1], (l, i)
+            assert rel_fro(a[18:54], b[18:54]) < NE_TOL and rel_fro(a[12:18], b[12:18]) < NE_TOL, (l, i)
+            assert abs(a[2] - b[2]) <= NE_TOL * abs(b[2]), (l, i)                       # chi2
+            assert abs(a[4] - b[4]) <= 1e-6 * abs(b[4]) and a[5] == b[5] == 0, (l, i)  # scale of the photometric residuals
+            assert np.allclose(a[54:60], b[54:60], rtol=1e-4, atol=1e-9), (l, i)       # the step
+    dt, dr = pose_err(O, got["pose"], ref["pose"])
+    assert dt < POSE_TOL and dr < POSE_TOL
+    assert rel_fro(got["cov"], ref["cov"]) < 1e-3
+    if not prior:
+        dt, dr = pose_err(O, got["pose"], poses[K])
+        assert dt < 0.01 and dr < 0.01
+    # the nearest-pixel entry points refuse the mode instead of silently answering for another one
+    with pytest.raises(Exception):
+        ctx.evaluate(0, K, 0, poses[0])
+    ctx.set_config(A.make_config())
+
+
+@pytest.mark.gpu
+def test_bilinear_extension_batch_is_independent_of_batch_order(ctx, capi, synth):
+    """The extension's sums are combined in block order by the last block to finish: a job's result does not depend on
+    what else is in the batch (bit-identical poses alone, in a batch of 6 and in the reversed batch)."""
+    A = capi
+    W, H, L = 320, 240, 3
+    cam = synth.cam_for(W, H)
+    rng = np.random.default_rng(5)
+    xis = [np.zeros(6)] + [np.concatenate([rng.uniform(-0.02, 0.02, 3), rng.uniform(-0.01, 0.01, 3)]) for _ in range(6)]
+    raw = []
+    for xi in xis:
+        R, t = synth.se3_exp(xi)
+        raw.append(synth.render(W, H, cam, R, t, scene_seed=6006))
+    ctx.upload(np.arange(7), np.stack([g for g, _ in raw]), np.stack([d for _, d in raw]), cam, L)
+    ctx.set_config(A.make_config(max_iterations=30, sampling=A.SAMPLING_BILINEAR, depth_weight=1e6))
+    ident = np.array([0, 0, 0, 1, 0, 0, 0.0])
+    jobs = [dict(to=k, to_pose=ident, frm=[0], from_poses=ident[None], multi=False) for k in range(1, 7)]
+    alone = [ctx.align([j])[0] for j in jobs]
+    batch = ctx.align(jobs)
+    rev = ctx.align(jobs[::-1])[::-1]
+    for a, b, c in zip(alone, batch, rev):
+        assert a["status"] == b["status"] == c["status"] == 0
+        assert np.array_equal(a["pose"], b["pose"]) and np.array_equal(a["pose"], c["pose"])
+        assert list(a["iters"]) == list(b["iters"]) == list(c["iters"])
+    ctx.set_config(A.make_config())

@@ -247,3 +247,54 @@ def test_levenberg_marquardt_extension(oracle, synth):
     gn = O.align(O.make_config(max_iterations=40), f0, O.IDENTITY, f1, O.IDENTITY)
     d = O.se3_log(O.se3_mul(r["pose"], O.se3_inv(gn["pose"])))
     assert np.linalg.norm(d) < 5e-3                             # both solvers end in the same basin
+
+
+def test_bilinear_depth_extension(oracle, synth):
+    """The extended mode's own contract (oracle/vslam_oracle.cpp, view_normal_equations_ext): the first evaluation's b
+    is the derivative of chi2 with respect to a right perturbation of the warp (checked by central differences on the
+    quadratic loss, where chi2 is smooth), the mode reaches the rendered motion in fewer iterations than nearest-pixel
+    sampling, and the depth residual keeps the solution in the same place."""
+    O = oracle
+    p = synth.make_pair(320, 240, 1234)
+    L = 3
+    f0 = O.Frame(p["gray0"], p["depth0"].astype(np.float64), *p["cam"], L)
+    f1 = O.Frame(p["gray1"], p["depth1"].astype(np.float64), *p["cam"], L)
+    near = O.align(O.make_config(max_iterations=40), f0, O.IDENTITY, f1, O.IDENTITY)
+    res = {}
+    for dw in (0.0, 1e6):
+        cfg = O.make_config(max_iterations=40, sampling=O.SAMPLING_BILINEAR, depth_weight=dw)
+        r = O.align(cfg, f0, O.IDENTITY, f1, O.IDENTITY, want_trace=True)
+        assert r["status"] == 0
+        d = O.se3_log(O.se3_mul(r["pose"], O.se3_inv(p["pose1"])))
+        assert np.linalg.norm(d[:3]) < 0.005 and np.linalg.norm(d[3:]) < 0.005
+        res[dw] = r
+    assert sum(res[0.0]["iters"]) < sum(near["iters"])
+    assert not np.allclose(res[0.0]["trace"][L - 1, 0, 18:54], res[1e6]["trace"][L - 1, 0, 18:54], rtol=1e-3)
+    # gradient check: one evaluation on a one-level pyramid with a quadratic loss (weights 1, scale 1): b is half the
+    # derivative of chi2 along a right perturbation of the warp.  The images are smoothed first: the gradient planes are
+    # Sobel derivatives of a blurred image, on sharp edges they are not the slope of the bilinear interpolant.
+    from scipy.ndimage import gaussian_filter
+    q = _small_pair(synth)
+    sm = lambda g: np.clip(np.round(gaussian_filter(g.astype(float), 2.5)), 0, 255).astype(np.uint8)
+    g0 = O.Frame(sm(q["gray0"]), q["depth0"].astype(np.float64), *q["cam"], 1)
+    g1 = O.Frame(sm(q["gray1"]), q["depth1"].astype(np.float64), *q["cam"], 1)
+    start = O.se3_exp(np.array([0.004, -0.003, 0.002, 0.002, -0.001, 0.0015]))
+    grads = {}
+    for dw in (0.0, 5000.0):
+        c1 = O.make_config(min_gradient=5.0, max_iterations=1, loss=O.LOSS_QUADRATIC, scaler=O.SCALER_IDENTITY,
+                           sampling=O.SAMPLING_BILINEAR, depth_weight=dw)
+
+        def chi2_at(xi):
+            t = O.align(c1, g0, O.IDENTITY, g1, O.se3_mul(start, O.se3_exp(xi)), want_trace=True)["trace"][0, 0]
+            return t[2], t[12:18].copy()
+        _, b = chi2_at(np.zeros(6))
+        num = np.zeros(6)
+        for k in range(6):
+            e = np.zeros(6)
+            e[k] = 2e-4
+            num[k] = (chi2_at(e)[0] - chi2_at(-e)[0]) / 4e-4
+        grads[dw] = (num, 2 * b)
+        assert np.allclose(num, 2 * b, rtol=0.08, atol=0.01 * np.abs(b).max()), (dw, num, 2 * b)
+    # the depth term alone (difference of the two runs): its Jacobian is the exact derivative of the bilinear depth sample
+    dn, da = grads[5000.0][0] - grads[0.0][0], grads[5000.0][1] - grads[0.0][1]
+    assert np.abs(da).max() > 10 and np.allclose(dn, da, rtol=0.05, atol=0.02 * np.abs(da).max()), (dn, da)

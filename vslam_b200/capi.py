@@ -17,6 +17,7 @@ ROW_MAJOR, COL_MAJOR = 0, 1
 DEPTH_F32, DEPTH_F64, DEPTH_U16 = 0, 1, 2
 RGB, BGR = 0, 1
 SOLVER_GN, SOLVER_LM = 0, 1
+SAMPLING_NEAREST, SAMPLING_BILINEAR = 0, 1
 R_NOT_INTEREST, R_INVISIBLE = -32768, -32767
 STOP_NAMES = ["maxiter", "constraints", "hessian", "chi2", "converged", "nan"]
 
@@ -25,7 +26,8 @@ class Config(C.Structure):
     _fields_ = [("min_gradient", C.c_double), ("loss_kind", C.c_int), ("huber_c", C.c_double),
                 ("loss_v", C.c_double), ("scaler_kind", C.c_int), ("scaler_v", C.c_double),
                 ("min_step_size", C.c_double), ("max_iterations", C.c_int), ("include_prior", C.c_int),
-                ("solver_kind", C.c_int), ("lm_lambda0", C.c_double), ("lm_up", C.c_double), ("lm_down", C.c_double)]
+                ("solver_kind", C.c_int), ("lm_lambda0", C.c_double), ("lm_up", C.c_double), ("lm_down", C.c_double),
+                ("sampling", C.c_int), ("depth_weight", C.c_double)]
 
 
 class Job(C.Structure):
@@ -110,9 +112,9 @@ def ptr(a):
 
 def make_config(min_gradient=30.0, loss=LOSS_TDIST, scaler=SCALER_TDIST, huber_c=1.345, v=5.0,
                 min_step_size=1e-7, max_iterations=100, include_prior=False, solver=SOLVER_GN, lm_lambda0=1e-3,
-                lm_up=10.0, lm_down=0.1):
+                lm_up=10.0, lm_down=0.1, sampling=SAMPLING_NEAREST, depth_weight=0.0):
     return Config(min_gradient, loss, huber_c, v, scaler, v, min_step_size, max_iterations, int(include_prior), solver,
-                  lm_lambda0, lm_up, lm_down)
+                  lm_lambda0, lm_up, lm_down, sampling, depth_weight)
 
 
 class Context:

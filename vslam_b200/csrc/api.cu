@@ -91,7 +91,7 @@ struct vslamb200_ctx
   DevBuf dFrames;  // FrameDev table
   DevBuf stageGray, stageDepth, slotsBuf;
   // alignment workspace
-  DevBuf jobs, views, chunkCounts, partials, lists, trace, plane;
+  DevBuf jobs, views, chunkCounts, partials, lists, trace, plane, ext;
   int traceEnabled = 0, timing = 0;
   int traceJobs = 0, traceLevels = 0, traceMaxIter = 0;
   vslamb200_stats stats;
@@ -354,6 +354,14 @@ static int check_cfg(const vslamb200_config * cfg)
   if (cfg->solver_kind == VSLAMB200_SOLVER_LM &&
       !(cfg->lm_lambda0 > 0.0 && cfg->lm_up > 1.0 && cfg->lm_down > 0.0 && cfg->lm_down <= 1.0))
     return fail(VSLAMB200_EINVAL, "bad Levenberg-Marquardt parameters (lambda0 > 0, up > 1, 0 < down <= 1)");
+  if (cfg->sampling != VSLAMB200_SAMPLING_NEAREST && cfg->sampling != VSLAMB200_SAMPLING_BILINEAR)
+    return fail(VSLAMB200_EINVAL, "bad sampling");
+  if (!(cfg->depth_weight >= 0.0)) return fail(VSLAMB200_EINVAL, "bad depth_weight");
+  if (cfg->sampling == VSLAMB200_SAMPLING_NEAREST && cfg->depth_weight != 0.0)
+    return fail(VSLAMB200_EINVAL, "the depth residual needs bilinear sampling");
+  if (cfg->sampling == VSLAMB200_SAMPLING_BILINEAR && cfg->loss_kind != VSLAMB200_LOSS_NONE &&
+      cfg->scaler_kind != VSLAMB200_SCALER_IDENTITY && cfg->scaler_kind != VSLAMB200_SCALER_TDIST)
+    return fail(VSLAMB200_EINVAL, "bilinear sampling supports the identity and t-distribution scalers");
   return 0;
 }
 
@@ -411,7 +419,7 @@ void vslamb200_destroy(vslamb200_ctx * c)
     if (a.ptr) cudaFree(a.ptr);
   }
   DevBuf * bufs[] = {&c->dFrames, &c->stageGray, &c->stageDepth, &c->slotsBuf, &c->jobs, &c->views,
-                     &c->chunkCounts, &c->partials, &c->lists, &c->trace, &c->plane};
+                     &c->chunkCounts, &c->partials, &c->lists, &c->trace, &c->plane, &c->ext};
   for (auto b : bufs) b->release();
   if (c->copyStream) {
     cudaStreamSynchronize(c->copyStream);
@@ -673,6 +681,8 @@ vb::SolverParams solver_params(const vslamb200_config & cfg)
   p.lmLambda0 = cfg.lm_lambda0;
   p.lmUp = cfg.lm_up;
   p.lmDown = cfg.lm_down;
+  p.sampling = cfg.sampling;
+  p.depthWeight = cfg.depth_weight;
   return p;
 }
 
@@ -793,7 +803,23 @@ int run_level(vslamb200_ctx * c, Problem & P, int level, const vb::SolverParams 
                          listChunks, stream);
   vb::launch_level_begin(dJobs, dViews, job0, nJobs, level, stream);
   if (c->timing) CK(cudaEventRecord(c->ev[1], stream));
-  if (use_incremental(P, sp, npx)) {
+  if (sp.sampling == VSLAMB200_SAMPLING_BILINEAR) {
+    // extension (ext.cu): three launches per evaluation over all jobs; every fourth evaluation the host reads how many
+    // jobs are still running and stops queueing when none is
+    int * dActive = c->ext.as<int>();
+    for (int it = 0; it < maxEvals; it++) {
+      const bool check = (it & 3) == 3 || it + 1 == maxEvals;
+      vb::launch_ext_iteration(dJobs, dViews, job0, nJobs, view0, nViews, npx, sp, level, it + 1 >= maxEvals, dTrace,
+                               traceJobStride, check ? dActive : nullptr, stream);
+      c->stats.kernel_launches += 3 + (check ? 1 : 0);
+      if (check && it + 1 < maxEvals) {
+        int active = 0;
+        CK(cudaMemcpyAsync(&active, dActive, sizeof(int), cudaMemcpyDeviceToHost, stream));
+        CK(cudaStreamSynchronize(stream));
+        if (active == 0) break;
+      }
+    }
+  } else if (use_incremental(P, sp, npx)) {
     // VSLAMB200_INC_CHECK=1 (tests): every point is re-evaluated in every iteration and the points whose residual changed
     // although their motion bound had not asked for them are counted (stats.phase_clocks[level][9], must stay 0)
     const char * chk = std::getenv("VSLAMB200_INC_CHECK");
@@ -837,6 +863,17 @@ int prepare_workspace(vslamb200_ctx * c, Problem & P, const vb::SolverParams & s
     V.r = (int16_t *)(b + tileBytes);
     V.lim = (float *)(b + tileBytes + listStride * 2);
     V.tileState = (float *)(b + tileBytes + listStride * 6);
+  }
+  if (sp.sampling == VSLAMB200_SAMPLING_BILINEAR) {
+    // bilinear extension: per view 16 B per candidate pixel (r_I, r_Z in fp64) + 28 partial sums per 2048 list entries
+    const size_t chunks = (npx0 + vb::EXT_CHUNK - 1) / vb::EXT_CHUNK;
+    const size_t rBytes = listStride * sizeof(double2), partBytes = align_up(chunks * vb::NE_TERMS * sizeof(double), 256);
+    CK(c->ext.ensure((rBytes + partBytes) * nViews + 256));
+    uint8_t * eb = c->ext.as<uint8_t>() + 256;  // the first 256 bytes hold the active-job counter
+    for (int v = 0; v < nViews; v++) {
+      P.views[v].extR = (double2 *)(eb + (size_t)v * (rBytes + partBytes));
+      P.views[v].extPart = (double *)(eb + (size_t)v * (rBytes + partBytes) + rBytes);
+    }
   }
   CK(c->jobs.ensure(nJobs * sizeof(vb::JobState)));
   CK(c->views.ensure(nViews * sizeof(vb::ViewState)));
@@ -882,9 +919,10 @@ int vslamb200_align(vslamb200_ctx * c, const vslamb200_job * jobs, int nJobs, vs
   // Jobs stop after different numbers of iterations, so every level kernel ends with a tail of a few long-running
   // clusters.  A large batch is therefore cut into two halves that walk down the pyramid on their own streams: one
   // half's tail is filled by the other half's next kernel.  (Timing mode keeps one stream: it measures whole launches.)
-  int nParts = (!c->timing && nJobs >= 2 * kMinJobsPerPart) ? 2 : 1;
+  int nParts = (!c->timing && nJobs >= 2 * kMinJobsPerPart && sp.sampling == VSLAMB200_SAMPLING_NEAREST) ? 2 : 1;
   if (const char * e = std::getenv("VSLAMB200_PARTS")) nParts = std::max(1, std::min(vslamb200_ctx::kMaxParts, std::atoi(e)));
   nParts = std::min(nParts, nJobs);
+  if (sp.sampling != VSLAMB200_SAMPLING_NEAREST) nParts = 1;  // the extension's host loop reads one active-job counter
   if (nParts == 1) {
     for (int level = P.nLevels - 1; level >= 0; level--)
       if (int e = run_level(c, P, level, sp, sp.maxIterations + 1, 0, nJobs, c->stream)) return e;
@@ -961,6 +999,8 @@ int vslamb200_evaluate(
   Problem P;
   if (int e = build_problem(c, &job, 1, P)) return e;
   if (level < 0 || level >= P.nLevels) return fail(VSLAMB200_EINVAL, "evaluate: no such level");
+  if (c->cfg.sampling != VSLAMB200_SAMPLING_NEAREST)
+    return fail(VSLAMB200_EINVAL, "evaluate: single evaluations are defined for nearest-pixel sampling only");
   vb::SolverParams sp = solver_params(c->cfg);
   sp.includePrior = 0;
   const int savedTrace = c->traceEnabled;

@@ -75,6 +75,14 @@ struct ViewState
   // be re-evaluated; per LIST_TILE 8 floats: u, v, 1/depth ranges of the tile's points, cumulative motion bound, spare
   float * lim;
   float * tileState;
+  // bilinear extension (ext.cu): per list entry {r_I, r_Z} of the current iteration (NaN = not visible / no depth),
+  // per 2048-entry block the 28 partial sums, scale of the depth residuals
+  double2 * extR;
+  double * extPart;
+  double scaleZ;
+  const float * Zt;         // target depth(level)
+  const int16_t * gxt;      // target dIx(level), dIy(level)
+  const int16_t * gyt;
   double scale, offset;
 };
 
@@ -92,7 +100,8 @@ struct JobState
   double chi2Prev;
   // Levenberg-Marquardt (extension): damping, b and chi2 of the last accepted evaluation (its A is lastA)
   double lambda, bAcc[6], chi2Acc;
-  int accepted, lmPad;
+  int accepted;
+  int extCount;            // ext.cu: blocks of the job that have delivered their partial sums in this evaluation
   int iter;                 // Gauss-Newton iteration index within the level
   int nPushed;              // completed steps within the level
   int active;               // 1 while the level's solve is running
@@ -120,6 +129,8 @@ struct SolverParams
   int includePrior;
   int solverKind;            // VSLAMB200_SOLVER_*
   double lmLambda0, lmUp, lmDown;
+  int sampling;              // VSLAMB200_SAMPLING_*
+  double depthWeight;
 };
 
 // ------------------------------------------------------------------------------------------------
@@ -274,6 +285,11 @@ void launch_scatter_rcode(const ViewState * views, int view, int16_t * plane, cu
 size_t gn_level_static_smem();
 cudaError_t launch_gn_level(JobState * jobs, ViewState * views, int job0, int nJobs, int maxViewsPerJob, int clusterSize,
                             SolverParams p, int level, int maxEvals, double * trace, size_t traceJobStride, double * viewSums, cudaStream_t s);
+// ext.cu (bilinear / depth-residual extension): one Gauss-Newton (or LM) evaluation + step for every active job
+constexpr int EXT_CHUNK = 2048;  // list entries per block
+void launch_ext_iteration(JobState * jobs, ViewState * views, int job0, int nJobs, int view0, int nViews, int maxPoints,
+                          SolverParams p, int level, bool forceStop, double * trace, size_t traceJobStride, int * activeCount,
+                          cudaStream_t s);
 // gn_inc.cu (incremental level kernel: single keyframe, zero-offset scalers)
 cudaError_t launch_gn_inc(JobState * jobs, ViewState * views, int job0, int nJobs, SolverParams p, int level, int maxEvals,
                           double * trace, size_t traceJobStride, int checkMode, cudaStream_t s);

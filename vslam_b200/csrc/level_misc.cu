@@ -28,6 +28,10 @@ __global__ void level_setup_kernel(
   V.Wt = ft.W[level];
   V.Ht = ft.H[level];
   V.I = ft.I[level];
+  V.Zt = ft.Z[level];
+  V.gxt = ft.gx[level];
+  V.gyt = ft.gy[level];
+  V.scaleZ = 1.0;
   V.fx = ff.cam[level][0];
   V.fy = ff.cam[level][1];
   V.cx = ff.cam[level][2];
