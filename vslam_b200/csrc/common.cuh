@@ -84,6 +84,7 @@ struct ViewState
   const int16_t * gxt;      // target dIx(level), dIy(level)
   const int16_t * gyt;
   double scale, offset;
+  double scaleAcc, offsetAcc;  // Levenberg-Marquardt: the scale of the last accepted evaluation (what the trace reports)
 };
 
 struct JobState

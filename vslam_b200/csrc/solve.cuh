@@ -406,10 +406,13 @@ __device__ __forceinline__ void lm_step_block(
   __syncthreads();
   const bool rejected = X.dChi2 != 0.0;
   if (tid < K) {
-    if (rejected)
+    if (rejected) {
       jv[tid].se3 = jv[tid].se3Acc;
-    else
+    } else {
       jv[tid].se3Acc = jv[tid].se3;
+      jv[tid].scaleAcc = jv[tid].scale;
+      jv[tid].offsetAcc = jv[tid].offset;
+    }
   }
   __syncthreads();
   // ---- 3. damped solve (thread 0: determinant, thread 32: step)
@@ -463,8 +466,8 @@ __device__ __forceinline__ void lm_step_block(
         t[1] = (double)X.nTotal;
         t[2] = J.chi2Acc;
         t[3] = step;
-        t[4] = jv[0].scale;
-        t[5] = jv[0].offset;
+        t[4] = jv[0].scaleAcc;
+        t[5] = jv[0].offsetAcc;
         for (int k = 0; k < 6; k++) t[6 + k] = jv[0].xCur[k];
         for (int k = 0; k < 6; k++) t[12 + k] = J.bAcc[k];
         for (int k = 0; k < 36; k++) t[18 + k] = J.lastA[k];
