@@ -45,7 +45,10 @@ constexpr int CTAS_PER_SM = 2;
 constexpr int NC = 256;            // residual magnitudes 0..255
 constexpr int MT = 27;             // moments per magnitude: 21 (upper A) + 6 (b)
 constexpr int JS = 7;              // doubles per stashed point: 6 scaled Jacobian components + the b-term scale
-constexpr int QCAP = 64;           // queue entries per warp (at most 31 left over + 32 new)
+constexpr int EB = 4;              // re-evaluation super-batch: EB points per lane, all loads of a round trip in flight together
+constexpr int QE = 256;            // evaluation queue per warp (circular): < 32 EB left over + one tile of 128 new entries
+constexpr int QC = 160;            // change queue per warp: <= 31 left over + 32 EB new entries
+constexpr float LIMQ = 2048.f;     // limits and accumulated motion bounds are compared as 16-bit fixed point, 1/2048 px
 constexpr double BSCALE = 1048576.0;  // 2^20: extra scale of the b moments (|sum_k J'_ki| <= 2^10 * 2^30.5)
 constexpr int NCHUNK = 8;          // the A-from-moments pass splits the 256 magnitudes into 8 chunks of 32
 constexpr unsigned FLAGGED = 0x80000000u;  // eval-queue entry: the motion bound asked for this point (check mode)
@@ -78,13 +81,13 @@ struct Shared
   int redi[NW];
   unsigned long long nFlagged, nChanged, nMissed;
 };
-// dynamic shared memory: Mlo u32[NC][MT] | Mhi u32[NC][MT] | stash double[NW][32][JS] | evalQ u32[NW][QCAP] |
-// changeQ uint2[NW][QCAP]
+// dynamic shared memory: Mlo u32[NC][MT] | Mhi u32[NC][MT] | stash double[NW][32][JS] | evalQ u32[NW][QE] |
+// changeQ u32[NW][QC]
 constexpr size_t OFF_MHI = (size_t)NC * MT * 4;
 constexpr size_t OFF_STASH = OFF_MHI + (size_t)NC * MT * 4;
 constexpr size_t OFF_EVALQ = OFF_STASH + (size_t)NW * 32 * JS * 8;
-constexpr size_t OFF_CHGQ = OFF_EVALQ + (size_t)NW * QCAP * 4;
-constexpr size_t DYN_BYTES = OFF_CHGQ + (size_t)NW * QCAP * 8;
+constexpr size_t OFF_CHGQ = OFF_EVALQ + (size_t)NW * QE * 4;
+constexpr size_t DYN_BYTES = OFF_CHGQ + (size_t)NW * QC * 4;
 
 template <typename T>
 __device__ __forceinline__ void block_copy(T * dst, const T * src)
@@ -131,35 +134,73 @@ __device__ __forceinline__ void term_pair(int t, int & i, int & j)
   }
 }
 
-// Sampled target pixel (or -1) of one interest point and the margin by which its projection may still move (in
-// the max-norm, pixels) before the sampled pixel or the visibility can change.  Same decisions as the dense
-// kernel's warp_pick_ring / warp_exact pair (warp_filter.cuh).
-__device__ __forceinline__ int warp_point(const WarpConsts & c, const ViewState & V, uint32_t pk, float d, float & margin)
+// Sampled target pixel (or -1) of one interest point and the DIRECTIONAL margins by which its projection may still
+// move before the sampled pixel or the visibility can change: m[0] towards +u, m[1] towards -u, m[2] towards +v,
+// m[3] towards -v (pixels).  Same decisions as the dense kernel's warp_pick_ring / warp_exact pair (warp_filter.cuh).
+// With u' = iu + fu, fu in [-0.5, 0.5], the rounded pixel changes at fu = +-0.5; on the visibility ring (iu == 1 or
+// iu == W-1: visible iff u' > 1 resp. u' < W-1, InverseCompositional.cpp:115-116) the nearer boundary is fu = 0.
+__device__ __forceinline__ int warp_point(const WarpConsts & c, const ViewState & V, uint32_t pk, float d, float (&m)[4])
 {
   const WarpEval e = warp_eval(c, pk, d);
   const int iu = e.iu, iv = e.iv;
-  const float au = fabsf(e.fu), av = fabsf(e.fv);
+  float pu = 0.5f - e.fu, nu = 0.5f + e.fu, pv = 0.5f - e.fv, nv = 0.5f + e.fv;
   const bool ringu = iu == 1 || iu == c.Wt - 1, ringv = iv == 1 || iv == c.Ht - 1;
-  float dist = 0.5f - fmaxf(au, av);
-  dist = ringu ? fminf(dist, au) : dist;
-  dist = ringv ? fminf(dist, av) : dist;
+  if (ringu) {
+    if (e.fu > 0.f) nu = e.fu; else pu = -e.fu;
+  }
+  if (ringv) {
+    if (e.fv > 0.f) nv = e.fv; else pv = -e.fv;
+  }
+  const float dist = fminf(fminf(pu, nu), fminf(pv, nv));
   const bool ok = e.okb && dist > e.eps;
   bool vis = (unsigned)(iu - 1) <= (unsigned)(c.Wt - 2) && (unsigned)(iv - 1) <= (unsigned)(c.Ht - 2);
   vis = vis && !(iu == 1 && e.fu < 0.f) && !(iu == c.Wt - 1 && e.fu > 0.f);
   vis = vis && !(iv == 1 && e.fv < 0.f) && !(iv == c.Ht - 1 && e.fv > 0.f);
-  margin = ok ? dist - e.eps : 0.f;
+  const float slack = e.eps + 2e-5f;  // the fp32 evaluation's own error, the rounding of the limit arithmetic
+  m[0] = ok ? pu - slack : 0.f;
+  m[1] = ok ? nu - slack : 0.f;
+  m[2] = ok ? pv - slack : 0.f;
+  m[3] = ok ? nv - slack : 0.f;
   if (!ok) return warp_exact(V, pk & 0xfff, (pk >> 12) & 0xfff, d);
   return vis ? iv * c.Wt + iu : -1;
 }
 
-// Upper bound (pixels, max-norm) of the image motion that one Gauss-Newton step causes for ANY point whose
-// template pixel lies in [ulo,uhi] x [vlo,vhi] and whose inverse depth lies in [zlo,zhi].
+// 16-bit fixed-point forms (1/2048 px): a limit is rounded DOWN, an accumulated bound UP, so the comparison
+// accumulated >= limit never flags later than the real numbers would.  NaN limit -> 0 (always flagged), NaN or
+// infinite bound -> 65535 (flags everything; limits saturate at 65535 too).
+__device__ __forceinline__ uint32_t limit_q(float x)
+{
+  const float y = x * LIMQ;
+  return y > 0.f ? (uint32_t)__float2int_rd(fminf(y, 65535.f)) : 0u;
+}
+__device__ __forceinline__ uint32_t bound_q(float x)
+{
+  const float y = x * LIMQ;
+  return y < 65535.f ? (uint32_t)__float2int_ru(fmaxf(y, 0.f)) : 65535u;
+}
+// the point's limits {+u | -u << 16, +v | -v << 16} given the tile's accumulated bounds at evaluation time
+__device__ __forceinline__ uint2 point_limits(const float4 acc, const float (&m)[4])
+{
+  return make_uint2(limit_q(acc.x + m[0]) | (limit_q(acc.y + m[1]) << 16), limit_q(acc.z + m[2]) | (limit_q(acc.w + m[3]) << 16));
+}
+__device__ __forceinline__ uint2 bounds_q(const float4 acc)
+{
+  return make_uint2(bound_q(acc.x) | (bound_q(acc.y) << 16), bound_q(acc.z) | (bound_q(acc.w) << 16));
+}
+__device__ __forceinline__ bool limit_reached(const uint2 accq, const uint2 lim)
+{
+  return (__vcmpgeu2(accq.x, lim.x) | __vcmpgeu2(accq.y, lim.y)) != 0u;
+}
+
+// Upper bounds (pixels) of the image motion that one Gauss-Newton step causes, per direction (+u, -u, +v, -v), for
+// ANY point whose template pixel lies in [ulo,uhi] x [vlo,vhi] and whose inverse depth lies in [zlo,zhi].
 // With p = d (xn, yn, 1), zi = 1/d:  q_a = T_a p,  q_b = T_a (dT p)  =>  with s = q_a / d = R_a (xn,yn,1) + t_a zi,
 // m = ((dR - I)(xn,yn,1) + dt zi),  g = R_a m = (q_b - q_a) / d, the projected x' = q_x / q_z moves by EXACTLY
 //     dx' = (g_x - x'_a g_z) / (s_z + g_z),      x'_a = s_x / s_z,
 // s, m, g are affine in (xn, yn, zi), so centre +- radius intervals bound them without slack; the products are
-// bounded term by term.  The result is inflated by 1 % + 1e-5 px, which covers the fp32 evaluation of the bound.
-__device__ __forceinline__ float tile_motion_bound(const StepConsts & k, float ulo, float uhi, float vlo, float vhi, float zlo, float zhi)
+// bounded term by term; the denominator is positive.  The numerator's interval [c - r, c + r] gives the two signed
+// bounds.  Each is inflated by 1 % + 1e-5 px, which covers the fp32 evaluation of the bound.
+__device__ __forceinline__ float4 tile_motion_bound(const StepConsts & k, float ulo, float uhi, float vlo, float vhi, float zlo, float zhi)
 {
   const float xlo = fmaf(k.ifx, ulo, k.kx), xhi = fmaf(k.ifx, uhi, k.kx);
   const float ylo = fmaf(k.ify, vlo, k.ky), yhi = fmaf(k.ify, vhi, k.ky);
@@ -180,18 +221,25 @@ __device__ __forceinline__ float tile_motion_bound(const StepConsts & k, float u
     gr[i] = fabsf(k.Ro[3 * i]) * mr[0] + fabsf(k.Ro[3 * i + 1]) * mr[1] + fabsf(k.Ro[3 * i + 2]) * mr[2];
   }
   const float INF = __int_as_float(0x7f800000);
+  const float4 ALL = make_float4(INF, INF, INF, INF);
   const float szmin = sc[2] - sr[2];
-  if (!(szmin > 0.25f)) return INF;
+  if (!(szmin > 0.25f)) return ALL;
   const float gz = fabsf(gc[2]) + gr[2];
   const float den = szmin - gz;
-  if (!(den > 0.125f)) return INF;
+  if (!(den > 0.125f)) return ALL;
   const float isz = 1.f / sc[2], iszmin = 1.f / szmin;
   const float xpc = sc[0] * isz, xpr = (sr[0] + fabsf(xpc) * sr[2]) * iszmin;
   const float ypc = sc[1] * isz, ypr = (sr[1] + fabsf(ypc) * sr[2]) * iszmin;
-  const float nu = fabsf(fmaf(-xpc, gc[2], gc[0])) + gr[0] + fabsf(xpc) * gr[2] + xpr * gz;
-  const float nv = fabsf(fmaf(-ypc, gc[2], gc[1])) + gr[1] + fabsf(ypc) * gr[2] + ypr * gz;
-  const float b = fmaxf(k.fx * nu, k.fy * nv) / den;
-  return fmaf(b, 1.01f, 1e-5f);  // NaN propagates and flags everything (comparisons below are written for that)
+  const float cu = fmaf(-xpc, gc[2], gc[0]), ru = gr[0] + fabsf(xpc) * gr[2] + xpr * gz;
+  const float cv = fmaf(-ypc, gc[2], gc[1]), rv = gr[1] + fabsf(ypc) * gr[2] + ypr * gz;
+  const float su = k.fx / den, sv = k.fy / den;
+  // NaN propagates (fmaxf would drop it: keep the sums explicit) and flags everything through bound_q
+  float4 b;
+  b.x = fmaf(su * (ru + cu > 0.f ? ru + cu : (ru + cu == ru + cu ? 0.f : ru + cu)), 1.01f, 1e-5f);
+  b.y = fmaf(su * (ru - cu > 0.f ? ru - cu : (ru - cu == ru - cu ? 0.f : ru - cu)), 1.01f, 1e-5f);
+  b.z = fmaf(sv * (rv + cv > 0.f ? rv + cv : (rv + cv == rv + cv ? 0.f : rv + cv)), 1.01f, 1e-5f);
+  b.w = fmaf(sv * (rv - cv > 0.f ? rv - cv : (rv - cv == rv - cv ? 0.f : rv - cv)), 1.01f, 1e-5f);
+  return b;
 }
 
 __device__ __forceinline__ void moment_add(uint32_t * Mlo, uint32_t * Mhi, int code, int lane, long long v, bool subtract)
@@ -274,8 +322,8 @@ __global__ void __launch_bounds__(NT, CTAS_PER_SM) gn_inc_kernel(
   uint32_t * Mlo = reinterpret_cast<uint32_t *>(dyn);
   uint32_t * Mhi = reinterpret_cast<uint32_t *>(dyn + OFF_MHI);
   double * stash = reinterpret_cast<double *>(dyn + OFF_STASH) + warp * 32 * JS;
-  uint32_t * evalQ = reinterpret_cast<uint32_t *>(dyn + OFF_EVALQ) + warp * QCAP;
-  uint2 * chgQ = reinterpret_cast<uint2 *>(dyn + OFF_CHGQ) + warp * QCAP;
+  uint32_t * evalQ = reinterpret_cast<uint32_t *>(dyn + OFF_EVALQ) + warp * QE;
+  uint32_t * chgQ = reinterpret_cast<uint32_t *>(dyn + OFF_CHGQ) + warp * QC;
 
   block_copy(&S.J, jobs + job);
   __syncthreads();
@@ -289,7 +337,8 @@ __global__ void __launch_bounds__(NT, CTAS_PER_SM) gn_inc_kernel(
   const int n = V.nIp;
   const int nTiles = (n + LIST_TILE - 1) / LIST_TILE;
   const uint8_t * __restrict__ I = V.I;
-  float * lim = V.lim;
+  uint2 * lim = reinterpret_cast<uint2 *>(V.lim);  // per list entry: 4 x 16-bit limits {+u | -u, +v | -v}
+  // per tile 8 words: ulo | uhi << 16, vlo | vhi << 16, zlo, zhi (1/depth range), accumulated bounds +u, -u, +v, -v
   float * tileState = V.tileState;
   int16_t * rcode = V.r;
   int ti, tj;
@@ -318,6 +367,7 @@ __global__ void __launch_bounds__(NT, CTAS_PER_SM) gn_inc_kernel(
     if (first) {
       // ---------------------------------------------------------------- first evaluation: every point
       float sq[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};  // sum_k J_ki^2 (fp32, for the fixed-point scales)
+      const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
       for (int tile = warp; tile < nTiles; tile += NW) {
         const unsigned char * tp = V.tiles + (size_t)tile * LIST_TILE_BYTES;
         const int g0 = tile * LIST_TILE + 4 * lane;
@@ -328,17 +378,17 @@ __global__ void __launch_bounds__(NT, CTAS_PER_SM) gn_inc_kernel(
         const float dd[4] = {dd4.x, dd4.y, dd4.z, dd4.w};
         const uint32_t gg[4] = {gg4.x, gg4.y, gg4.z, gg4.w};
         int code[4];
-        float lm[4];
+        uint2 lq[4];
         unsigned ulo = 0xffffffffu, uhi = 0u, vlo = 0xffffffffu, vhi = 0u, zlo = 0xffffffffu, zhi = 0u;
 #pragma unroll
         for (int q = 0; q < 4; q++) {
           const bool in = g0 + q < n;
-          float margin;
-          int pix = warp_point(c, V, pk[q], dd[q], margin);  // padding lanes compute on stale data: harmless
+          float m[4];
+          int pix = warp_point(c, V, pk[q], dd[q], m);  // padding lanes compute on stale data: harmless
           pix = in ? pix : -1;
           const int val = pix >= 0 ? (int)__ldg(I + pix) : 0;
           code[q] = pix >= 0 ? val - (int)(pk[q] >> 24) + 255 : R_CODE_INVISIBLE;
-          lm[q] = in ? margin - 1e-6f : __int_as_float(0x7f800000);
+          lq[q] = point_limits(zero4, m);
           if (code[q] != R_CODE_INVISIBLE) atomicAdd(&S.hist[code[q]], 1);
           if (in) {
             const unsigned ui = pk[q] & 0xfff, vi = (pk[q] >> 12) & 0xfff;
@@ -362,15 +412,18 @@ __global__ void __launch_bounds__(NT, CTAS_PER_SM) gn_inc_kernel(
         if (g0 < n) {
           reinterpret_cast<uint2 *>(rcode + tile * LIST_TILE)[lane] =
             make_uint2((uint32_t)code[0] | ((uint32_t)code[1] << 16), (uint32_t)code[2] | ((uint32_t)code[3] << 16));
-          reinterpret_cast<float4 *>(lim + tile * LIST_TILE)[lane] = make_float4(lm[0], lm[1], lm[2], lm[3]);
+          uint4 * lp = reinterpret_cast<uint4 *>(lim + tile * LIST_TILE + 4 * lane);
+          lp[0] = make_uint4(lq[0].x, lq[0].y, lq[1].x, lq[1].y);
+          lp[1] = make_uint4(lq[2].x, lq[2].y, lq[3].x, lq[3].y);
         }
         ulo = __reduce_min_sync(0xffffffffu, ulo); uhi = __reduce_max_sync(0xffffffffu, uhi);
         vlo = __reduce_min_sync(0xffffffffu, vlo); vhi = __reduce_max_sync(0xffffffffu, vhi);
         zlo = __reduce_min_sync(0xffffffffu, zlo); zhi = __reduce_max_sync(0xffffffffu, zhi);
         if (lane == 0) {
           float4 * ts = reinterpret_cast<float4 *>(tileState + tile * 8);
-          ts[0] = make_float4((float)ulo, (float)uhi, (float)vlo, (float)vhi);
-          ts[1] = make_float4(__uint_as_float(zlo) * 0.9999f, __uint_as_float(zhi) * 1.0001f, 0.f, 0.f);  // 1/d was approximate
+          ts[0] = make_float4(__uint_as_float(ulo | (uhi << 16)), __uint_as_float(vlo | (vhi << 16)),
+                              __uint_as_float(zlo) * 0.9999f, __uint_as_float(zhi) * 1.0001f);  // 1/d was approximate
+          ts[1] = zero4;
         }
       }
       lap(0);
@@ -417,96 +470,134 @@ __global__ void __launch_bounds__(NT, CTAS_PER_SM) gn_inc_kernel(
       lap(1);
     } else {
       // ---------------------------------------------------------------- later evaluations
-      // motion bound of the last step per tile (one lane per tile), accumulated
+      // directional motion bounds of the last step per tile (one lane per tile), accumulated
       for (int t0 = warp; t0 < nTiles; t0 += NW * 32) {
         const int tile = t0 + NW * lane;
         if (tile < nTiles) {
           float4 * ts = reinterpret_cast<float4 *>(tileState + tile * 8);
           const float4 a = ts[0];
-          float4 b = ts[1];
-          b.z += tile_motion_bound(S.stp, a.x, a.y, a.z, a.w, b.x, b.y);
-          ts[1] = b;
+          float4 acc = ts[1];
+          const unsigned uw = __float_as_uint(a.x), vw = __float_as_uint(a.y);
+          const float4 b = tile_motion_bound(S.stp, (float)(uw & 0xffff), (float)(uw >> 16), (float)(vw & 0xffff),
+                                             (float)(vw >> 16), a.z, a.w);
+          acc.x += b.x; acc.y += b.y; acc.z += b.z; acc.w += b.w;
+          ts[1] = acc;
         }
       }
       __syncwarp();
-      int qe = 0, qc = 0;  // entries in this warp's eval / change queues (warp-uniform)
-      // re-evaluates `cnt` queued points (lane l < cnt owns evalQ[l]); changed residuals go to the change queue
-      auto eval_batch = [&](int cnt) {
-        const unsigned ent = lane < cnt ? evalQ[lane] : 0u;
-        const int idx = (int)(ent & ~FLAGGED);
-        bool ch = false;
-        int oldc = R_CODE_INVISIBLE, code = R_CODE_INVISIBLE;
+      int qh = 0, qe = 0, qc = 0;  // evaluation queue: head and fill (circular); change queue fill.  Warp-uniform
+      // moves the moments of the last `cnt` (<= 32) entries of the change queue: list index | new code << 20
+      auto move_batch = [&](int cnt) {
+        const uint32_t e = lane < cnt ? chgQ[qc - cnt + lane] : 0u;
+        const int idx = (int)(e & 0xfffffu);
+        int oldc = R_CODE_INVISIBLE, newc = R_CODE_INVISIBLE;
         if (lane < cnt) {
-          const int tile = idx / LIST_TILE, j = idx % LIST_TILE;
-          const unsigned char * tp = V.tiles + (size_t)tile * LIST_TILE_BYTES;
-          const uint32_t pk = reinterpret_cast<const uint32_t *>(tp + TILE_OFF_UVT)[j];
-          const float d = reinterpret_cast<const float *>(tp + TILE_OFF_D)[j];
+          newc = (int)(e >> 20);
           oldc = (int)(uint16_t)rcode[idx];
-          const float B = tileState[tile * 8 + 6];
-          float margin;
-          const int pix = warp_point(c, V, pk, d, margin);
-          const int val = pix >= 0 ? (int)__ldg(I + pix) : 0;
-          code = pix >= 0 ? val - (int)(pk >> 24) + 255 : R_CODE_INVISIBLE;
-          ch = code != oldc;
-          if (ent & FLAGGED) lim[idx] = B + margin - 1e-6f;
-          if (ch) {
-            rcode[idx] = (int16_t)code;
-            if (oldc != R_CODE_INVISIBLE) atomicSub(&S.hist[oldc], 1);
-            if (code != R_CODE_INVISIBLE) atomicAdd(&S.hist[code], 1);
-          }
+          rcode[idx] = (int16_t)newc;
+          if (oldc != R_CODE_INVISIBLE) atomicSub(&S.hist[oldc], 1);
+          if (newc != R_CODE_INVISIBLE) atomicAdd(&S.hist[newc], 1);
         }
-        const unsigned m = __ballot_sync(0xffffffffu, ch);
-        if (lane == 0) myChanged += __popc(m);
-        const unsigned miss = __ballot_sync(0xffffffffu, ch && !(ent & FLAGGED));
-        if (lane == 0) myMissed += __popc(miss);
-        if (m) {
-          if (ch) chgQ[qc + __popc(m & ((1u << lane) - 1u))] = make_uint2((uint32_t)idx, (uint32_t)oldc | ((uint32_t)code << 16));
-          qc += __popc(m);
-          __syncwarp();
-          if (qc >= 32) {
-            const uint2 e = chgQ[lane];
-            move_moments(V, S.scaleJ, Mlo, Mhi, stash, 32, (int)e.x, (int)(e.y & 0xffff), (int)(e.y >> 16), ti, tj);
-            const uint2 rest = lane + 32 < qc ? chgQ[lane + 32] : make_uint2(0, 0);
-            __syncwarp();
-            if (lane + 32 < qc) chgQ[lane] = rest;
-            qc -= 32;
-            __syncwarp();
-          }
-        }
+        move_moments(V, S.scaleJ, Mlo, Mhi, stash, cnt, idx, oldc, newc, ti, tj);
+        qc -= cnt;
       };
-      for (int tile = warp; tile < nTiles; tile += NW) {
-        const int g0 = tile * LIST_TILE + 4 * lane;
-        const float B = tileState[tile * 8 + 6];
-        const float4 l4 = reinterpret_cast<const float4 *>(lim + tile * LIST_TILE)[lane];
-        const float lm[4] = {l4.x, l4.y, l4.z, l4.w};
+      // re-evaluates the first `cnt` (<= 32 EB) queued points; lane l owns entries l, l + 32, ...  All loads of a
+      // round trip (list entry, residual code and tile bounds; then the target pixels) are in flight together.
+      auto eval_batch = [&](int cnt) {
+        uint32_t ent[EB], pk[EB];
+        float d[EB];
+        int oldc[EB], pix[EB], val[EB];
+        float4 acc[EB];
+        uint2 lq[EB];
 #pragma unroll
-        for (int q = 0; q < 4; q++) {
-          const bool in = g0 + q < n;
-          const bool fl = in && !(B < lm[q]);      // also true when the bound is NaN
-          const bool ev = fl || (checkMode && in);  // check mode looks at every point; only flagged ones may change
-          const unsigned m = __ballot_sync(0xffffffffu, ev);
-          const unsigned mf = __ballot_sync(0xffffffffu, fl);
-          if (lane == 0) myFlagged += __popc(mf);
-          if (m) {
-            if (ev) evalQ[qe + __popc(m & ((1u << lane) - 1u))] = (uint32_t)(g0 + q) | (fl ? FLAGGED : 0u);
-            qe += __popc(m);
-            __syncwarp();
-            if (qe >= 32) {
-              eval_batch(32);
-              const uint32_t rest = lane + 32 < qe ? evalQ[lane + 32] : 0u;
-              __syncwarp();
-              if (lane + 32 < qe) evalQ[lane] = rest;
-              qe -= 32;
-              __syncwarp();
-            }
+        for (int j = 0; j < EB; j++) {
+          const bool on = j * 32 + lane < cnt;
+          ent[j] = on ? evalQ[(qh + j * 32 + lane) & (QE - 1)] : 0xffffffffu;
+        }
+#pragma unroll
+        for (int j = 0; j < EB; j++) {
+          pk[j] = 0u; d[j] = 1.f; oldc[j] = R_CODE_INVISIBLE; acc[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (ent[j] != 0xffffffffu) {
+            const int idx = (int)(ent[j] & ~FLAGGED);
+            const int tile = idx / LIST_TILE, k = idx % LIST_TILE;
+            const unsigned char * tp = V.tiles + (size_t)tile * LIST_TILE_BYTES;
+            pk[j] = reinterpret_cast<const uint32_t *>(tp + TILE_OFF_UVT)[k];
+            d[j] = reinterpret_cast<const float *>(tp + TILE_OFF_D)[k];
+            oldc[j] = (int)(uint16_t)rcode[idx];
+            acc[j] = reinterpret_cast<const float4 *>(tileState + tile * 8)[1];
           }
         }
+#pragma unroll
+        for (int j = 0; j < EB; j++) {
+          float m[4];
+          pix[j] = warp_point(c, V, pk[j], d[j], m);
+          lq[j] = point_limits(acc[j], m);
+          if (ent[j] == 0xffffffffu) pix[j] = -1;
+        }
+#pragma unroll
+        for (int j = 0; j < EB; j++) val[j] = pix[j] >= 0 ? (int)__ldg(I + pix[j]) : 0;
+#pragma unroll
+        for (int j = 0; j < EB; j++) {
+          const bool on = ent[j] != 0xffffffffu;
+          const int idx = (int)(ent[j] & ~FLAGGED);
+          const int code = pix[j] >= 0 ? val[j] - (int)(pk[j] >> 24) + 255 : R_CODE_INVISIBLE;
+          const bool ch = on && code != oldc[j];
+          if (on && (ent[j] & FLAGGED)) lim[idx] = lq[j];
+          const unsigned mch = __ballot_sync(0xffffffffu, ch);
+          if (lane == 0) myChanged += __popc(mch);
+          if (checkMode) {
+            const unsigned miss = __ballot_sync(0xffffffffu, ch && !(ent[j] & FLAGGED));
+            if (lane == 0) myMissed += __popc(miss);
+          }
+          if (ch) chgQ[qc + __popc(mch & ((1u << lane) - 1u))] = (uint32_t)idx | ((uint32_t)code << 20);
+          qc += __popc(mch);
+        }
+        qh = (qh + cnt) & (QE - 1);
+        qe -= cnt;
+        __syncwarp();
+        while (qc >= 32) move_batch(32);
+      };
+      // scan: two tiles per step, their limits and bounds loaded together
+      for (int tile0 = warp; tile0 < nTiles; tile0 += 2 * NW) {
+        uint4 la[2][2];
+        float4 accv[2];
+#pragma unroll
+        for (int t = 0; t < 2; t++) {
+          const int tile = tile0 + t * NW;
+          if (tile < nTiles) {
+            const uint4 * lp = reinterpret_cast<const uint4 *>(lim + tile * LIST_TILE + 4 * lane);
+            la[t][0] = lp[0];
+            la[t][1] = lp[1];
+            accv[t] = reinterpret_cast<const float4 *>(tileState + tile * 8)[1];
+          }
+        }
+#pragma unroll
+        for (int t = 0; t < 2; t++) {
+          const int tile = tile0 + t * NW;
+          if (tile >= nTiles) break;
+          const int g0 = tile * LIST_TILE + 4 * lane;
+          const uint2 aq = bounds_q(accv[t]);
+          const uint2 lm[4] = {make_uint2(la[t][0].x, la[t][0].y), make_uint2(la[t][0].z, la[t][0].w),
+                               make_uint2(la[t][1].x, la[t][1].y), make_uint2(la[t][1].z, la[t][1].w)};
+#pragma unroll
+          for (int q = 0; q < 4; q++) {
+            const bool in = g0 + q < n;
+            const bool fl = in && limit_reached(aq, lm[q]);
+            const bool ev = fl || (checkMode && in);  // check mode looks at every point; only flagged ones may change
+            const unsigned m = __ballot_sync(0xffffffffu, ev);
+            if (checkMode || m) {
+              const unsigned mf = __ballot_sync(0xffffffffu, fl);
+              if (lane == 0) myFlagged += __popc(mf);
+            }
+            if (ev) evalQ[(qh + qe + __popc(m & ((1u << lane) - 1u))) & (QE - 1)] = (uint32_t)(g0 + q) | (fl ? FLAGGED : 0u);
+            qe += __popc(m);
+          }
+          __syncwarp();
+          if (qe >= 32 * EB) eval_batch(32 * EB);
+        }
       }
-      if (qe > 0) eval_batch(qe);
-      if (qc > 0) {
-        const uint2 e = lane < qc ? chgQ[lane] : make_uint2(0u, (uint32_t)R_CODE_INVISIBLE | ((uint32_t)R_CODE_INVISIBLE << 16));
-        move_moments(V, S.scaleJ, Mlo, Mhi, stash, qc, (int)e.x, (int)(e.y & 0xffff), (int)(e.y >> 16), ti, tj);
-      }
+      while (qe > 0) eval_batch(min(qe, 32 * EB));
+      if (qc > 0) move_batch(qc);
       lap(0);
     }
     __syncthreads();
