@@ -112,6 +112,7 @@ typedef struct vslamb200_stats
      second cluster barrier, weight table */
   uint64_t phase_clocks[VSLAMB200_MAX_LEVELS][10];
   uint64_t incremental_launches; /* level launches that ran the incremental (per-residual moments) kernel */
+  uint64_t bounded_launches;     /* level launches of the cluster kernel whose phase A re-evaluates only flagged points */
 } vslamb200_stats;
 
 const char * vslamb200_last_error(void);

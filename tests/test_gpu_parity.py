@@ -31,17 +31,25 @@ def _upload(ctx, p, levels, ids=(1, 2)):
     ctx.upload(np.array(ids), np.stack([p["gray0"], p["gray1"]]), np.stack([p["depth0"], p["depth1"]]), p["cam"], levels)
 
 
-@pytest.fixture(params=["dense", "incremental"])
+@pytest.fixture(params=["dense", "bounded", "incremental"])
 def level_kernel(request, monkeypatch):
-    """Both Gauss-Newton level kernels: the dense one (gn_level.cu) and the incremental per-residual-moments one
-    (gn_inc.cu; forced on every level it supports - one keyframe per job, scaler without offset)."""
-    monkeypatch.setenv("VSLAMB200_INC", "0" if request.param == "dense" else "2")
+    """The Gauss-Newton level kernels: the cluster kernel with the dense phase A (gn_level.cu), its bounded variant
+    (phase A re-evaluates only the points whose sampled pixel can have changed; forced on every level it supports - one
+    keyframe per job, Gauss-Newton) and the incremental per-residual-moments kernel (gn_inc.cu; forced on every level
+    it supports - one keyframe per job, scaler without offset)."""
+    monkeypatch.setenv("VSLAMB200_INC", "2" if request.param == "incremental" else "0")
+    monkeypatch.setenv("VSLAMB200_BOUND", "2" if request.param == "bounded" else "0")
     return request.param
 
 
 def _kernel_was_used(ctx, level_kernel, applicable=True):
-    n = ctx.stats()["incremental_launches"]
-    return n > 0 if (level_kernel == "incremental" and applicable) else n == 0
+    st = ctx.stats()
+    n, b = st["incremental_launches"], st["bounded_launches"]
+    if level_kernel == "incremental":
+        return (n > 0 if applicable else n == 0) and b == 0
+    if level_kernel == "bounded":
+        return b > 0 and n == 0
+    return n == 0 and b == 0
 
 
 def rel_fro(a, b):
@@ -224,13 +232,15 @@ def test_batch_of_pairs_matches_oracle(ctx, capi, oracle, synth, level_kernel):
         assert dt < 0.01 and dr < 0.01, k
 
 
-def test_incremental_motion_bounds_never_miss_a_change(capi, oracle, synth, monkeypatch):
-    """Check mode of the incremental kernel: every point is re-evaluated in every iteration, and a point whose
+@pytest.mark.parametrize("kernel", ["bounded", "incremental"])
+def test_incremental_motion_bounds_never_miss_a_change(capi, oracle, synth, monkeypatch, kernel):
+    """Check mode of the bounded cluster kernel and of the incremental kernel (they share bounds.cuh): every point is re-evaluated in every iteration, and a point whose
     residual changed although its tile's accumulated motion bound had not reached the point's limit is counted.
     The bound is rigorous, so the count must be zero - on clean pairs, pairs with depth holes, larger motions (the
     level kernels start far from the optimum on the coarse levels) and at every pyramid level."""
     O, A = oracle, capi
-    monkeypatch.setenv("VSLAMB200_INC", "2")
+    monkeypatch.setenv("VSLAMB200_INC", "2" if kernel == "incremental" else "0")
+    monkeypatch.setenv("VSLAMB200_BOUND", "2" if kernel == "bounded" else "0")
     monkeypatch.setenv("VSLAMB200_INC_CHECK", "1")
     n, L = 8, 4
     pairs = [_pair(synth, 640, 480, 4321 + k, holes=(40 if k % 2 else 0)) for k in range(n)]
@@ -248,7 +258,7 @@ def test_incremental_motion_bounds_never_miss_a_change(capi, oracle, synth, monk
         st = ctx.stats()
     finally:
         ctx.close()
-    assert st["incremental_launches"] == L
+    assert st["incremental_launches" if kernel == "incremental" else "bounded_launches"] == L
     flagged = sum(st["phase_clocks"][l][7] for l in range(L))
     changed = sum(st["phase_clocks"][l][8] for l in range(L))
     missed = sum(st["phase_clocks"][l][9] for l in range(L))

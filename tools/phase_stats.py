@@ -27,7 +27,8 @@ capi.check(capi.lib().vslamb200_set_timing(ctx.h, args.timing))
 ctx.reset_stats()
 res = ctx.align(jobs)
 st = ctx.stats()
-print("INC", os.environ.get("VSLAMB200_INC"), "incremental launches", st["incremental_launches"], "ms_gn_level",
+print("INC", os.environ.get("VSLAMB200_INC"), "BOUND", os.environ.get("VSLAMB200_BOUND"), "incremental launches", st["incremental_launches"],
+      "bounded launches", st["bounded_launches"], "ms_gn_level",
       [round(x, 3) for x in st["ms_gn_level"][:args.levels]], "ms_lists", round(st["ms_lists"], 3))
 for l in range(args.levels):
     pc = st["phase_clocks"][l]
@@ -35,6 +36,6 @@ for l in range(args.levels):
     ev = st["pixel_iterations_level"][l] / (W * H / 4 ** l)
     print(" level", l, "evals/job", round(ev / len(jobs), 2), "kclocks/job", [round(c / len(jobs) / 1e3, 1) for c in pc[:7]],
           "share", [round(c / tot, 3) for c in pc[:7]])
-    if st["incremental_launches"] and st["point_iterations"]:
+    if (st["incremental_launches"] or st["bounded_launches"]) and st["point_iterations"]:
         print("   slots 7-9 (incremental: flagged, changed, missed points; dense: scale sub-laps)", pc[7:10])
 ctx.close()

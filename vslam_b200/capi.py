@@ -46,7 +46,7 @@ class Stats(C.Structure):
                 ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64), ("ms_lists", C.c_double),
                 ("ms_preprocess", C.c_double), ("ms_gn_level", C.c_double * MAX_LEVELS),
                 ("pixel_iterations_level", C.c_uint64 * MAX_LEVELS), ("phase_clocks", (C.c_uint64 * 10) * MAX_LEVELS),
-                ("incremental_launches", C.c_uint64)]
+                ("incremental_launches", C.c_uint64), ("bounded_launches", C.c_uint64)]
 
 
 EXPORTS = [

@@ -826,8 +826,19 @@ int run_level(vslamb200_ctx * c, Problem & P, int level, const vb::SolverParams 
     c->stats.incremental_launches++;
     CK(vb::launch_gn_inc(dJobs, dViews, job0, nJobs, sp, level, maxEvals, dTrace, traceJobStride, chk && std::atoi(chk) > 0, stream));
   } else {
+    // bounded variant of the cluster kernel (phase A re-evaluates only the points whose sampled pixel can have
+    // changed; bounds.cuh): one keyframe per job and Gauss-Newton.  Exact and parity-tested, but its scan and queueing cost
+    // about as many instructions as the dense phase A saves at the 5-10 % of points the bounds flag per iteration
+    // (DESIGN.md section 4), so it is opt-in: VSLAMB200_BOUND=1 uses it on levels of at least 50 000 pixels, =2 on every
+    // level (tests).
+    int mode = 0;
+    if (const char * e = std::getenv("VSLAMB200_BOUND")) mode = std::atoi(e);
+    const bool bounded = mode > 0 && P.maxViews == 1 && sp.solverKind == VSLAMB200_SOLVER_GN && npx <= (1 << 20) &&
+                         (mode >= 2 || npx >= 50000);
+    const char * chk = std::getenv("VSLAMB200_INC_CHECK");
+    if (bounded) c->stats.bounded_launches++;
     CK(vb::launch_gn_level(dJobs, dViews, job0, nJobs, P.maxViews, cluster, sp, level, maxEvals, dTrace, traceJobStride,
-                           c->partials.as<double>(), stream));
+                           c->partials.as<double>(), stream, bounded, chk && std::atoi(chk) > 0));
   }
   if (c->timing) CK(cudaEventRecord(c->ev[2], stream));
   c->stats.kernel_launches += 6;
@@ -848,10 +859,10 @@ int prepare_workspace(vslamb200_ctx * c, Problem & P, const vb::SolverParams & s
   const int nJobs = (int)P.jobs.size(), nViews = (int)P.views.size();
   const size_t npx0 = (size_t)P.W * P.H;
   const size_t listStride = align_up(npx0, vb::LIST_TILE);
-  // per view: list tiles (20 B per candidate pixel) | r u16 | lim f32 | 32 B per tile   (26.25 bytes per candidate pixel)
+  // per view: list tiles (20 B per candidate pixel) | r u16 | lim 4 x u16 | 32 B per tile   (30.25 bytes per candidate pixel)
   const size_t tileBytes = listStride / vb::LIST_TILE * vb::LIST_TILE_BYTES;
   const size_t tileStateBytes = listStride / vb::LIST_TILE * 32;
-  const size_t viewBytes = tileBytes + listStride * 6 + tileStateBytes;
+  const size_t viewBytes = tileBytes + listStride * 10 + tileStateBytes;
   CK(c->lists.ensure(viewBytes * nViews));
   CK(c->chunkCounts.ensure((size_t)nViews * vb::list_chunks_for((int)npx0) * sizeof(int)));
   CK(c->partials.ensure((size_t)nViews * vb::NE_TERMS * sizeof(double)));
@@ -862,7 +873,7 @@ int prepare_workspace(vslamb200_ctx * c, Problem & P, const vb::SolverParams & s
     V.tiles = b;
     V.r = (int16_t *)(b + tileBytes);
     V.lim = (float *)(b + tileBytes + listStride * 2);
-    V.tileState = (float *)(b + tileBytes + listStride * 6);
+    V.tileState = (float *)(b + tileBytes + listStride * 10);
   }
   if (sp.sampling == VSLAMB200_SAMPLING_BILINEAR) {
     // bilinear extension: per view 16 B per candidate pixel (r_I, r_Z in fp64) + 28 partial sums per 2048 list entries

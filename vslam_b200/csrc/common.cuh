@@ -285,7 +285,8 @@ void launch_scatter_rcode(const ViewState * views, int view, int16_t * plane, cu
 // gn_level.cu
 size_t gn_level_static_smem();
 cudaError_t launch_gn_level(JobState * jobs, ViewState * views, int job0, int nJobs, int maxViewsPerJob, int clusterSize,
-                            SolverParams p, int level, int maxEvals, double * trace, size_t traceJobStride, double * viewSums, cudaStream_t s);
+                            SolverParams p, int level, int maxEvals, double * trace, size_t traceJobStride, double * viewSums, cudaStream_t s,
+                            bool bounded = false, int checkMode = 0);
 // ext.cu (bilinear / depth-residual extension): one Gauss-Newton (or LM) evaluation + step for every active job
 constexpr int EXT_CHUNK = 2048;  // list entries per block
 void launch_ext_iteration(JobState * jobs, ViewState * views, int job0, int nJobs, int view0, int nViews, int maxPoints,

@@ -34,6 +34,7 @@
 #include "robust.cuh"
 #include "solve.cuh"
 #include "warp_filter.cuh"
+#include "bounds.cuh"
 
 namespace vb
 {
@@ -48,19 +49,9 @@ constexpr int JS = 7;              // doubles per stashed point: 6 scaled Jacobi
 constexpr int EB = 4;              // re-evaluation super-batch: EB points per lane, all loads of a round trip in flight together
 constexpr int QE = 256;            // evaluation queue per warp (circular): < 32 EB left over + one tile of 128 new entries
 constexpr int QC = 160;            // change queue per warp: <= 31 left over + 32 EB new entries
-constexpr float LIMQ = 2048.f;     // limits and accumulated motion bounds are compared as 16-bit fixed point, 1/2048 px
 constexpr double BSCALE = 1048576.0;  // 2^20: extra scale of the b moments (|sum_k J'_ki| <= 2^10 * 2^30.5)
 constexpr int NCHUNK = 8;          // the A-from-moments pass splits the 256 magnitudes into 8 chunks of 32
 constexpr unsigned FLAGGED = 0x80000000u;  // eval-queue entry: the motion bound asked for this point (check mode)
-
-// what one Gauss-Newton step did, for the motion bounds: the increment exp(-dx) applied on the template side
-// (Warp.cpp:153-157: se3 <- se3 * exp(-dx)) and the pose before it
-struct StepConsts
-{
-  float E[9], dt[3];   // rotation of exp(-dx) minus identity, its translation
-  float Ro[9], to[3];  // se3 before the step
-  float ifx, kx, ify, ky, fx, fy;
-};
 
 struct Shared
 {
@@ -132,114 +123,6 @@ __device__ __forceinline__ void term_pair(int t, int & i, int & j)
     i = t - 21;
     j = 6;
   }
-}
-
-// Sampled target pixel (or -1) of one interest point and the DIRECTIONAL margins by which its projection may still
-// move before the sampled pixel or the visibility can change: m[0] towards +u, m[1] towards -u, m[2] towards +v,
-// m[3] towards -v (pixels).  Same decisions as the dense kernel's warp_pick_ring / warp_exact pair (warp_filter.cuh).
-// With u' = iu + fu, fu in [-0.5, 0.5], the rounded pixel changes at fu = +-0.5; on the visibility ring (iu == 1 or
-// iu == W-1: visible iff u' > 1 resp. u' < W-1, InverseCompositional.cpp:115-116) the nearer boundary is fu = 0.
-__device__ __forceinline__ int warp_point(const WarpConsts & c, const ViewState & V, uint32_t pk, float d, float (&m)[4])
-{
-  const WarpEval e = warp_eval(c, pk, d);
-  const int iu = e.iu, iv = e.iv;
-  float pu = 0.5f - e.fu, nu = 0.5f + e.fu, pv = 0.5f - e.fv, nv = 0.5f + e.fv;
-  const bool ringu = iu == 1 || iu == c.Wt - 1, ringv = iv == 1 || iv == c.Ht - 1;
-  if (ringu) {
-    if (e.fu > 0.f) nu = e.fu; else pu = -e.fu;
-  }
-  if (ringv) {
-    if (e.fv > 0.f) nv = e.fv; else pv = -e.fv;
-  }
-  const float dist = fminf(fminf(pu, nu), fminf(pv, nv));
-  const bool ok = e.okb && dist > e.eps;
-  bool vis = (unsigned)(iu - 1) <= (unsigned)(c.Wt - 2) && (unsigned)(iv - 1) <= (unsigned)(c.Ht - 2);
-  vis = vis && !(iu == 1 && e.fu < 0.f) && !(iu == c.Wt - 1 && e.fu > 0.f);
-  vis = vis && !(iv == 1 && e.fv < 0.f) && !(iv == c.Ht - 1 && e.fv > 0.f);
-  const float slack = e.eps + 2e-5f;  // the fp32 evaluation's own error, the rounding of the limit arithmetic
-  m[0] = ok ? pu - slack : 0.f;
-  m[1] = ok ? nu - slack : 0.f;
-  m[2] = ok ? pv - slack : 0.f;
-  m[3] = ok ? nv - slack : 0.f;
-  if (!ok) return warp_exact(V, pk & 0xfff, (pk >> 12) & 0xfff, d);
-  return vis ? iv * c.Wt + iu : -1;
-}
-
-// 16-bit fixed-point forms (1/2048 px): a limit is rounded DOWN, an accumulated bound UP, so the comparison
-// accumulated >= limit never flags later than the real numbers would.  NaN limit -> 0 (always flagged), NaN or
-// infinite bound -> 65535 (flags everything; limits saturate at 65535 too).
-__device__ __forceinline__ uint32_t limit_q(float x)
-{
-  const float y = x * LIMQ;
-  return y > 0.f ? (uint32_t)__float2int_rd(fminf(y, 65535.f)) : 0u;
-}
-__device__ __forceinline__ uint32_t bound_q(float x)
-{
-  const float y = x * LIMQ;
-  return y < 65535.f ? (uint32_t)__float2int_ru(fmaxf(y, 0.f)) : 65535u;
-}
-// the point's limits {+u | -u << 16, +v | -v << 16} given the tile's accumulated bounds at evaluation time
-__device__ __forceinline__ uint2 point_limits(const float4 acc, const float (&m)[4])
-{
-  return make_uint2(limit_q(acc.x + m[0]) | (limit_q(acc.y + m[1]) << 16), limit_q(acc.z + m[2]) | (limit_q(acc.w + m[3]) << 16));
-}
-__device__ __forceinline__ uint2 bounds_q(const float4 acc)
-{
-  return make_uint2(bound_q(acc.x) | (bound_q(acc.y) << 16), bound_q(acc.z) | (bound_q(acc.w) << 16));
-}
-__device__ __forceinline__ bool limit_reached(const uint2 accq, const uint2 lim)
-{
-  return (__vcmpgeu2(accq.x, lim.x) | __vcmpgeu2(accq.y, lim.y)) != 0u;
-}
-
-// Upper bounds (pixels) of the image motion that one Gauss-Newton step causes, per direction (+u, -u, +v, -v), for
-// ANY point whose template pixel lies in [ulo,uhi] x [vlo,vhi] and whose inverse depth lies in [zlo,zhi].
-// With p = d (xn, yn, 1), zi = 1/d:  q_a = T_a p,  q_b = T_a (dT p)  =>  with s = q_a / d = R_a (xn,yn,1) + t_a zi,
-// m = ((dR - I)(xn,yn,1) + dt zi),  g = R_a m = (q_b - q_a) / d, the projected x' = q_x / q_z moves by EXACTLY
-//     dx' = (g_x - x'_a g_z) / (s_z + g_z),      x'_a = s_x / s_z,
-// s, m, g are affine in (xn, yn, zi), so centre +- radius intervals bound them without slack; the products are
-// bounded term by term; the denominator is positive.  The numerator's interval [c - r, c + r] gives the two signed
-// bounds.  Each is inflated by 1 % + 1e-5 px, which covers the fp32 evaluation of the bound.
-__device__ __forceinline__ float4 tile_motion_bound(const StepConsts & k, float ulo, float uhi, float vlo, float vhi, float zlo, float zhi)
-{
-  const float xlo = fmaf(k.ifx, ulo, k.kx), xhi = fmaf(k.ifx, uhi, k.kx);
-  const float ylo = fmaf(k.ify, vlo, k.ky), yhi = fmaf(k.ify, vhi, k.ky);
-  const float xc = 0.5f * (xlo + xhi), xr = 0.5f * fabsf(xhi - xlo) + 1e-6f;
-  const float yc = 0.5f * (ylo + yhi), yr = 0.5f * fabsf(yhi - ylo) + 1e-6f;
-  const float zc = 0.5f * (zlo + zhi), zr = 0.5f * (zhi - zlo) + 1e-5f * zhi;
-  float mc[3], mr[3], gc[3], gr[3], sc[3], sr[3];
-#pragma unroll
-  for (int i = 0; i < 3; i++) {
-    mc[i] = fmaf(k.E[3 * i], xc, fmaf(k.E[3 * i + 1], yc, fmaf(k.dt[i], zc, k.E[3 * i + 2])));
-    mr[i] = fabsf(k.E[3 * i]) * xr + fabsf(k.E[3 * i + 1]) * yr + fabsf(k.dt[i]) * zr;
-    sc[i] = fmaf(k.Ro[3 * i], xc, fmaf(k.Ro[3 * i + 1], yc, fmaf(k.to[i], zc, k.Ro[3 * i + 2])));
-    sr[i] = fabsf(k.Ro[3 * i]) * xr + fabsf(k.Ro[3 * i + 1]) * yr + fabsf(k.to[i]) * zr;
-  }
-#pragma unroll
-  for (int i = 0; i < 3; i++) {
-    gc[i] = k.Ro[3 * i] * mc[0] + k.Ro[3 * i + 1] * mc[1] + k.Ro[3 * i + 2] * mc[2];
-    gr[i] = fabsf(k.Ro[3 * i]) * mr[0] + fabsf(k.Ro[3 * i + 1]) * mr[1] + fabsf(k.Ro[3 * i + 2]) * mr[2];
-  }
-  const float INF = __int_as_float(0x7f800000);
-  const float4 ALL = make_float4(INF, INF, INF, INF);
-  const float szmin = sc[2] - sr[2];
-  if (!(szmin > 0.25f)) return ALL;
-  const float gz = fabsf(gc[2]) + gr[2];
-  const float den = szmin - gz;
-  if (!(den > 0.125f)) return ALL;
-  const float isz = 1.f / sc[2], iszmin = 1.f / szmin;
-  const float xpc = sc[0] * isz, xpr = (sr[0] + fabsf(xpc) * sr[2]) * iszmin;
-  const float ypc = sc[1] * isz, ypr = (sr[1] + fabsf(ypc) * sr[2]) * iszmin;
-  const float cu = fmaf(-xpc, gc[2], gc[0]), ru = gr[0] + fabsf(xpc) * gr[2] + xpr * gz;
-  const float cv = fmaf(-ypc, gc[2], gc[1]), rv = gr[1] + fabsf(ypc) * gr[2] + ypr * gz;
-  const float su = k.fx / den, sv = k.fy / den;
-  // NaN propagates (fmaxf would drop it: keep the sums explicit) and flags everything through bound_q
-  float4 b;
-  b.x = fmaf(su * (ru + cu > 0.f ? ru + cu : (ru + cu == ru + cu ? 0.f : ru + cu)), 1.01f, 1e-5f);
-  b.y = fmaf(su * (ru - cu > 0.f ? ru - cu : (ru - cu == ru - cu ? 0.f : ru - cu)), 1.01f, 1e-5f);
-  b.z = fmaf(sv * (rv + cv > 0.f ? rv + cv : (rv + cv == rv + cv ? 0.f : rv + cv)), 1.01f, 1e-5f);
-  b.w = fmaf(sv * (rv - cv > 0.f ? rv - cv : (rv - cv == rv - cv ? 0.f : rv - cv)), 1.01f, 1e-5f);
-  return b;
 }
 
 __device__ __forceinline__ void moment_add(uint32_t * Mlo, uint32_t * Mhi, int code, int lane, long long v, bool subtract)
