@@ -318,6 +318,7 @@ int preprocess(vslamb200_ctx * c, const std::vector<int> & slots, int nLevels, b
   const int * dSlots = c->dSlots[ring].as<int>();
   const vb::FrameDev & f = c->frames[slots[0]].dev;
   const vb::FrameDev * table = c->dFrames.as<vb::FrameDev>();
+  if (c->timing) CK(cudaEventRecord(c->ev[0], stream));
   for (int l = 1; l < nLevels; l++) {
     vb::launch_pyramid_level(table, dSlots, n, l, f.W[l], f.H[l], f.Wd[l], f.Hd[l], f.W[l - 1], f.H[l - 1], f.Wd[l - 1],
                              f.Hd[l - 1], stream);
@@ -329,6 +330,13 @@ int preprocess(vslamb200_ctx * c, const std::vector<int> & slots, int nLevels, b
   }
   CK(cudaGetLastError());
   CK(cudaEventRecord(c->slotsEv[ring], stream));
+  if (c->timing) {
+    CK(cudaEventRecord(c->ev[1], stream));
+    CK(cudaStreamSynchronize(stream));
+    float ms = 0;
+    CK(cudaEventElapsedTime(&ms, c->ev[0], c->ev[1]));
+    c->stats.ms_preprocess += ms;
+  }
   if (sync) CK(cudaStreamSynchronize(stream));
   c->stats.frames_uploaded += n;
   return 0;

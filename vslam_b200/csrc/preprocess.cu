@@ -216,11 +216,72 @@ __global__ void __launch_bounds__(256) depth_down_kernel(
   f.Zsf[level][(size_t)i * Wd + j] = (z0 > 0.f) ? out : 0.f;
 }
 
+// cv::pyrDown for source widths that are a multiple of 8, register-resident: a lane owns four consecutive output
+// columns and marches down a band of output rows.  Per source row it loads the 11 bytes 2x-2 .. 2x+8 (four aligned
+// words), forms the horizontal [1 4 6 4 1] sums at the four even centres, and keeps the sums of five source rows; every
+// output row consumes two new source rows.  Same integers as the tiled kernel: (sum + 128) >> 8, reflect-101.
+constexpr int PB_ROWS = 16;  // output rows per warp
+
+__device__ __forceinline__ void pyr_hrow(const uint8_t * __restrict__ in, int Wp, int Hp, int sy, int sx, int (&h)[4])
+{
+  const uint8_t * row = in + (size_t)reflect101(sy, Hp) * Wp;
+  const uint32_t w1 = *reinterpret_cast<const uint32_t *>(row + sx), w2 = *reinterpret_cast<const uint32_t *>(row + sx + 4);
+  int p[11];
+  p[2] = w1 & 0xff; p[3] = (w1 >> 8) & 0xff; p[4] = (w1 >> 16) & 0xff; p[5] = w1 >> 24;
+  p[6] = w2 & 0xff; p[7] = (w2 >> 8) & 0xff; p[8] = (w2 >> 16) & 0xff; p[9] = w2 >> 24;
+  if (sx >= 4) {
+    const uint32_t w0 = *reinterpret_cast<const uint32_t *>(row + sx - 4);
+    p[0] = (w0 >> 16) & 0xff; p[1] = w0 >> 24;
+  } else {  // left border (sx == 0): columns -2, -1 reflect to 2, 1
+    p[0] = p[4]; p[1] = p[3];
+  }
+  if (sx + 8 < Wp) p[10] = row[sx + 8];
+  else p[10] = p[8];  // right border (sx + 8 == Wp): column Wp reflects to Wp - 2
+#pragma unroll
+  for (int j = 0; j < 4; j++) h[j] = p[2 * j] + 4 * p[2 * j + 1] + 6 * p[2 * j + 2] + 4 * p[2 * j + 3] + p[2 * j + 4];
+}
+
+__global__ void __launch_bounds__(256) pyr_down_v4_kernel(
+  const FrameDev * __restrict__ frames, const int * __restrict__ slots, int level, int Wp, int Hp, int W, int H)
+{
+  const FrameDev & f = frames[slots[blockIdx.z]];
+  const uint8_t * __restrict__ in = f.I[level - 1];
+  uint8_t * __restrict__ out = f.I[level];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int x = (blockIdx.x * 32 + lane) * 4;
+  const int y0 = (blockIdx.y * 8 + warp) * PB_ROWS;
+  if (x >= W || y0 >= H) return;
+  const int y1 = min(y0 + PB_ROWS, H);
+  int h0[4], h1[4], h2[4], h3[4], h4[4];  // source rows 2y-2 .. 2y+2
+  pyr_hrow(in, Wp, Hp, 2 * y0 - 2, 2 * x, h0);
+  pyr_hrow(in, Wp, Hp, 2 * y0 - 1, 2 * x, h1);
+  pyr_hrow(in, Wp, Hp, 2 * y0, 2 * x, h2);
+  for (int y = y0; y < y1; y++) {
+    pyr_hrow(in, Wp, Hp, 2 * y + 1, 2 * x, h3);
+    pyr_hrow(in, Wp, Hp, 2 * y + 2, 2 * x, h4);
+    uint32_t o = 0;
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+      const int sacc = h0[j] + 4 * h1[j] + 6 * h2[j] + 4 * h3[j] + h4[j];
+      o |= (uint32_t)((sacc + 128) >> 8) << (8 * j);
+      h0[j] = h2[j];
+      h1[j] = h3[j];
+      h2[j] = h4[j];
+    }
+    *reinterpret_cast<uint32_t *>(out + (size_t)y * W + x) = o;
+  }
+}
+
 void launch_pyramid_level(const FrameDev * frames, const int * slots, int n, int level, int W, int H, int Wd, int Hd,
                           int Wp, int Hp, int Wdp, int Hdp, cudaStream_t s)
 {
-  dim3 g1((W + PT - 1) / PT, (H + PT - 1) / PT, n);
-  pyr_down_u8_kernel<<<g1, 256, 0, s>>>(frames, slots, level, Wp, Hp, W, H);
+  if (Wp % 8 == 0 && Wp >= 16 && Hp >= 3) {
+    dim3 g1((W / 4 + 31) / 32, (H + 8 * PB_ROWS - 1) / (8 * PB_ROWS), n);
+    pyr_down_v4_kernel<<<g1, 256, 0, s>>>(frames, slots, level, Wp, Hp, W, H);
+  } else {
+    dim3 g1((W + PT - 1) / PT, (H + PT - 1) / PT, n);
+    pyr_down_u8_kernel<<<g1, 256, 0, s>>>(frames, slots, level, Wp, Hp, W, H);
+  }
   if (Wd > 0 && Hd > 0) {
     dim3 g2((Wd + 31) / 32, (Hd + 7) / 8, n);
     depth_down_kernel<<<g2, 256, 0, s>>>(frames, slots, level, Wdp, Hdp, Wd, Hd);
@@ -266,8 +327,91 @@ __global__ void __launch_bounds__(256) blur_sobel_kernel(
   }
 }
 
+// The same operation for image widths that are a multiple of 4 (every level of the usual sizes), register-resident:
+// a lane owns four consecutive columns and marches down a band of rows.  Per source row it loads the 8 bytes
+// x-2 .. x+5 (three aligned words), forms the horizontal [1 2 1] sums of 6 columns, completes the blurred row of the
+// row above from three such rows (the 3x3 binomial is separable and the rounding (s+8)>>4 is applied once), and from
+// three blurred rows the Sobel pair of the row above that.  Reflect-101 of the raw image with a halo of 2 equals
+// reflect-101 of the blurred image with a halo of 1 (the kernel is symmetric), so one border rule serves both steps.
+// One 32-bit load per source byte quadruple instead of nine byte loads per pixel; 8-byte stores of gx and gy.
+constexpr int GB_ROWS = 32;  // output rows per warp
+
+__device__ __forceinline__ void load_row8(const uint8_t * __restrict__ in, int W, int H, int y, int x, int (&p)[8])
+{
+  const uint8_t * row = in + (size_t)reflect101(y, H) * W;
+  const uint32_t w1 = *reinterpret_cast<const uint32_t *>(row + x);
+  p[2] = w1 & 0xff; p[3] = (w1 >> 8) & 0xff; p[4] = (w1 >> 16) & 0xff; p[5] = w1 >> 24;
+  if (x >= 4) {
+    const uint32_t w0 = *reinterpret_cast<const uint32_t *>(row + x - 4);
+    p[0] = (w0 >> 16) & 0xff; p[1] = w0 >> 24;
+  } else {  // left border (x == 0): columns -2, -1 reflect to 2, 1
+    p[0] = p[4]; p[1] = p[3];
+  }
+  if (x + 8 <= W) {
+    const uint32_t w2 = *reinterpret_cast<const uint32_t *>(row + x + 4);
+    p[6] = w2 & 0xff; p[7] = (w2 >> 8) & 0xff;
+  } else {  // right border (x == W-4): columns W, W+1 reflect to W-2, W-3
+    p[6] = p[4]; p[7] = p[3];
+  }
+}
+
+__global__ void __launch_bounds__(256) blur_sobel_v4_kernel(
+  const FrameDev * __restrict__ frames, const int * __restrict__ slots, int level, int W, int H)
+{
+  const FrameDev & f = frames[slots[blockIdx.z]];
+  const uint8_t * __restrict__ in = f.I[level];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int x = (blockIdx.x * 32 + lane) * 4;
+  const int y0 = (blockIdx.y * 8 + warp) * GB_ROWS;
+  if (x >= W || y0 >= H) return;
+  const int y1 = min(y0 + GB_ROWS, H);
+  int hA[6], hB[6], hC[6];  // horizontal sums of source rows s-2, s-1, s
+  int bA[6], bB[6];         // blurred rows s-3, s-2 (bC, row s-1, is formed from hA, hB, hC)
+#pragma unroll
+  for (int k = 0; k < 6; k++) hA[k] = hB[k] = hC[k] = bA[k] = bB[k] = 0;
+  // source rows y0-2 .. y1+1; after source row s: blurred row s-1, output row s-2
+  for (int sr = y0 - 2; sr <= y1 + 1; sr++) {
+    int p[8];
+    load_row8(in, W, H, sr, x, p);
+#pragma unroll
+    for (int k = 0; k < 6; k++) {
+      hA[k] = hB[k];
+      hB[k] = hC[k];
+      hC[k] = p[k] + 2 * p[k + 1] + p[k + 2];
+    }
+    if (sr < y0) continue;  // fewer than three source rows yet
+    int bC[6];
+#pragma unroll
+    for (int k = 0; k < 6; k++) bC[k] = (hA[k] + 2 * hB[k] + hC[k] + 8) >> 4;
+    const int oy = sr - 2;
+    if (oy >= y0) {  // blurred rows oy-1, oy, oy+1 = bA, bB, bC
+      int gx[4], gy[4];
+#pragma unroll
+      for (int k = 0; k < 4; k++) {
+        gx[k] = (bA[k + 2] - bA[k]) + 2 * (bB[k + 2] - bB[k]) + (bC[k + 2] - bC[k]);
+        gy[k] = (bC[k] + 2 * bC[k + 1] + bC[k + 2]) - (bA[k] + 2 * bA[k + 1] + bA[k + 2]);
+      }
+      const size_t o = (size_t)oy * W + x;
+      *reinterpret_cast<uint2 *>(f.gx[level] + o) =
+        make_uint2(((uint32_t)gx[0] & 0xffffu) | ((uint32_t)gx[1] << 16), ((uint32_t)gx[2] & 0xffffu) | ((uint32_t)gx[3] << 16));
+      *reinterpret_cast<uint2 *>(f.gy[level] + o) =
+        make_uint2(((uint32_t)gy[0] & 0xffffu) | ((uint32_t)gy[1] << 16), ((uint32_t)gy[2] & 0xffffu) | ((uint32_t)gy[3] << 16));
+    }
+#pragma unroll
+    for (int k = 0; k < 6; k++) {
+      bA[k] = bB[k];
+      bB[k] = bC[k];
+    }
+  }
+}
+
 void launch_gradients(const FrameDev * frames, const int * slots, int n, int level, int W, int H, cudaStream_t s)
 {
+  if (W % 4 == 0 && W >= 8 && H >= 4) {
+    dim3 g((W / 4 + 31) / 32, (H + 8 * GB_ROWS - 1) / (8 * GB_ROWS), n);
+    blur_sobel_v4_kernel<<<g, 256, 0, s>>>(frames, slots, level, W, H);
+    return;
+  }
   dim3 g((W + GT_X - 1) / GT_X, (H + GT_Y - 1) / GT_Y, n);
   blur_sobel_kernel<<<g, 256, 0, s>>>(frames, slots, level, W, H);
 }
