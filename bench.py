@@ -278,8 +278,11 @@ def main():
             t0 = time.perf_counter()
             ctx.align_raw(jobs, 1, one)
             ts.append((time.perf_counter() - t0) * 1e3)
-        assert list(one[0].pose) == list(resident_poses[0]), "single-pair call differs from the batched result"
-        lat = {"p50_ms": float(np.percentile(ts, 50)), "p95_ms": float(np.percentile(ts, 95)), "calls": len(ts),
+        # a single job runs on larger clusters than a throughput batch (latency mode), so its sums are added in another
+        # order: the same pose up to rounding, not bit for bit
+        lat_diff = float(np.max(np.abs(np.array(list(one[0].pose)) - np.array(list(resident_poses[0])))))
+        assert lat_diff < 1e-9, "single-pair call differs from the batched result"
+        lat = {"p50_ms": float(np.percentile(ts, 50)), "p95_ms": float(np.percentile(ts, 95)), "calls": len(ts), "max_pose_diff_vs_batched": lat_diff,
                "what": "one 640x480 pair, 4 levels, frames resident, host submit -> pose on host"}
 
     # per-kernel timing pass (events around every residual / accumulate launch; separate from the timed runs)

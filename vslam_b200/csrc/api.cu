@@ -763,17 +763,19 @@ int build_problem(vslamb200_ctx * c, const vslamb200_job * jobs, int nJobs, Prob
 
 // cluster size of a level's Gauss-Newton kernel: enough CTAs per job that a slice of the interest list is a few
 // ten thousand points (its residuals then stay in shared memory), never more than the portable maximum of 8
-int pick_cluster(int npx, int maxViewsPerJob)
+int pick_cluster(int npx, int nJobs)
 {
-  (void)maxViewsPerJob;
   if (const char * e = std::getenv("VSLAMB200_CLUSTER")) {  // tuning override
     const int c = std::atoi(e);
-    if (c == 1 || c == 2 || c == 4 || c == 8) return c;
+    if (c == 1 || c == 2 || c == 4 || c == 8 || c == 16) return c;
   }
-  if (npx > 160000) return 8;
-  if (npx > 40000) return 4;
-  if (npx > 12000) return 2;
-  return 1;
+  int c = npx > 160000 ? 8 : npx > 40000 ? 4 : npx > 12000 ? 2 : 1;
+  // Latency mode: a handful of jobs cannot fill the device, so each job spreads over as many SMs as a cluster can
+  // span (16 CTAs is the non-portable cluster maximum of sm_100; the launcher opts in).  Measured on one 640x480
+  // pair, 4 levels: 3.43 ms with the throughput sizes 8/4/2/1, 2.88 ms with 8 everywhere, 2.13 ms with 16 everywhere.
+  // Throughput batches keep the smaller clusters: there the per-CTA work amortises the serial sections better.
+  if (nJobs <= 8) c = npx > 12000 ? 16 : npx > 3000 ? 8 : 4;
+  return c;
 }
 
 // Which Gauss-Newton level kernel runs a level.  The incremental kernel (gn_inc.cu) keeps per-residual moments in shared
@@ -803,7 +805,7 @@ int run_level(vslamb200_ctx * c, Problem & P, int level, const vb::SolverParams 
   const vb::FrameDev * table = c->dFrames.as<vb::FrameDev>();
   double * dTrace = c->traceEnabled ? c->trace.as<double>() : nullptr;
   const size_t traceJobStride = (size_t)P.nLevels * sp.maxIterations * vb::TRACE_STRIDE;
-  const int cluster = pick_cluster(npx, 1);
+  const int cluster = pick_cluster(npx, nJobs);
 
   if (c->timing) CK(cudaEventRecord(c->ev[0], stream));
   vb::launch_level_setup(table, dJobs, dViews, view0, nViews, level, stream);

@@ -931,6 +931,10 @@ static cudaError_t launch_gn_level_t(
   const size_t dyn = level_dyn_smem(maxViewsPerJob);
   cudaError_t e = cudaFuncSetAttribute(gn_level_kernel<BOUNDED>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
   if (e != cudaSuccess) return e;
+  if (clusterSize > 8) {
+    e = cudaFuncSetAttribute(gn_level_kernel<BOUNDED>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+    if (e != cudaSuccess) return e;
+  }
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3((unsigned)nJobs * clusterSize, 1, 1);
   cfg.blockDim = dim3(GT, 1, 1);
