@@ -36,6 +36,6 @@ for l in range(args.levels):
     ev = st["pixel_iterations_level"][l] / (W * H / 4 ** l)
     print(" level", l, "evals/job", round(ev / len(jobs), 2), "kclocks/job", [round(c / len(jobs) / 1e3, 1) for c in pc[:7]],
           "share", [round(c / tot, 3) for c in pc[:7]])
-    if (st["incremental_launches"] or st["bounded_launches"]) and st["point_iterations"]:
+    if st["point_iterations"]:
         print("   slots 7-9 (incremental: flagged, changed, missed points; dense: scale sub-laps)", pc[7:10])
 ctx.close()
