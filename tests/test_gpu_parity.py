@@ -74,6 +74,27 @@ def test_pyramid_and_gradients_exact(ctx, oracle, synth, W, H, levels, holes):
         assert np.array_equal(got["Z"].astype(np.float64), ref["Z"]), f"depth level {l}"
 
 
+@pytest.mark.parametrize("W,H,levels", [(8, 4, 1), (16, 8, 2), (40, 24, 2), (48, 40, 3), (36, 20, 2), (132, 36, 2),
+                                        (1280, 720, 4)])
+def test_pyramid_and_gradients_exact_on_random_images(ctx, oracle, W, H, levels):
+    """The register-resident pyrDown / blur+Sobel kernels (widths that are multiples of 8 / 4) and the tiled ones (other
+    widths) against the oracle on random and saturated images: smallest sizes, widths that switch kernels between
+    levels, borders on every side."""
+    rng = np.random.default_rng(W * 1000 + H)
+    gray = rng.integers(0, 256, (2, H, W), dtype=np.uint8)
+    gray[1] = np.where(rng.random((H, W)) < 0.5, 0, 255).astype(np.uint8)     # saturated checker noise
+    depth = (rng.uniform(0.5, 4.0, (2, H, W)) * (rng.random((2, H, W)) > 0.2)).astype(np.float32)
+    cam = (100.0, 100.0, W / 2 - 0.5, H / 2 - 0.5)
+    ctx.upload(np.array([1, 2]), gray, depth, cam, levels)
+    for k in range(2):
+        f = oracle.Frame(gray[k], depth[k].astype(np.float64), *cam, levels)
+        for l in range(levels):
+            ref, got = f.level(l), ctx.download(k + 1, l)
+            assert np.array_equal(got["I"], ref["I"]), (k, l)
+            assert np.array_equal(got["dIx"], ref["dIx"]) and np.array_equal(got["dIy"], ref["dIy"]), (k, l)
+            assert np.array_equal(got["Z"].astype(np.float64), ref["Z"]), (k, l)
+
+
 def test_single_frame_uploads(ctx, oracle, synth):
     """One frame per call (what the odometry loop does), f32 row-major: the direct copy path with a one-row pitch."""
     p = _pair(synth, 320, 240, 3)
