@@ -676,21 +676,14 @@ __global__ void __launch_bounds__(GT, CTAS_PER_SM) gn_level_kernel(
           }
           if (P.g < p1) r4[P.g >> 2] = make_uint2(rr[0] | (rr[1] << 16), rr[2] | (rr[3] << 16));
         };
-        Pend Pa, Pb;
-        int ch = 0;
-        if (nCh > 0) start_chunk(0, Pa);
-        for (ch = 1; ch + 1 < nCh; ch += 2) {
-          start_chunk(ch, Pb);
-          finish_chunk(Pa);
-          start_chunk(ch + 1, Pa);
-          finish_chunk(Pb);
-        }
-        if (ch < nCh) {
-          start_chunk(ch, Pb);
-          finish_chunk(Pa);
-          finish_chunk(Pb);
-        } else if (nCh > 0) {
-          finish_chunk(Pa);
+        // one instance of each half of the pipeline (instruction-cache footprint): the chunk started in this turn
+        // is finished in the next one
+        Pend P, Pn;
+#pragma unroll 1
+        for (int ch = 0; ch <= nCh; ch++) {
+          if (ch < nCh) start_chunk(ch, Pn);
+          if (ch > 0) finish_chunk(P);
+          P = Pn;
         }
         item += nCh;
       }
