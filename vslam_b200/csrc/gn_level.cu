@@ -146,7 +146,7 @@ __device__ void compute_scale(
   offsetOut = s_offset;
 }
 
-// Weight table {w(r), w(r) r} per residual code (Loss.cpp:51-92); code 511 (not visible) -> {0, 0}.
+// Weight table {sqrt(w(r)), sqrt(w(r)) r} per residual code (Loss.cpp:51-92); code 511 (not visible) -> {0, 0}.
 // Returns this thread's share of chi2 = sum_k w_k r_k^2 (NormalEquations.cpp:58) given its visible counts.
 __device__ __forceinline__ double build_weights(
   const SolverParams & p, double scale, double offset, double2 * lut, const double (&nvis)[BPT])
@@ -158,7 +158,10 @@ __device__ __forceinline__ double build_weights(
     const double r = (double)(b - 255);
     const double w = p.lossKind == VSLAMB200_LOSS_NONE ? 1.0 : loss_weight(p, (r - offset) / scale);
     const double wr = w * r;
-    lut[b] = b == HIST_BINS - 1 ? make_double2(0.0, 0.0) : make_double2(w, wr);
+    // the table holds {sqrt(w), sqrt(w) r}: phase C scales the template gradient by sqrt(w) once and forms
+    // (sqrt(w) J)(sqrt(w) J)^T, which saves the six w * J_i products per point
+    const double sw = sqrt(w);
+    lut[b] = b == HIST_BINS - 1 ? make_double2(0.0, 0.0) : make_double2(sw, sw * r);
     c2 = fma(nvis[j], wr * r, c2);
   }
   return c2;
@@ -236,7 +239,7 @@ struct LevelShared
 {
   JobState J;
   int hist[2][HIST_BINS];
-  double2 lut[HIST_BINS];  // {w(r), w(r) r} per residual code; code 511 (not visible) -> {0, 0}
+  double2 lut[HIST_BINS];  // {sqrt(w(r)), sqrt(w(r)) r} per residual code; code 511 (not visible) -> {0, 0}
   double red[GT / 32 * NE_TERMS];
   SolveScratch X;
   double so[2];  // {scale, offset} of the current view, written by the cluster's leading CTA
@@ -778,10 +781,11 @@ __global__ void __launch_bounds__(GT, CTAS_PER_SM) gn_level_kernel(
             const uint32_t gb = gg[q] ^ 0x80008000u;
             const double u = __hiloint2double(0x43300000, (int)(pk[q] & 0xfff)) - 4503599627370496.0;
             const double v = __hiloint2double(0x43300000, (int)((pk[q] >> 12) & 0xfff)) - 4503599627370496.0;
-            const double a = (__hiloint2double(0x43300000, (int)(gb & 0xffff)) - 4503599627403264.0) * fxJ;  // dIx * fx
-            const double b = (__hiloint2double(0x43300000, (int)(gb >> 16)) - 4503599627403264.0) * fyJ;     // dIy * fy
-            const double2 wwr = lut[rq[q]];                                                                  // {w, w r}
-            const double w = wwr.x, wr = wwr.y;
+            const double2 swr = lut[rq[q]];  // {sqrt(w), sqrt(w) r}
+            const double sw = swr.x, swr_ = swr.y;
+            // sqrt(w) dIx fx, sqrt(w) dIy fy: every Jacobian component below carries the factor sqrt(w)
+            const double a = (__hiloint2double(0x43300000, (int)(gb & 0xffff)) - 4503599627403264.0) * fxJ * sw;
+            const double b = (__hiloint2double(0x43300000, (int)(gb >> 16)) - 4503599627403264.0) * fyJ * sw;
             const double zi = zz[q];
             const double xn = fma(ifx, u, kx), yn = fma(ify, v, ky);
             const double cc = fma(a, xn, b * yn);
@@ -795,13 +799,12 @@ __global__ void __launch_bounds__(GT, CTAS_PER_SM) gn_level_kernel(
             int s = 0;
 #pragma unroll
             for (int i = 0; i < 6; i++) {
-              const double wj = w * J[i];
 #pragma unroll
               for (int j = i; j < 6; j++) {
-                acc[s] = fma(wj, J[j], acc[s]);
+                acc[s] = fma(J[i], J[j], acc[s]);
                 s++;
               }
-              acc[21 + i] = fma(J[i], wr, acc[21 + i]);
+              acc[21 + i] = fma(J[i], swr_, acc[21 + i]);
             }
           }
         }
