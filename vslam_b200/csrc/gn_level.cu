@@ -532,7 +532,11 @@ __global__ void __launch_bounds__(GT, CTAS_PER_SM) gn_level_kernel(
   cg::cluster_group cluster = cg::this_cluster();
   const unsigned C = cluster.num_blocks(), rank = cluster.block_rank();
   const int job = job0 + blockIdx.x / C;
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  // read once through a volatile asm: the compiler otherwise re-reads the special register in every chunk (S2R has a
+  // long latency and sits in the hot loops)
+  unsigned tidv;
+  asm volatile("mov.u32 %0, %%tid.x;" : "=r"(tidv));
+  const int tid = (int)tidv, lane = tid & 31, warp = tid >> 5;
   __shared__ LevelShared S;
   extern __shared__ __align__(128) unsigned char ring[];
 
