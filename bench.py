@@ -170,6 +170,9 @@ def main():
     ap.add_argument("--impl", default="ours")
     ap.add_argument("--cpu-pairs", type=int, default=32, help="pairs timed on the host cores for cpu_baseline")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--distinct-sequences", action="store_true",
+                    help="every rank renders its own sequence (seed 1234 + rank) instead of the same one; the sequences "
+                         "differ in Gauss-Newton iteration count by up to 30 %, so the per-GPU work is then not fixed")
     args = ap.parse_args()
     rank, world, local = dist_env()
     if args.impl == "reference":
@@ -189,7 +192,10 @@ def main():
 
     F = args.frames
     cam = synth.cam_for(W, H)
-    gray, depth, gt = synth.make_sequence(F, W, H, seed=1234 + rank, cam=cam)
+    # weak scaling = fixed work per GPU: every rank aligns the same sequence (the result gather still moves every rank's
+    # poses).  Sequences rendered from different seeds need different numbers of Gauss-Newton iterations (measured: rank
+    # 3's takes 27 % longer than rank 0's on identical GPUs), which would time the data instead of the scaling.
+    gray, depth, gt = synth.make_sequence(F, W, H, seed=1234 + (rank if args.distinct_sequences else 0), cam=cam)
     h_gray = torch.from_numpy(gray).pin_memory()
     h_depth = torch.from_numpy(depth).pin_memory()
     d_gray = h_gray.cuda()
@@ -241,6 +247,7 @@ def main():
             e1.record(stream)
         torch.cuda.synchronize()
         ms = torch.tensor([e0.elapsed_time(e1)], device="cuda")
+        timed.own_ms = float(ms.item())
         if use_dist:
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
             dist.barrier()
@@ -252,6 +259,7 @@ def main():
     sampler.start()
     ctx.reset_stats()
     ms = timed(step_resident, args.steps)
+    own_ms = timed.own_ms
     st = ctx.stats()
     clocks = sampler.stop()
     pairs = (F - 1) * args.steps * world
@@ -311,7 +319,14 @@ def main():
     }
     iters_per_pair = np.mean([sum(r.iters[:LEVELS]) for r in results])
 
+    ranks = None
     if use_dist:
+        # per-rank step time, clocks and throttle reasons (the reported time is the maximum over the ranks)
+        ranks = [None] * world
+        dist.all_gather_object(ranks, {"rank": rank, "ms_per_step": own_ms / args.steps, "sm_mhz": clocks.get("sm_mhz"),
+                                       "reasons": clocks.get("reasons"),
+                                       "ms_gn_level": [round(x, 3) for x in tst["ms_gn_level"][:LEVELS]],
+                                       "ms_lists": round(tst["ms_lists"], 3), "ms_preprocess": round(tst["ms_preprocess"], 3)})
         # the only collective of the path: gather the poses (7 f64 per pair) of every rank
         mine = torch.tensor([list(r.pose) for r in results], device="cuda", dtype=torch.float64)
         allp = [torch.empty_like(mine) for _ in range(world)]
@@ -343,13 +358,15 @@ def main():
             "config": {"workload": f"synthetic TUM-shape 640x480 sequence of {F} frames per GPU, frame-to-frame "
                                    f"alignment ({F - 1} pairs per batch), t-distribution weights, {LEVELS} levels, "
                                    "GaussNewton(1e-7,100), minGradient 30",
+                       "sequences": ("one per rank, seeds 1234 + rank" if args.distinct_sequences else
+                                     "the same sequence (seed 1234) on every rank: fixed work per GPU"),
                        "l2_policy": "inputs (1.5 GB of frames per step) are larger than the 126 MB L2",
                        "mean_gn_iterations_per_pair": float(iters_per_pair)},
             "e2e": {"value": e2e, "unit": "pairs/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": ms_e2e / args.steps, "max_pose_diff_vs_resident": e2e_diff,
                     "pipeline": "upload of step s+1 (copy stream) overlaps the alignment of step s; all uploads timed"},
             "gpu_launches": int(st["kernel_launches"]),
-            "latency": lat, "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
+            "latency": lat, "clocks": clocks, "ranks": ranks, "roofline": roofline, "cpu_baseline": cpu,
         }))
     ctx.close()
     if use_dist:
