@@ -936,17 +936,34 @@ static cudaError_t launch_gn_level_t(
     if (e != cudaSuccess) return e;
   }
   cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3((unsigned)nJobs * clusterSize, 1, 1);
   cfg.blockDim = dim3(GT, 1, 1);
   cfg.dynamicSmemBytes = dyn;
   cfg.stream = s;
   cudaLaunchAttribute at[1];
   at[0].id = cudaLaunchAttributeClusterDimension;
-  at[0].val.clusterDim.x = clusterSize;
   at[0].val.clusterDim.y = 1;
   at[0].val.clusterDim.z = 1;
   cfg.attrs = at;
   cfg.numAttrs = 1;
+  if (clusterSize > 8) {
+    // 16-CTA clusters need a GPC with 16 SMs that can each take a CTA of this size: asked once per shared-memory size;
+    // a device (or partition) that cannot co-schedule them falls back to the portable maximum
+    static int ok16[2] = {-1, -1};
+    static size_t dyn16[2] = {0, 0};
+    const int v = BOUNDED ? 1 : 0;
+    if (ok16[v] < 0 || dyn16[v] != dyn) {
+      cfg.gridDim = dim3(16, 1, 1);
+      at[0].val.clusterDim.x = 16;
+      int n = 0;
+      const cudaError_t q = cudaOccupancyMaxActiveClusters(&n, gn_level_kernel<BOUNDED>, &cfg);
+      if (q != cudaSuccess) cudaGetLastError();
+      ok16[v] = (q == cudaSuccess && n >= 1) ? 1 : 0;
+      dyn16[v] = dyn;
+    }
+    if (!ok16[v]) clusterSize = 8;
+  }
+  cfg.gridDim = dim3((unsigned)nJobs * clusterSize, 1, 1);
+  at[0].val.clusterDim.x = clusterSize;
   return cudaLaunchKernelEx(&cfg, gn_level_kernel<BOUNDED>, jobs, views, p, level, maxEvals, trace, traceJobStride, viewSums,
                             job0, checkMode);
 }
