@@ -2,6 +2,8 @@
 Tolerances are BASELINE.json's: masks / indices bit-exact, pyramid and gradient images <= 1e-5 relative
 (integer planes are required to be exact), per-iteration normal equations <= 1e-4 relative Frobenius,
 final pose <= 1e-4 m and 1e-4 rad."""
+import os
+
 import numpy as np
 import pytest
 
@@ -93,6 +95,37 @@ def test_pyramid_and_gradients_exact_on_random_images(ctx, oracle, W, H, levels)
             assert np.array_equal(got["I"], ref["I"]), (k, l)
             assert np.array_equal(got["dIx"], ref["dIx"]) and np.array_equal(got["dIy"], ref["dIy"]), (k, l)
             assert np.array_equal(got["Z"].astype(np.float64), ref["Z"]), (k, l)
+
+
+def test_real_tum_frame_pair_matches_oracle(ctx, capi, oracle, level_kernel):
+    """The one real RGB-D frame the reference ships (odometry/test/resource; crops in tests/golden/tum_frame.npz, made by
+    tests/golden/make_tum_frame.py): real texture and 40 % invalid depth.  Every pyramid level bit-exact, then the
+    alignment of the two crops: same iteration counts, stop reasons and pose as the oracle, with every level kernel."""
+    O, A = oracle, capi
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "tum_frame.npz"))
+    cam, L = (525.0 / 2, 525.0 / 2, 159.5, 119.5), 3
+    gray = np.stack([g["gray0"], g["gray1"]])
+    depth = np.stack([g["depth0"], g["depth1"]]).astype(np.float64) / 5000.0  # test_alignment_se3.cpp:99
+    fr = [O.Frame(gray[k], depth[k], *cam, L) for k in range(2)]
+    ctx.upload(np.array([1, 2]), gray, depth.astype(np.float32), cam, L)
+    for k in range(2):
+        for l in range(L):
+            ref, got = fr[k].level(l), ctx.download(k + 1, l)
+            assert np.array_equal(got["I"], ref["I"]), (k, l)
+            assert np.array_equal(got["dIx"], ref["dIx"]) and np.array_equal(got["dIy"], ref["dIy"]), (k, l)
+            assert np.array_equal(got["Z"].astype(np.float64), ref["Z"]), (k, l)
+    kw = dict(max_iterations=50)
+    ctx.set_config(A.make_config(**kw))
+    ctx.reset_stats()
+    ref = O.align(O.make_config(**kw), fr[0], O.IDENTITY, fr[1], O.IDENTITY)
+    got = ctx.align([dict(to=2, to_pose=O.IDENTITY, frm=[1], from_poses=O.IDENTITY, multi=False)])[0]
+    assert _kernel_was_used(ctx, level_kernel)
+    assert got["status"] == ref["status"] == 0
+    assert list(got["iters"][:L]) == list(ref["iters"]), (got["iters"], ref["iters"])
+    assert list(got["stop"][:L]) == list(ref["stop"])
+    dt, dr = pose_err(O, got["pose"], ref["pose"])
+    assert dt < POSE_TOL and dr < POSE_TOL
+    assert rel_fro(got["cov"], ref["cov"]) < 1e-3
 
 
 def test_single_frame_uploads(ctx, oracle, synth):

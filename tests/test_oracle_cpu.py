@@ -161,3 +161,47 @@ def test_camera_projecting_invalid_is_nan(oracle):
         ok = lib.vo_camera2image(C.c_double(10), C.c_double(10), C.c_double(320), C.c_double(240), oracle._p(p), oracle._p(uv))
         assert not ok
         assert np.isnan(uv).all()
+
+
+# ---------------------------------------------------------------------------------------------------------
+# the one real RGB-D frame the reference ships (odometry/test/resource/rgb.png, depth.png; crops of it in
+# tests/golden/tum_frame.npz, made by tests/golden/make_tum_frame.py): real texture, 40 % invalid depth
+# ---------------------------------------------------------------------------------------------------------
+TUM_FRAME = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "tum_frame.npz")
+TUM_CAM = (525.0 / 2, 525.0 / 2, 159.5, 119.5)  # test_alignment_se3.cpp:69 scaled to the 320x240 crop
+
+
+def test_real_frame_pyramid_and_gradients_match_opencv(oracle):
+    g = np.load(TUM_FRAME)
+    depth = g["depth0"].astype(np.float64) / 5000.0  # test_alignment_se3.cpp:99
+    f = oracle.Frame(g["gray0"], depth, *TUM_CAM, 3)
+    for l in range(3):
+        lv = f.level(l)
+        if l:
+            assert np.array_equal(lv["I"], g[f"pyr{l}"]), l
+        assert np.array_equal(lv["dIx"], g[f"dx{l}"]) and np.array_equal(lv["dIy"], g[f"dy{l}"]), l
+        # the depth pyramid keeps holes as zeros and never invents depth where the 3x3 window holds none
+        Z = lv["Z"]
+        assert np.isfinite(Z).all() and (Z >= 0).all()
+    Z0, Z1 = f.level(0)["Z"], f.level(1)["Z"]
+    assert 0.3 < (Z0 == 0).mean() < 0.5 and (Z1 == 0).mean() > 0.25
+    # a level-1 pixel is the masked median of the 3x3 level-0 window around (2i, 2j): it lies within the window's range
+    for (i, j) in [(10, 10), (40, 100), (100, 30), (77, 141)]:
+        w = Z0[2 * i - 1:2 * i + 2, 2 * j - 1:2 * j + 2]
+        valid = w[w > 0]
+        if valid.size == 0:
+            assert Z1[i, j] == 0
+        else:
+            assert valid.min() - 1e-12 <= Z1[i, j] <= valid.max() + 1e-12
+
+
+def test_real_frame_pair_aligns_on_the_oracle(oracle):
+    """Two crops of the real frame offset by (3, 2) pixels: the aligner must run to a regular stop on real imagery with
+    depth holes (this is the pair the GPU parity test repeats)."""
+    O = oracle
+    g = np.load(TUM_FRAME)
+    fr = [O.Frame(g[f"gray{k}"], g[f"depth{k}"].astype(np.float64) / 5000.0, *TUM_CAM, 3) for k in range(2)]
+    ref = O.align(O.make_config(max_iterations=50), fr[0], O.IDENTITY, fr[1], O.IDENTITY)
+    assert ref["status"] == 0 and sum(ref["iters"]) >= 3
+    xi = O.se3_log(ref["pose"])
+    assert np.all(np.isfinite(xi)) and 1e-4 < np.linalg.norm(xi) < 0.2  # the crops differ: the pose moved, sanely
