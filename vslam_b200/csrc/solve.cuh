@@ -333,7 +333,7 @@ __device__ __forceinline__ void gn_step_block(
 //   worse than the accepted state: reject (pose <- accepted pose, lambda *= up); else accept (lambda *= down from the
 //   second accept on); then dx = ldlt(A_acc + lambda diag A_acc)^-1 b_acc, se3 <- se3_acc * exp(-dx).
 // ------------------------------------------------------------------------------------------------
-__device__ __forceinline__ void lm_step_block(
+static __device__ __noinline__ void lm_step_block(
   JobState & J, ViewState * jv, const double * sums, SolveScratch & X, const SolverParams & p, int level,
   double * trace, bool forceStop)
 {
