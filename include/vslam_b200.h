@@ -50,6 +50,10 @@ enum { VSLAMB200_SOLVER_GN = 0, VSLAMB200_SOLVER_LM = 1 };
  * EXTENSION (forward formulation: bilinear sampling, Jacobians at the warped point every iteration, optional depth
  * residual; semantics of lukas_kanade/src/ForwardAdditive.cpp:52-137, defined by oracle/vslam_oracle.cpp) */
 enum { VSLAMB200_SAMPLING_NEAREST = 0, VSLAMB200_SAMPLING_BILINEAR = 1 };
+/* level_kernel: AUTO picks the moment-based kernel (csrc/gn_mom.cu) wherever it applies - scalers without offset
+ * (identity, t-distribution), at most 8 keyframes per job, the same number in every job of the call - and the dense
+ * kernel (csrc/gn_level.cu) otherwise; DENSE forces the dense kernel; MOMENTS is AUTO (tests assert which one ran) */
+enum { VSLAMB200_KERNEL_AUTO = 0, VSLAMB200_KERNEL_DENSE = 1, VSLAMB200_KERNEL_MOMENTS = 2 };
 
 typedef struct vslamb200_ctx vslamb200_ctx;
 
@@ -71,6 +75,10 @@ typedef struct vslamb200_config
   double lm_down;        /* LM only: lambda *= lm_down after an accepted step (0 < lm_down <= 1) */
   int sampling;          /* VSLAMB200_SAMPLING_* */
   double depth_weight;   /* BILINEAR only: weight of the depth residual Z_to(u',v') - q_z against the photometric one; 0 = off */
+  /* execution choices (results do not depend on them beyond rounding); 0 = automatic */
+  int level_kernel;      /* VSLAMB200_KERNEL_*: which Gauss-Newton level kernel runs the nearest-sampling path */
+  int cluster_size;      /* CTAs per alignment job of the level kernels (1, 2, 4, 8 or 16) */
+  int stream_parts;      /* a batch is cut into this many parts that walk the pyramid on their own streams (1..8) */
 } vslamb200_config;
 
 /* One alignment: SE3Alignment::align(from, to) (n_from == 1, multi == 0) or the vector overload (multi != 0).
@@ -107,12 +115,14 @@ typedef struct vslamb200_stats
   /* filled only when timing is enabled: interest-list construction and the Gauss-Newton level kernel per level */
   double ms_lists, ms_preprocess, ms_gn_level[VSLAMB200_MAX_LEVELS];
   uint64_t pixel_iterations_level[VSLAMB200_MAX_LEVELS];  /* pixel_iterations split by pyramid level */
-  /* SM clocks of the jobs' leading CTA per level, summed over jobs: phase A, histogram barrier, scale + weights,
-     phase C, block reduction, sums barrier, solve, then the scale section split: histogram gather + scaler, publish +
-     second cluster barrier, weight table */
+  /* SM clocks of the jobs' leading CTA per level, summed over jobs.  Dense kernel: phase A, histogram barrier, scale +
+     weights, phase C, block reduction, sums barrier, solve, then the scale section split: histogram gather + scaler,
+     publish + second cluster barrier, weight table.  Moment kernel: warp + sample + moment moves (evaluations after the
+     first), histogram barrier, scale + weights, A / b from the moments, sums barrier, cluster sums, solve, first
+     evaluation's warp + sample, moment build, and (a count, not clocks) points whose residual changed */
   uint64_t phase_clocks[VSLAMB200_MAX_LEVELS][10];
-  uint64_t incremental_launches; /* level launches that ran the incremental (per-residual moments) kernel */
-  uint64_t bounded_launches;     /* level launches of the cluster kernel whose phase A re-evaluates only flagged points */
+  uint64_t moment_launches;      /* level launches that ran the moment-based kernel */
+  uint64_t dense_launches;       /* level launches that ran the dense kernel */
 } vslamb200_stats;
 
 const char * vslamb200_last_error(void);

@@ -35,7 +35,9 @@ def capi():
 
 
 @pytest.fixture()
-def ctx(capi):
+def ctx(capi, request):
+    if "level_kernel" in request.fixturenames:  # the kernel choice reaches make_config through the environment
+        request.getfixturevalue("level_kernel")
     c = capi.Context(capi.make_config())
     yield c
     c.close()

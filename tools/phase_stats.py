@@ -1,6 +1,8 @@
 """Per-level timing and per-phase SM clocks of a full alignment batch (F-1 pairs of a 640x480 sequence, 4 levels).
-Phase slots of the dense kernel: phaseA, bar_hist, scale, phaseC, blockred, bar_sums, solve; of the incremental
-kernel: 0 warp+sample(+moment moves), 1 moment build (first evaluation), 2 scale, 3 A/b from moments, 6 solve."""
+Phase slots of the dense kernel: phaseA, bar_hist, scale, phaseC, blockred, bar_sums, solve (7-9: scale sub-laps); of the
+moment kernel: 0 warp+sample+moment moves (evaluations after the first), 1 histogram barrier, 2 scale+weights, 3 A/b from
+the moments, 4 sums barrier, 5 cluster sums, 6 solve, 7 first evaluation's warp+sample, 8 moment build, 9 moved points (a
+count).  VSLAMB200_KERNEL=dense|moments, VSLAMB200_CLUSTER, VSLAMB200_PARTS select the execution (capi.make_config)."""
 import argparse
 import os
 import sys
@@ -27,15 +29,19 @@ capi.check(capi.lib().vslamb200_set_timing(ctx.h, args.timing))
 ctx.reset_stats()
 res = ctx.align(jobs)
 st = ctx.stats()
-print("INC", os.environ.get("VSLAMB200_INC"), "BOUND", os.environ.get("VSLAMB200_BOUND"), "incremental launches", st["incremental_launches"],
-      "bounded launches", st["bounded_launches"], "ms_gn_level",
+print("KERNEL", os.environ.get("VSLAMB200_KERNEL"), "moment launches", st["moment_launches"],
+      "dense launches", st["dense_launches"], "ms_gn_level",
       [round(x, 3) for x in st["ms_gn_level"][:args.levels]], "ms_lists", round(st["ms_lists"], 3))
 for l in range(args.levels):
     pc = st["phase_clocks"][l]
-    tot = sum(pc[:7]) or 1
+    tot = sum(pc[:9] if st["moment_launches"] else pc[:7]) or 1
     ev = st["pixel_iterations_level"][l] / (W * H / 4 ** l)
-    print(" level", l, "evals/job", round(ev / len(jobs), 2), "kclocks/job", [round(c / len(jobs) / 1e3, 1) for c in pc[:7]],
-          "share", [round(c / tot, 3) for c in pc[:7]])
-    if st["point_iterations"]:
-        print("   slots 7-9 (incremental: flagged, changed, missed points; dense: scale sub-laps)", pc[7:10])
+    nsl = 9 if st["moment_launches"] else 7
+    print(" level", l, "evals/job", round(ev / len(jobs), 2), "kclocks/job", [round(c / len(jobs) / 1e3, 1) for c in pc[:nsl]],
+          "share", [round(c / tot, 3) for c in pc[:nsl]])
+    if st["moment_launches"]:
+        pts = st["point_iterations"] / max(1, st["gn_iterations"]) if l == 0 else 0
+        print("   moved points per job and evaluation", round(pc[9] / len(jobs) / max(ev / len(jobs), 1), 1))
+    else:
+        print("   slots 7-9 (scale sub-laps)", pc[7:10])
 ctx.close()

@@ -365,6 +365,11 @@ static int check_cfg(const vslamb200_config * cfg)
   if (cfg->sampling != VSLAMB200_SAMPLING_NEAREST && cfg->sampling != VSLAMB200_SAMPLING_BILINEAR)
     return fail(VSLAMB200_EINVAL, "bad sampling");
   if (!(cfg->depth_weight >= 0.0)) return fail(VSLAMB200_EINVAL, "bad depth_weight");
+  if (cfg->level_kernel < 0 || cfg->level_kernel > VSLAMB200_KERNEL_MOMENTS) return fail(VSLAMB200_EINVAL, "bad level_kernel");
+  if (cfg->cluster_size != 0 && cfg->cluster_size != 1 && cfg->cluster_size != 2 && cfg->cluster_size != 4 &&
+      cfg->cluster_size != 8 && cfg->cluster_size != 16)
+    return fail(VSLAMB200_EINVAL, "bad cluster_size (0, 1, 2, 4, 8 or 16)");
+  if (cfg->stream_parts < 0 || cfg->stream_parts > 8) return fail(VSLAMB200_EINVAL, "bad stream_parts (0..8)");
   if (cfg->sampling == VSLAMB200_SAMPLING_NEAREST && cfg->depth_weight != 0.0)
     return fail(VSLAMB200_EINVAL, "the depth residual needs bilinear sampling");
   if (cfg->sampling == VSLAMB200_SAMPLING_BILINEAR && cfg->loss_kind != VSLAMB200_LOSS_NONE &&
@@ -699,6 +704,7 @@ struct Problem
   std::vector<vb::JobState> jobs;
   std::vector<vb::ViewState> views;
   int W = 0, H = 0, nLevels = 0, maxViews = 1;
+  bool uniformViews = true;  // every job has the same number of keyframes
   vb::FrameDev geo;
 };
 
@@ -751,6 +757,7 @@ int build_problem(vslamb200_ctx * c, const vslamb200_job * jobs, int nJobs, Prob
     }
     J.nLevels = P.nLevels;
     P.maxViews = std::max(P.maxViews, in.n_from);
+    if (in.n_from != jobs[0].n_from) P.uniformViews = false;
     P.jobs[j] = J;
   }
   // the reference indexes the point cloud (depth dims) with the intensity width; at odd sizes the
@@ -761,14 +768,12 @@ int build_problem(vslamb200_ctx * c, const vslamb200_job * jobs, int nJobs, Prob
   return 0;
 }
 
-// cluster size of a level's Gauss-Newton kernel: enough CTAs per job that a slice of the interest list is a few
-// ten thousand points (its residuals then stay in shared memory), never more than the portable maximum of 8
-int pick_cluster(int npx, int nJobs)
+// cluster size of the dense level kernel: enough CTAs per job that a slice of the interest list is a few ten thousand
+// points, never more than the portable maximum of 8
+int pick_cluster(const vslamb200_config & cfg, int npx, int nJobs)
 {
-  if (const char * e = std::getenv("VSLAMB200_CLUSTER")) {  // tuning override
-    const int c = std::atoi(e);
-    if (c == 1 || c == 2 || c == 4 || c == 8 || c == 16) return c;
-  }
+  const int o = cfg.cluster_size;  // tuning override
+  if (o == 1 || o == 2 || o == 4 || o == 8 || o == 16) return o;
   int c = npx > 160000 ? 8 : npx > 40000 ? 4 : npx > 12000 ? 2 : 1;
   // Latency mode: a handful of jobs cannot fill the device, so each job spreads over as many SMs as a cluster can
   // span (16 CTAs is the non-portable cluster maximum of sm_100; the launcher opts in).  Measured on one 640x480
@@ -778,17 +783,27 @@ int pick_cluster(int npx, int nJobs)
   return c;
 }
 
-// Which Gauss-Newton level kernel runs a level.  The incremental kernel (gn_inc.cu) keeps per-residual moments in shared
-// memory and needs one keyframe per job and a scaler without offset.  It is exact and parity-tested, but with one CTA per
-// job its scans are latency-bound and it is slower than the dense cluster kernel today, so it is
-// opt-in: VSLAMB200_INC=1 uses it on levels of at least 50 000 pixels, =2 wherever it is applicable (tests).
-bool use_incremental(const Problem & P, const vb::SolverParams & sp, int npx)
+// The moment-based level kernel (gn_mom.cu) keeps per-residual-magnitude moments of one keyframe per CTA: it needs a
+// weight that is a function of |r| (scalers without offset), the same number K <= 8 of keyframes in every job of the
+// launch (the cluster's CTAs are split among them) and list indices that fit 20 bits.
+bool use_moments(const vslamb200_config & cfg, const Problem & P, const vb::SolverParams & sp, int npx)
 {
-  int mode = 0;
-  if (const char * e = std::getenv("VSLAMB200_INC")) mode = std::atoi(e);
-  if (mode <= 0 || P.maxViews != 1 || npx > (1 << 20) || sp.solverKind != VSLAMB200_SOLVER_GN) return false;
-  if (sp.scalerKind != VSLAMB200_SCALER_IDENTITY && sp.scalerKind != VSLAMB200_SCALER_TDIST) return false;
-  return mode >= 2 || npx >= 50000;
+  if (cfg.level_kernel == VSLAMB200_KERNEL_DENSE) return false;
+  if (!P.uniformViews || P.maxViews > 8 || npx > (1 << 20)) return false;
+  return sp.scalerKind == VSLAMB200_SCALER_IDENTITY || sp.scalerKind == VSLAMB200_SCALER_TDIST;
+}
+
+// CTAs per keyframe of the moment kernel (256 threads each): a slice of a few ten thousand points per CTA; small
+// batches spread every job over as many SMs as a cluster can span (latency mode, as above)
+int pick_cpv(const vslamb200_config & cfg, int npx, int nJobs, int K)
+{
+  int c = npx > 160000 ? 4 : npx > 40000 ? 2 : 1;
+  if (nJobs <= 8) c = npx > 12000 ? 16 : npx > 3000 ? 8 : 4;
+  const int o = cfg.cluster_size;
+  if (o == 1 || o == 2 || o == 4 || o == 8 || o == 16) c = o;
+  const int cap = nJobs <= 8 ? 16 : 8;
+  while (c > 1 && c * K > cap) c >>= 1;
+  return c;
 }
 
 // One pyramid level for the jobs [job0, job0 + nJobs) (their views are contiguous: [view0, view0 + nViews)), queued on
@@ -805,7 +820,6 @@ int run_level(vslamb200_ctx * c, Problem & P, int level, const vb::SolverParams 
   const vb::FrameDev * table = c->dFrames.as<vb::FrameDev>();
   double * dTrace = c->traceEnabled ? c->trace.as<double>() : nullptr;
   const size_t traceJobStride = (size_t)P.nLevels * sp.maxIterations * vb::TRACE_STRIDE;
-  const int cluster = pick_cluster(npx, nJobs);
 
   if (c->timing) CK(cudaEventRecord(c->ev[0], stream));
   vb::launch_level_setup(table, dJobs, dViews, view0, nViews, level, stream);
@@ -829,26 +843,14 @@ int run_level(vslamb200_ctx * c, Problem & P, int level, const vb::SolverParams 
         if (active == 0) break;
       }
     }
-  } else if (use_incremental(P, sp, npx)) {
-    // VSLAMB200_INC_CHECK=1 (tests): every point is re-evaluated in every iteration and the points whose residual changed
-    // although their motion bound had not asked for them are counted (stats.phase_clocks[level][9], must stay 0)
-    const char * chk = std::getenv("VSLAMB200_INC_CHECK");
-    c->stats.incremental_launches++;
-    CK(vb::launch_gn_inc(dJobs, dViews, job0, nJobs, sp, level, maxEvals, dTrace, traceJobStride, chk && std::atoi(chk) > 0, stream));
+  } else if (use_moments(c->cfg, P, sp, npx)) {
+    c->stats.moment_launches++;
+    CK(vb::launch_gn_mom(dJobs, dViews, job0, nJobs, P.maxViews, pick_cpv(c->cfg, npx, nJobs, P.maxViews), sp, level, maxEvals,
+                         dTrace, traceJobStride, c->partials.as<double>(), stream));
   } else {
-    // bounded variant of the cluster kernel (phase A re-evaluates only the points whose sampled pixel can have
-    // changed; bounds.cuh): one keyframe per job and Gauss-Newton.  Exact and parity-tested, but its scan and queueing cost
-    // about as many instructions as the dense phase A saves at the 5-10 % of points the bounds flag per iteration
-    // (DESIGN.md section 4), so it is opt-in: VSLAMB200_BOUND=1 uses it on levels of at least 50 000 pixels, =2 on every
-    // level (tests).
-    int mode = 0;
-    if (const char * e = std::getenv("VSLAMB200_BOUND")) mode = std::atoi(e);
-    const bool bounded = mode > 0 && P.maxViews == 1 && sp.solverKind == VSLAMB200_SOLVER_GN && npx <= (1 << 20) &&
-                         (mode >= 2 || npx >= 50000);
-    const char * chk = std::getenv("VSLAMB200_INC_CHECK");
-    if (bounded) c->stats.bounded_launches++;
-    CK(vb::launch_gn_level(dJobs, dViews, job0, nJobs, P.maxViews, cluster, sp, level, maxEvals, dTrace, traceJobStride,
-                           c->partials.as<double>(), stream, bounded, chk && std::atoi(chk) > 0));
+    c->stats.dense_launches++;
+    CK(vb::launch_gn_level(dJobs, dViews, job0, nJobs, P.maxViews, pick_cluster(c->cfg, npx, nJobs), sp, level, maxEvals, dTrace,
+                           traceJobStride, c->partials.as<double>(), stream));
   }
   if (c->timing) CK(cudaEventRecord(c->ev[2], stream));
   c->stats.kernel_launches += 6;
@@ -869,10 +871,10 @@ int prepare_workspace(vslamb200_ctx * c, Problem & P, const vb::SolverParams & s
   const int nJobs = (int)P.jobs.size(), nViews = (int)P.views.size();
   const size_t npx0 = (size_t)P.W * P.H;
   const size_t listStride = align_up(npx0, vb::LIST_TILE);
-  // per view: list tiles (20 B per candidate pixel) | r u16 | lim 4 x u16 | 32 B per tile   (30.25 bytes per candidate pixel)
+  // per view and candidate pixel: list tile 8 B | record 16 B | residual code 2 B | sort permutation 4 B = 30 B
   const size_t tileBytes = listStride / vb::LIST_TILE * vb::LIST_TILE_BYTES;
-  const size_t tileStateBytes = listStride / vb::LIST_TILE * 32;
-  const size_t viewBytes = tileBytes + listStride * 10 + tileStateBytes;
+  const size_t recBytes = listStride * sizeof(vb::ListRec);
+  const size_t viewBytes = tileBytes + recBytes + listStride * 2 + listStride * 4 + 256;
   CK(c->lists.ensure(viewBytes * nViews));
   CK(c->chunkCounts.ensure((size_t)nViews * vb::list_chunks_for((int)npx0) * sizeof(int)));
   CK(c->partials.ensure((size_t)nViews * vb::NE_TERMS * sizeof(double)));
@@ -881,9 +883,9 @@ int prepare_workspace(vslamb200_ctx * c, Problem & P, const vb::SolverParams & s
     vb::ViewState & V = P.views[v];
     uint8_t * b = base + (size_t)v * viewBytes;
     V.tiles = b;
-    V.r = (int16_t *)(b + tileBytes);
-    V.lim = (float *)(b + tileBytes + listStride * 2);
-    V.tileState = (float *)(b + tileBytes + listStride * 10);
+    V.rec = (vb::ListRec *)(b + tileBytes);
+    V.r = (int16_t *)(b + tileBytes + recBytes);
+    V.perm = (uint32_t *)(b + tileBytes + recBytes + listStride * 2);
   }
   if (sp.sampling == VSLAMB200_SAMPLING_BILINEAR) {
     // bilinear extension: per view 16 B per candidate pixel (r_I, r_Z in fp64) + 28 partial sums per 2048 list entries
@@ -941,7 +943,7 @@ int vslamb200_align(vslamb200_ctx * c, const vslamb200_job * jobs, int nJobs, vs
   // clusters.  A large batch is therefore cut into two halves that walk down the pyramid on their own streams: one
   // half's tail is filled by the other half's next kernel.  (Timing mode keeps one stream: it measures whole launches.)
   int nParts = (!c->timing && nJobs >= 2 * kMinJobsPerPart && sp.sampling == VSLAMB200_SAMPLING_NEAREST) ? 2 : 1;
-  if (const char * e = std::getenv("VSLAMB200_PARTS")) nParts = std::max(1, std::min(vslamb200_ctx::kMaxParts, std::atoi(e)));
+  if (c->cfg.stream_parts > 0) nParts = std::min(vslamb200_ctx::kMaxParts, c->cfg.stream_parts);
   nParts = std::min(nParts, nJobs);
   if (sp.sampling != VSLAMB200_SAMPLING_NEAREST) nParts = 1;  // the extension's host loop reads one active-job counter
   if (nParts == 1) {
@@ -1047,8 +1049,15 @@ int vslamb200_evaluate(
   vb::view_set_x(V);
   CK(cudaMemcpyAsync(dViews, &V, sizeof(V), cudaMemcpyHostToDevice, c->stream));
   CK(cudaMemsetAsync(c->partials.p, 0, vb::NE_TERMS * sizeof(double), c->stream));
-  const int cluster = pick_cluster(npx, 1);
-  CK(vb::launch_gn_level(dJobs, dViews, 0, nJobs, 1, cluster, sp, level, 1, nullptr, 0, c->partials.as<double>(), c->stream));
+  if (use_moments(c->cfg, P, sp, npx)) {
+    c->stats.moment_launches++;
+    CK(vb::launch_gn_mom(dJobs, dViews, 0, nJobs, 1, pick_cpv(c->cfg, npx, 1, 1), sp, level, 1, nullptr, 0, c->partials.as<double>(),
+                         c->stream));
+  } else {
+    c->stats.dense_launches++;
+    CK(vb::launch_gn_level(dJobs, dViews, 0, nJobs, 1, pick_cluster(c->cfg, npx, 1), sp, level, 1, nullptr, 0,
+                           c->partials.as<double>(), c->stream));
+  }
   c->stats.kernel_launches += 6;
   if (rcode) {
     CK(c->plane.ensure((size_t)npx * 2));

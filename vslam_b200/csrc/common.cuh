@@ -38,7 +38,15 @@ struct Pose
 
 // Per (job, keyframe) state of the current pyramid level.
 constexpr int LIST_TILE = 128;
-constexpr int TILE_OFF_D = 0, TILE_OFF_UVT = 512, TILE_OFF_G = 1024, TILE_OFF_ZI = 1536, LIST_TILE_BYTES = 2560;
+constexpr int TILE_OFF_D = 0, TILE_OFF_UVT = 512, LIST_TILE_BYTES = 1024;
+// Per interest point, in list order: what the Jacobian needs (Warp.cpp:166-201, InverseCompositional.cpp:79-80)
+struct alignas(16) ListRec
+{
+  uint32_t uvt;  // u | v << 12 | T << 24
+  uint32_t g;    // dIx (low 16) | dIy (high 16)
+  double zi;     // 1 / depth in fp64 (Warp.cpp:170)
+};
+constexpr int JSTAT = 12;  // per view: max |dIx P_i| (6), max |dIy Q_i| (6) over the list, J_i = fxJ dIx P_i + fyJ dIy Q_i
 
 struct ViewState
 {
@@ -54,11 +62,15 @@ struct ViewState
   // fp32 hi/lo splits of the fp64 constants: keeps the fp32 Jacobian free of coherent rounding bias
   float ifxH, ifxL, ifyH, ifyL, kxH, kxL, kyH, kyL, fxJH, fxJL, fyJH, fyJL;
   float fx32, fy32;
-  // interest list: LIST_TILE-point tiles, each  d f32[128] | uvt u32[128] | g u32[128] | zi f64[128]  so that one
-  // bulk copy brings what a phase needs ([d|uvt] for the warp phase, [uvt|g|zi] for the Jacobian phase)
+  // interest list, two streams in the same (row-major) order:
+  //   tiles  LIST_TILE-point tiles  d f32[128] | uvt u32[128]  - what the warp phase streams (one bulk copy per tile)
+  //   rec    one ListRec per point  {uvt, g, zi}               - what the Jacobian needs
   //   uvt = u | v<<12 | T<<24, d = depth, g = dIx (low 16) | dIy (high 16), zi = 1 / depth in fp64 (Warp.cpp:170)
   unsigned char * tiles;
+  ListRec * rec;
   int16_t * r;              // residual code of the current iteration: r + 255, R_CODE_INVISIBLE if not visible
+  uint32_t * perm;          // moments kernel: list indices of a CTA's slice ordered by residual code (first evaluation)
+  unsigned jstat[JSTAT];    // float bits (non-negative): bounds of the Jacobian components over the list (lists.cu)
   int nIp;                  // retained interest points (nConstraints of this view)
   // warp
   Pose poseRef;             // keyframe pose
@@ -70,11 +82,6 @@ struct ViewState
   double xPred[6];          // MotionPrior::_xPred (SE3Alignment.cpp:32)
   double xCur[6];           // log(se3), kept in step with se3
   Pose se3Acc;              // Levenberg-Marquardt: se3 at the last accepted evaluation
-  // robust weights of the current iteration
-  // incremental kernel (gn_inc.cu): per point the value of the tile's cumulative motion bound at which the point has to
-  // be re-evaluated; per LIST_TILE 8 floats: u, v, 1/depth ranges of the tile's points, cumulative motion bound, spare
-  float * lim;
-  float * tileState;
   // bilinear extension (ext.cu): per list entry {r_I, r_Z} of the current iteration (NaN = not visible / no depth),
   // per 2048-entry block the 28 partial sums, scale of the depth residuals
   double2 * extR;
@@ -285,14 +292,14 @@ void launch_scatter_rcode(const ViewState * views, int view, int16_t * plane, cu
 // gn_level.cu
 size_t gn_level_static_smem();
 cudaError_t launch_gn_level(JobState * jobs, ViewState * views, int job0, int nJobs, int maxViewsPerJob, int clusterSize,
-                            SolverParams p, int level, int maxEvals, double * trace, size_t traceJobStride, double * viewSums, cudaStream_t s,
-                            bool bounded = false, int checkMode = 0);
+                            SolverParams p, int level, int maxEvals, double * trace, size_t traceJobStride, double * viewSums, cudaStream_t s);
+// gn_mom.cu (moment-based level kernel: K keyframes per job, cpv CTAs per keyframe, scalers without offset)
+cudaError_t launch_gn_mom(JobState * jobs, ViewState * views, int job0, int nJobs, int K, int cpv, SolverParams p, int level,
+                          int maxEvals, double * trace, size_t traceJobStride, double * viewSums, cudaStream_t s);
+size_t gn_mom_smem(int K);
 // ext.cu (bilinear / depth-residual extension): one Gauss-Newton (or LM) evaluation + step for every active job
 constexpr int EXT_CHUNK = 2048;  // list entries per block
 void launch_ext_iteration(JobState * jobs, ViewState * views, int job0, int nJobs, int view0, int nViews, int maxPoints,
                           SolverParams p, int level, bool forceStop, double * trace, size_t traceJobStride, int * activeCount,
                           cudaStream_t s);
-// gn_inc.cu (incremental level kernel: single keyframe, zero-offset scalers)
-cudaError_t launch_gn_inc(JobState * jobs, ViewState * views, int job0, int nJobs, SolverParams p, int level, int maxEvals,
-                          double * trace, size_t traceJobStride, int checkMode, cudaStream_t s);
 }  // namespace vb

@@ -25,7 +25,7 @@
 #include "robust.cuh"
 #include "solve.cuh"
 #include "warp_filter.cuh"
-#include "bounds.cuh"
+#include "level_common.cuh"
 
 namespace cg = cooperative_groups;
 
@@ -175,65 +175,14 @@ constexpr int CH = 4 * GT;                  // interest points per chunk (4 per 
 constexpr int NS = 4;                       // ring stages
 constexpr int WCH = CH / (GT / 32);         // points of a chunk owned by one warp == one list tile
 static_assert(WCH == LIST_TILE, "a warp's share of a chunk is one list tile");
-static_assert(LIST_TILE * 8 == 1024, "a tile's limits fill the phase-A part of a ring stage");
-// one stage of a warp's private ring.  Phase A: [d | uvt] (the first 1024 B of the tile).  Phase C: [uvt | g | zi]
-// (the last 2048 B of the tile) followed by the tile's 128 residual codes.
+// one stage of a warp's private ring.  Phase A: the tile [d | uvt] (1024 B).  Phase C: the tile's 128 records
+// {uvt, g, zi} (2048 B) followed by its 128 residual codes.
 constexpr int A_OFF_D = 0, A_OFF_UVT = 512, A_BYTES = 1024;
-constexpr int C_OFF_UVT = 0, C_OFF_G = 512, C_OFF_ZI = 1024, C_OFF_R = 2048, C_TILE_BYTES = 2048, C_R_BYTES = 2 * WCH;
+constexpr int C_OFF_R = 2048, C_TILE_BYTES = 2048, C_R_BYTES = 2 * WCH;
 constexpr int WSTAGE_BYTES = C_OFF_R + C_R_BYTES;
 constexpr int STAGE_BYTES = WSTAGE_BYTES * (GT / 32);
-static_assert(TILE_OFF_D == 0 && TILE_OFF_UVT == A_OFF_UVT && TILE_OFF_G - TILE_OFF_UVT == C_OFF_G &&
-              TILE_OFF_ZI - TILE_OFF_UVT == C_OFF_ZI && LIST_TILE_BYTES - TILE_OFF_UVT == C_TILE_BYTES, "tile layout");
-
-__device__ __forceinline__ uint32_t smem_u32(const void * p) { return (uint32_t)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void mbar_init(uint64_t * bar, uint32_t count)
-{
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(uint64_t * bar, uint32_t bytes)
-{
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(uint64_t * bar)
-{
-  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint64_t * bar, uint32_t parity)
-{
-  const uint32_t a = smem_u32(bar);
-  uint32_t done;
-  do {
-    asm volatile(
-      "{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\tselp.u32 %0, 1, 0, p;\n\t}"
-      : "=r"(done)
-      : "r"(a), "r"(parity), "r"(0x989680u)  // suspend-time hint: sleep in hardware instead of re-polling
-      : "memory");
-  } while (!done);
-}
-// L2 policy for data that is streamed once per phase (the static interest lists): evict first, so that the lines
-// which are re-used within an iteration (the gathered target image, the residual codes) stay in L2
-__device__ __forceinline__ uint64_t l2_evict_first_policy()
-{
-  uint64_t pol;
-  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
-  return pol;
-}
-__device__ __forceinline__ void bulk_g2s_stream(void * dst, const void * src, uint32_t bytes, uint64_t * bar, uint64_t pol)
-{
-  asm volatile(
-    "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;" ::"r"(
-      smem_u32(dst)),
-    "l"(src), "r"(bytes), "r"(smem_u32(bar)), "l"(pol)
-    : "memory");
-}
-// global -> own shared memory, completion counted in bytes on an mbarrier of this CTA
-__device__ __forceinline__ void bulk_g2s(void * dst, const void * src, uint32_t bytes, uint64_t * bar)
-{
-  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
-                 smem_u32(dst)),
-               "l"(src), "r"(bytes), "r"(smem_u32(bar))
-               : "memory");
-}
+static_assert(TILE_OFF_D == A_OFF_D && TILE_OFF_UVT == A_OFF_UVT && LIST_TILE_BYTES == A_BYTES &&
+              sizeof(ListRec) * LIST_TILE == C_TILE_BYTES, "tile layout");
 
 struct LevelShared
 {
@@ -244,9 +193,6 @@ struct LevelShared
   SolveScratch X;
   double so[2];  // {scale, offset} of the current view, written by the cluster's leading CTA
   alignas(8) uint64_t full[GT / 32][NS];  // per warp and stage: the TMA bytes have landed
-  // bounded variant: what the last Gauss-Newton step did (for the motion bounds); flagged / changed / missed points
-  StepConsts stp;
-  unsigned long long cnt[3];
 };
 // dynamic shared memory: ring | ViewState[K] | partial[2][K][28] | sums[K][28]
 __host__ __device__ inline size_t level_dyn_smem(int K)
@@ -257,24 +203,13 @@ __host__ __device__ inline size_t level_dyn_smem(int K)
 template <typename T>
 __device__ __forceinline__ void block_copy(T * dst, const T * src)
 {
-  static_assert(sizeof(T) % 4 == 0, "word copy");
-  const uint32_t * s = reinterpret_cast<const uint32_t *>(src);
-  uint32_t * d = reinterpret_cast<uint32_t *>(dst);
-  for (int i = threadIdx.x; i < (int)(sizeof(T) / 4); i += GT) d[i] = s[i];
-}
-
-// slice of a view's interest list owned by one CTA of the cluster: whole list tiles
-__device__ __forceinline__ void slice_of(int n, unsigned C, unsigned rank, int & p0, int & p1)
-{
-  const int per = (((n + (int)C - 1) / (int)C) + LIST_TILE - 1) / LIST_TILE * LIST_TILE;
-  p0 = min(n, (int)rank * per);
-  p1 = min(n, p0 + per);
+  block_copy_n<GT>(dst, src);
 }
 
 // Every warp owns a private ring: lane 0 streams the warp's quarter of chunk c of the slice [p0, p1) into stage
 // (item % NS) of that ring.  A warp refills a stage right after it has copied it into registers, so no warp ever
 // waits for another one (no "empty" barriers, no producer thread that can fall behind).
-constexpr int CHUNK_A = 0, CHUNK_C = 1, CHUNK_LIMITS = 2;  // what a ring stage is filled with
+constexpr int CHUNK_A = 0, CHUNK_C = 1;  // what a ring stage is filled with
 __device__ __forceinline__ void issue_chunk(
   LevelShared & S, unsigned char * ring, const ViewState & V, int kind, int p0, int p1, int c, uint32_t item, int warp,
   uint64_t pol)
@@ -286,248 +221,19 @@ __device__ __forceinline__ void issue_chunk(
     return;
   }
   unsigned char * st = ring + (size_t)(warp * NS + item % NS) * WSTAGE_BYTES;
-  const unsigned char * tile = V.tiles + (size_t)(start / LIST_TILE) * LIST_TILE_BYTES;
   if (kind == CHUNK_C) {
     mbar_expect_tx(bar, C_TILE_BYTES + C_R_BYTES);
-    bulk_g2s_stream(st, tile + TILE_OFF_UVT, C_TILE_BYTES, bar, pol);
+    bulk_g2s_stream(st, V.rec + start, C_TILE_BYTES, bar, pol);
     bulk_g2s(st + C_OFF_R, V.r + start, C_R_BYTES, bar);
-  } else if (kind == CHUNK_LIMITS) {
-    // the tile's limits (4 x 16 bit per entry): re-read and partly rewritten every evaluation, so no evict-first hint
-    mbar_expect_tx(bar, A_BYTES);
-    bulk_g2s(st, reinterpret_cast<const unsigned char *>(V.lim) + (size_t)start * 8, A_BYTES, bar);
   } else {
     mbar_expect_tx(bar, A_BYTES);
-    bulk_g2s_stream(st, tile, A_BYTES, bar, pol);
+    bulk_g2s_stream(st, V.tiles + (size_t)(start / LIST_TILE) * LIST_TILE_BYTES, A_BYTES, bar, pol);
   }
 }
 
-// Start of a level in the bounded variant, per tile of this CTA's slice: the ranges of (u, v, 1/depth) over its
-// entries (for the motion bounds), accumulated bounds = 0, and every point's limits at the level's initial pose (the
-// pose of the first evaluation, whose dense phase A samples every point).  A point whose fp32 evaluation is within
-// its error bound of a decision boundary gets zero margins: it is looked at again in every evaluation.
-static __device__ __noinline__ void bounded_prologue(const ViewState & V, unsigned C, unsigned rank)
-{
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  WarpConsts c;
-  c.r00 = V.rI[0]; c.r01 = V.rI[1]; c.r02 = V.rI[2]; c.r10 = V.rI[3]; c.r11 = V.rI[4]; c.r12 = V.rI[5];
-  c.r20 = V.rI[6]; c.r21 = V.rI[7]; c.r22 = V.rI[8];
-  c.t0 = V.t32[0]; c.t1 = V.t32[1]; c.t2 = V.t32[2];
-  c.fx = V.fx32; c.fy = V.fy32; c.ifx = V.ifxH; c.ify = V.ifyH; c.kx = V.kxH; c.ky = V.kyH;
-  c.epsA = V.epsA; c.epsB = V.epsB; c.Wt = V.Wt; c.Ht = V.Ht;
-  if (V.Wt < 4 || V.Ht < 4) c.epsB = __int_as_float(0x7f800000);  // no strict interior: always the exact path
-  int p0, p1;
-  slice_of(V.nIp, C, rank, p0, p1);
-  uint2 * lim = reinterpret_cast<uint2 *>(V.lim);
-  for (int t = p0 / LIST_TILE + warp; t * LIST_TILE < p1; t += GT / 32) {
-    const unsigned char * tp = V.tiles + (size_t)t * LIST_TILE_BYTES;
-    const uint4 pk4 = reinterpret_cast<const uint4 *>(tp + TILE_OFF_UVT)[lane];
-    const float4 dd4 = reinterpret_cast<const float4 *>(tp + TILE_OFF_D)[lane];
-    const uint32_t pk[4] = {pk4.x, pk4.y, pk4.z, pk4.w};
-    const float dd[4] = {dd4.x, dd4.y, dd4.z, dd4.w};
-    unsigned ulo = 0xffffffffu, uhi = 0u, vlo = 0xffffffffu, vhi = 0u, zlo = 0xffffffffu, zhi = 0u;
-    uint32_t Lw[8];
-#pragma unroll
-    for (int q = 0; q < 4; q++) {
-      float m[4];
-      directional_margins(c, warp_eval(c, pk[q], dd[q]), m);  // padding entries compute on harmless values
-      Lw[2 * q] = margin_q15(m[0]) | (margin_q15(m[1]) << 16);
-      Lw[2 * q + 1] = margin_q15(m[2]) | (margin_q15(m[3]) << 16);
-      if (t * LIST_TILE + 4 * lane + q < p1) {
-        const unsigned ui = pk[q] & 0xfff, vi = (pk[q] >> 12) & 0xfff;
-        ulo = min(ulo, ui); uhi = max(uhi, ui); vlo = min(vlo, vi); vhi = max(vhi, vi);
-        const unsigned zb = __float_as_uint(__fdividef(1.f, dd[q]));  // positive floats order like their bit patterns
-        zlo = min(zlo, zb); zhi = max(zhi, zb);
-      }
-    }
-    uint4 * lp = reinterpret_cast<uint4 *>(lim + (size_t)t * LIST_TILE + 4 * lane);
-    lp[0] = make_uint4(Lw[0], Lw[1], Lw[2], Lw[3]);
-    lp[1] = make_uint4(Lw[4], Lw[5], Lw[6], Lw[7]);
-    ulo = __reduce_min_sync(0xffffffffu, ulo); uhi = __reduce_max_sync(0xffffffffu, uhi);
-    vlo = __reduce_min_sync(0xffffffffu, vlo); vhi = __reduce_max_sync(0xffffffffu, vhi);
-    zlo = __reduce_min_sync(0xffffffffu, zlo); zhi = __reduce_max_sync(0xffffffffu, zhi);
-    if (lane == 0) {
-      float4 * tsp = reinterpret_cast<float4 *>(V.tileState + (size_t)t * 8);
-      tsp[0] = make_float4(__uint_as_float(ulo | (uhi << 16)), __uint_as_float(vlo | (vhi << 16)),
-                           __uint_as_float(zlo) * 0.9999f, __uint_as_float(zhi) * 1.0001f);  // 1/d was approximate
-      tsp[1] = make_float4(0.f, 0.f, 0.f, 0.f);  // accumulated bounds {+u | -u << 16, +v | -v << 16} = 0, spare
-    }
-  }
-}
-
-// Phase A of the bounded variant for every evaluation of a level but the first (own function: its register
-// allocation stays apart from the dense phases of the kernel).
-static __device__ __noinline__ void bounded_phase_a(
-  LevelShared & S, unsigned char * ring, const ViewState & V, int * hist, int p0, int p1, int nCh, uint32_t item, uint64_t pol,
-  int checkMode)
-{
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  // Scan of the limits (streamed through the ring, one tile per warp and chunk) against the tile's accumulated
-  // motion bounds; the flagged entries are queued per warp and re-evaluated 32 EB at a time.
-  constexpr int EB = 4, QE = 256;
-  constexpr bool first = false;
-  WarpConsts c;
-  c.r00 = V.rI[0]; c.r01 = V.rI[1]; c.r02 = V.rI[2]; c.r10 = V.rI[3]; c.r11 = V.rI[4]; c.r12 = V.rI[5];
-  c.r20 = V.rI[6]; c.r21 = V.rI[7]; c.r22 = V.rI[8];
-  c.t0 = V.t32[0]; c.t1 = V.t32[1]; c.t2 = V.t32[2];
-  c.fx = V.fx32; c.fy = V.fy32; c.ifx = V.ifxH; c.ify = V.ifyH; c.kx = V.kxH; c.ky = V.kyH;
-  c.epsA = V.epsA; c.epsB = V.epsB; c.Wt = V.Wt; c.Ht = V.Ht;
-  if (V.Wt < 4 || V.Ht < 4) c.epsB = __int_as_float(0x7f800000);  // no strict interior: always the exact path
-  const uint8_t * __restrict__ I = V.I;
-  uint2 * lim = reinterpret_cast<uint2 *>(V.lim);
-  const uint32_t * tileState = reinterpret_cast<const uint32_t *>(V.tileState);
-  int16_t * rcode = V.r;
-  // the warp's queue lives in the part of its ring stage 0 that phase A leaves unused
-  uint32_t * evalQ = reinterpret_cast<uint32_t *>(ring + (size_t)(warp * NS) * WSTAGE_BYTES + A_BYTES);
-  static_assert(A_BYTES + QE * 4 <= WSTAGE_BYTES, "queue fits behind the limits");
-  int qh = 0, qe = 0;
-  unsigned nFl = 0, nCh2 = 0, nMiss = 0;
-  const unsigned ltmask = (1u << lane) - 1u;
-  // Re-evaluation pipeline of the warp, three ticks per batch of up to 32 EB queued entries so that the scan
-  // of the following tiles (and the other batch) covers both memory round trips:
-  //   start    entries -> registers; loads of the list entry and the stored residual code issued
-  //   advance  warp, limits, target pixel; gathers issued
-  //   finish   residual code, limit / code stores, histogram
-  uint32_t entL[EB], pkL[EB], entG[EB], pkG[EB];
-  float dL[EB];
-  int oldL[EB], oldG[EB], pixG[EB], valG[EB];
-  int nL = 0, nG = 0;
-  auto finish = [&]() {
-    if (nG == 0) return;
-#pragma unroll
-    for (int j = 0; j < EB; j++) {
-      const bool on = entG[j] != 0xffffffffu;
-      const int idx = (int)(entG[j] & 0x7fffffffu);
-      const int code = pixG[j] >= 0 ? valG[j] - (int)(pkG[j] >> 24) + 255 : R_CODE_INVISIBLE;
-      const bool ch = on && code != oldG[j];
-      if (ch) {
-        rcode[idx] = (int16_t)code;
-        atomicSub(&hist[oldG[j]], 1);
-        atomicAdd(&hist[code], 1);
-      }
-      if (checkMode) {
-        nCh2 += __popc(__ballot_sync(0xffffffffu, ch));
-        nMiss += __popc(__ballot_sync(0xffffffffu, ch && !(entG[j] >> 31)));
-      }
-    }
-    nG = 0;
-  };
-  auto advance = [&]() {
-    if (nL == 0) return;
-    uint2 acc[EB];
-#pragma unroll
-    for (int j = 0; j < EB; j++) {
-      acc[j] = make_uint2(0u, 0u);
-      if (entL[j] != 0xffffffffu)
-        acc[j] = *reinterpret_cast<const uint2 *>(tileState + (size_t)((entL[j] & 0x7fffffffu) / LIST_TILE) * 8 + 4);
-    }
-#pragma unroll
-    for (int j = 0; j < EB; j++) {
-      float m[4];
-      int pix = warp_point(c, V, pkL[j], dL[j], m);
-      const bool on = entL[j] != 0xffffffffu;
-      if (on && (entL[j] >> 31)) lim[entL[j] & 0x7fffffffu] = point_limits_q15(acc[j], m);
-      if (!on) pix = -1;
-      pixG[j] = pix;
-      entG[j] = entL[j];
-      pkG[j] = pkL[j];
-      oldG[j] = oldL[j];
-    }
-#pragma unroll
-    for (int j = 0; j < EB; j++) valG[j] = pixG[j] >= 0 ? (int)__ldg(I + pixG[j]) : 0;
-    nG = nL;
-    nL = 0;
-  };
-  auto start = [&](int cnt) {
-#pragma unroll
-    for (int j = 0; j < EB; j++) {
-      const bool on = j * 32 + lane < cnt;
-      entL[j] = on ? evalQ[(qh + j * 32 + lane) & (QE - 1)] : 0xffffffffu;
-    }
-#pragma unroll
-    for (int j = 0; j < EB; j++) {
-      pkL[j] = 0u; dL[j] = 1.f; oldL[j] = R_CODE_INVISIBLE;
-      if (entL[j] != 0xffffffffu) {
-        const int idx = (int)(entL[j] & 0x7fffffffu);
-        const int tile = idx / LIST_TILE, k = idx % LIST_TILE;
-        const unsigned char * tp = V.tiles + (size_t)tile * LIST_TILE_BYTES;
-        pkL[j] = reinterpret_cast<const uint32_t *>(tp + TILE_OFF_UVT)[k];
-        dL[j] = reinterpret_cast<const float *>(tp + TILE_OFF_D)[k];
-        if (!first) oldL[j] = (int)(uint16_t)rcode[idx];
-      }
-    }
-    nL = cnt;
-    qh = (qh + cnt) & (QE - 1);
-    qe -= cnt;
-    __syncwarp();
-  };
-  auto tick = [&](int cnt) {
-    finish();
-    advance();
-    if (cnt > 0) start(cnt);
-  };
-  uint2 accNext = make_uint2(0u, 0u);
-  if (nCh > 0 && p0 + warp * WCH < p1)
-    accNext = *reinterpret_cast<const uint2 *>(tileState + (size_t)((p0 + warp * WCH) / LIST_TILE) * 8 + 4);
-  for (int ch = 0; ch < nCh; ch++) {
-    const uint32_t it = item + ch;
-    const unsigned char * st = ring + (size_t)(warp * NS + it % NS) * WSTAGE_BYTES;
-    mbar_wait(&S.full[warp][it % NS], (it / NS) & 1);
-    const int t0 = p0 + ch * CH + warp * WCH;  // first entry of the warp's tile
-    if (t0 >= p1) {  // warp-uniform: nothing of this chunk belongs to the warp
-      if (lane == 0 && ch + NS < nCh) issue_chunk(S, ring, V, CHUNK_LIMITS, p0, p1, ch + NS, it + NS, warp, pol);
-      continue;
-    }
-    const uint4 la = *reinterpret_cast<const uint4 *>(st + lane * 32);
-    const uint4 lb = *reinterpret_cast<const uint4 *>(st + lane * 32 + 16);
-    __syncwarp();
-    if (lane == 0 && ch + NS < nCh) issue_chunk(S, ring, V, CHUNK_LIMITS, p0, p1, ch + NS, it + NS, warp, pol);
-    // the tile's accumulated bounds (loaded one chunk ahead), plus one per halfword for the >= test
-    const uint2 A = make_uint2(accNext.x + 0x00010001u, accNext.y + 0x00010001u);
-    if (t0 + CH < p1) accNext = *reinterpret_cast<const uint2 *>(tileState + (size_t)((t0 + CH) / LIST_TILE) * 8 + 4);
-    const uint32_t c0 = limits_clear(A, la.x, la.y), c1 = limits_clear(A, la.z, la.w);
-    const uint32_t c2 = limits_clear(A, lb.x, lb.y), c3 = limits_clear(A, lb.z, lb.w);
-    const int g0 = t0 + 4 * lane;
-    unsigned f = 0;  // which of the lane's four entries reached a limit
-    if (((c0 & c1 & c2 & c3) & 0x80008000u) != 0x80008000u)
-      f = ((c0 & 0x80008000u) != 0x80008000u ? 1u : 0u) | ((c1 & 0x80008000u) != 0x80008000u ? 2u : 0u) |
-          ((c2 & 0x80008000u) != 0x80008000u ? 4u : 0u) | ((c3 & 0x80008000u) != 0x80008000u ? 8u : 0u);
-    unsigned in = 0xfu;
-    if (t0 + LIST_TILE > p1) in = g0 + 3 < p1 ? 0xfu : (g0 < p1 ? (1u << (p1 - g0)) - 1u : 0u);  // last tile of the slice
-    f &= in;
-    const unsigned e = checkMode ? in : f;  // check mode looks at every point; only flagged ones may change
-    const int cn = __popc(e);
-    const unsigned b0 = __ballot_sync(0xffffffffu, cn & 1), b1 = __ballot_sync(0xffffffffu, cn & 2),
-                   b2 = __ballot_sync(0xffffffffu, cn & 4);
-    if (b0 | b1 | b2) {
-      if (e) {
-        int pos = qh + qe + __popc(b0 & ltmask) + 2 * __popc(b1 & ltmask) + 4 * __popc(b2 & ltmask);
-#pragma unroll
-        for (int q = 0; q < 4; q++)
-          if (e & (1u << q)) evalQ[(pos++) & (QE - 1)] = (uint32_t)(g0 + q) | ((f >> q) << 31);
-      }
-      const int tot = __popc(b0) + 2 * __popc(b1) + 4 * __popc(b2);
-      qe += tot;
-      if (checkMode) nFl += __popc(__ballot_sync(0xffffffffu, f & 1)) + __popc(__ballot_sync(0xffffffffu, f & 2)) +
-                            __popc(__ballot_sync(0xffffffffu, f & 4)) + __popc(__ballot_sync(0xffffffffu, f & 8));
-      else nFl += tot;
-      __syncwarp();
-      if (qe >= 32 * EB) tick(32 * EB);
-    }
-  }
-  while (qe > 0) tick(min(qe, 32 * EB));
-  tick(0);
-  tick(0);
-  if (lane == 0) atomicAdd(&S.cnt[0], (unsigned long long)nFl);
-  if (checkMode && lane == 0) {
-    atomicAdd(&S.cnt[1], (unsigned long long)nCh2);
-    atomicAdd(&S.cnt[2], (unsigned long long)nMiss);
-  }
-}
-
-template <bool BOUNDED>
 __global__ void __launch_bounds__(GT, CTAS_PER_SM) gn_level_kernel(
   JobState * __restrict__ jobs, ViewState * __restrict__ views, SolverParams p, int level, int maxEvals,
-  double * __restrict__ trace, size_t traceJobStride, double * __restrict__ viewSums, int job0, int checkMode)
+  double * __restrict__ trace, size_t traceJobStride, double * __restrict__ viewSums, int job0)
 {
   cg::cluster_group cluster = cg::this_cluster();
   const unsigned C = cluster.num_blocks(), rank = cluster.block_rank();
@@ -577,17 +283,12 @@ __global__ void __launch_bounds__(GT, CTAS_PER_SM) gn_level_kernel(
   };
   long long ts = 0;  // sub-laps of the scale section (do not reset the main lap clock)
   auto sublap = [&](int slot) {
-    if (!BOUNDED && tid == 0) {
+    if (tid == 0) {
       const long long now = clock64();
       S.J.clk[level][slot] += now - ts;
       ts = now;
     }
   };
-  if constexpr (BOUNDED) {
-    if (tid < 3) S.cnt[tid] = 0ull;
-    bounded_prologue(Vs[0], C, rank);
-    __syncthreads();
-  }
   for (;;) {
     const int pb = evals & 1;
     for (int k = 0; k < K; k++) {
@@ -595,25 +296,12 @@ __global__ void __launch_bounds__(GT, CTAS_PER_SM) gn_level_kernel(
       int p0, p1;
       slice_of(V.nIp, C, rank, p0, p1);
       const int nCh = (p1 - p0 + CH - 1) / CH;
-      // bounded variant: ONE persistent histogram, updated by the points whose residual changed (bin 511 collects
-      // the not-visible codes and is never read)
-      int * hist = S.hist[BOUNDED ? 0 : hb];
-      if (!BOUNDED || evals == 0) {
+      int * hist = S.hist[hb];
 #pragma unroll
-        for (int j = 0; j < BPT; j++) hist[tid + j * GT] = 0;
-      }
+      for (int j = 0; j < BPT; j++) hist[tid + j * GT] = 0;
       __syncthreads();
       // ---------------------------------------------------------------- phase A
-      bool denseA = true;  // the first evaluation of a level looks at every entry: the dense phase A (which also
-                           // stores every point's limits in the bounded variant)
-      if constexpr (BOUNDED) {
-        if (evals > 0) {
-        denseA = false;
-        bounded_phase_a(S, ring, V, hist, p0, p1, nCh, item, pol, checkMode);
-        item += nCh;
-        }
-      }
-      if (denseA) {
+      {
         WarpConsts c;
         c.r00 = V.rI[0]; c.r01 = V.rI[1]; c.r02 = V.rI[2]; c.r10 = V.rI[3]; c.r11 = V.rI[4]; c.r12 = V.rI[5];
         c.r20 = V.rI[6]; c.r21 = V.rI[7]; c.r22 = V.rI[8];
@@ -700,7 +388,7 @@ __global__ void __launch_bounds__(GT, CTAS_PER_SM) gn_level_kernel(
       __syncwarp();
       if (lane == 0)
         for (int c = 0; c < min(NS, nCh); c++) issue_chunk(S, ring, V, CHUNK_C, p0, p1, c, item + c, warp, pol);
-      lap(BOUNDED && !checkMode && evals == 0 ? 8 : 0);
+      lap(0);
       // ---------------------------------------------------------------- scale + weight table
       // The leading CTA sums the cluster's histograms, runs the scaler and publishes {scale, offset} into every
       // CTA's shared memory; the others only wait (they would repeat the same arithmetic, and the kernel is bound
@@ -723,7 +411,7 @@ __global__ void __launch_bounds__(GT, CTAS_PER_SM) gn_level_kernel(
             for (int j = 0; j < BPT; j++) a[j] += h[tid + j * GT];
           }
           // the other histogram buffer is idle (its last remote readers passed a cluster barrier since)
-          int * tot = S.hist[BOUNDED ? 1 : (hb ^ 1)];
+          int * tot = S.hist[hb ^ 1];
 #pragma unroll
           for (int j = 0; j < BPT; j++) tot[tid + j * GT] = tid + j * GT == R_CODE_INVISIBLE ? 0 : a[j];
           __syncthreads();
@@ -742,7 +430,7 @@ __global__ void __launch_bounds__(GT, CTAS_PER_SM) gn_level_kernel(
         if (rank == 0) chi2View = block_sum(c2, S.red);  // contains the barrier that publishes the table
         else __syncthreads();
         sublap(9);
-        if (!BOUNDED) hb ^= 1;
+        hb ^= 1;
         lap(2);
       }
       // ---------------------------------------------------------------- phase C
@@ -760,20 +448,18 @@ __global__ void __launch_bounds__(GT, CTAS_PER_SM) gn_level_kernel(
             if (lane == 0 && ch + NS < nCh) issue_chunk(S, ring, V, CHUNK_C, p0, p1, ch + NS, item + NS, warp, pol);
             continue;
           }
-          const uint4 pk4 = *reinterpret_cast<const uint4 *>(st + C_OFF_UVT + lane * 16);
-          const uint4 gg4 = *reinterpret_cast<const uint4 *>(st + C_OFF_G + lane * 16);
-          const double2 za = *reinterpret_cast<const double2 *>(st + C_OFF_ZI + lane * 32);
-          const double2 zb = *reinterpret_cast<const double2 *>(st + C_OFF_ZI + lane * 32 + 16);
-          const uint2 packed = *reinterpret_cast<const uint2 *>(st + C_OFF_R + lane * 8);
+          // lane l takes the tile's records l, l + 32, l + 64, l + 96 (16-byte records: conflict-free 128-bit loads)
+          uint4 rc[4];
+          int rq[4];
+#pragma unroll
+          for (int q = 0; q < 4; q++) {
+            rc[q] = *reinterpret_cast<const uint4 *>(st + (q * 32 + lane) * 16);
+            // residual codes: r + 255, or 511 when not visible.  Entries past the end of the list (padding of the last
+            // tile) may hold anything: masked to a valid table index, and their Jacobian is exactly zero (lists.cu)
+            rq[q] = (int)(*reinterpret_cast<const uint16_t *>(st + C_OFF_R + (q * 32 + lane) * 2)) & 0x1ff;
+          }
           __syncwarp();
           if (lane == 0 && ch + NS < nCh) issue_chunk(S, ring, V, CHUNK_C, p0, p1, ch + NS, item + NS, warp, pol);
-          const uint32_t pk[4] = {pk4.x, pk4.y, pk4.z, pk4.w};
-          const uint32_t gg[4] = {gg4.x, gg4.y, gg4.z, gg4.w};
-          const double zz[4] = {za.x, za.y, zb.x, zb.y};
-          // residual codes: r + 255, or 511 when not visible.  Entries past the end of the list (padding of the last
-          // tile) may hold anything: masked to a valid table index, and their Jacobian is exactly zero (lists.cu)
-          const int rq[4] = {(int)(packed.x & 0x1ff), (int)((packed.x >> 16) & 0x1ff), (int)(packed.y & 0x1ff),
-                             (int)((packed.y >> 16) & 0x1ff)};
 #pragma unroll
           for (int q = 0; q < 4; q++) {
             // branch-free: a point that is not visible gets weight 0, a padding entry has a zero Jacobian; both add
@@ -782,15 +468,16 @@ __global__ void __launch_bounds__(GT, CTAS_PER_SM) gn_level_kernel(
             // (InverseCompositional.cpp:79-80), in normalised coordinates xn = x/z, yn = y/z.
             // Integer -> double through the 2^52 trick (one full-rate add instead of a quarter-rate conversion):
             // the low word of 2^52 + k is k, and the gradients are biased by 2^15 to make them non-negative.
-            const uint32_t gb = gg[q] ^ 0x80008000u;
-            const double u = __hiloint2double(0x43300000, (int)(pk[q] & 0xfff)) - 4503599627370496.0;
-            const double v = __hiloint2double(0x43300000, (int)((pk[q] >> 12) & 0xfff)) - 4503599627370496.0;
+            const uint32_t pk = rc[q].x;
+            const uint32_t gb = rc[q].y ^ 0x80008000u;
+            const double u = __hiloint2double(0x43300000, (int)(pk & 0xfff)) - 4503599627370496.0;
+            const double v = __hiloint2double(0x43300000, (int)((pk >> 12) & 0xfff)) - 4503599627370496.0;
             const double2 swr = lut[rq[q]];  // {sqrt(w), sqrt(w) r}
             const double sw = swr.x, swr_ = swr.y;
             // sqrt(w) dIx fx, sqrt(w) dIy fy: every Jacobian component below carries the factor sqrt(w)
             const double a = (__hiloint2double(0x43300000, (int)(gb & 0xffff)) - 4503599627403264.0) * fxJ * sw;
             const double b = (__hiloint2double(0x43300000, (int)(gb >> 16)) - 4503599627403264.0) * fyJ * sw;
-            const double zi = zz[q];
+            const double zi = __hiloint2double((int)rc[q].w, (int)rc[q].z);
             const double xn = fma(ifx, u, kx), yn = fma(ify, v, ky);
             const double cc = fma(a, xn, b * yn);
             double J[6];
@@ -822,7 +509,7 @@ __global__ void __launch_bounds__(GT, CTAS_PER_SM) gn_level_kernel(
         slice_of(Vn.nIp, C, rank, q0, q1);
         const int nChN = (q1 - q0 + CH - 1) / CH;
         if (lane == 0)  // the warp's own ring is free as soon as the warp leaves phase C
-          for (int c = 0; c < min(NS, nChN); c++) issue_chunk(S, ring, Vn, BOUNDED ? CHUNK_LIMITS : CHUNK_A, q0, q1, c, item + c, warp, pol);
+          for (int c = 0; c < min(NS, nChN); c++) issue_chunk(S, ring, Vn, CHUNK_A, q0, q1, c, item + c, warp, pol);
       }
       // fixed-order block reduction: lanes (xor tree), then warps in order
 #pragma unroll
@@ -860,42 +547,10 @@ __global__ void __launch_bounds__(GT, CTAS_PER_SM) gn_level_kernel(
       S.J.evals[level]++;
       S.J.pointIters += (unsigned long long)S.J.totalPoints;
     }
-    if constexpr (BOUNDED) {  // the pose before the step, for the motion bounds
-      if (tid >= 32 && tid < 41) S.stp.Ro[tid - 32] = (float)Vs[0].R[tid - 32];
-      if (tid >= 41 && tid < 44) S.stp.to[tid - 41] = (float)Vs[0].t[tid - 41];
-    }
     solver_step_block(S.J, Vs, sums, S.X, p, level, (trace && rank == 0) ? trace + (size_t)job * traceJobStride : nullptr,
                   evals >= maxEvals);
     lap(6);
     if (!S.J.active) break;
-    if constexpr (BOUNDED) {
-      // what the step did (Warp.cpp:153-157: se3 <- se3 * exp(-dx)), then the directional motion bounds of this
-      // CTA's tiles, accumulated
-      ViewState & V = Vs[0];
-      if (tid == 0) {
-        double Rinc[9];
-        quat_to_R(S.X.inc.q, Rinc);
-        for (int i = 0; i < 9; i++) S.stp.E[i] = (float)(Rinc[i] - ((i % 4 == 0) ? 1.0 : 0.0));
-        for (int i = 0; i < 3; i++) S.stp.dt[i] = (float)S.X.inc.t[i];
-        S.stp.ifx = (float)V.ifx; S.stp.kx = (float)V.kx; S.stp.ify = (float)V.ify; S.stp.ky = (float)V.ky;
-        S.stp.fx = (float)V.fx; S.stp.fy = (float)V.fy;
-      }
-      __syncthreads();
-      int p0, p1;
-      slice_of(V.nIp, C, rank, p0, p1);
-      for (int t = p0 / LIST_TILE + tid; t * LIST_TILE < p1; t += GT) {
-        float4 * tsp = reinterpret_cast<float4 *>(V.tileState + (size_t)t * 8);
-        const float4 a = tsp[0];
-        uint2 * accp = reinterpret_cast<uint2 *>(tsp + 1);
-        const uint2 acc = *accp;
-        const unsigned uw = __float_as_uint(a.x), vw = __float_as_uint(a.y);
-        const float4 b = tile_motion_bound(S.stp, (float)(uw & 0xffff), (float)(uw >> 16), (float)(vw & 0xffff),
-                                           (float)(vw >> 16), a.z, a.w);
-        *accp = make_uint2(sat_add_q15x2(acc.x, bound_q15(b.x), bound_q15(b.y)), sat_add_q15x2(acc.y, bound_q15(b.z), bound_q15(b.w)));
-      }
-      __syncthreads();
-      lap(6);
-    }
   }
   // drain the speculative prologue of the phase A that will not run: no bulk copy may be in flight at exit
   {
@@ -905,16 +560,6 @@ __global__ void __launch_bounds__(GT, CTAS_PER_SM) gn_level_kernel(
     for (int c = 0; c < min(NS, nCh); c++) mbar_wait(&S.full[warp][(item + c) % NS], ((item + c) / NS) & 1);
   }
   cluster.sync();  // nobody leaves while its shared memory may still be read remotely
-  if constexpr (BOUNDED) {
-    {  // flagged / changed / missed points of the whole cluster -> statistics slots 7..9 of the level
-      if (rank == 0 && tid < (checkMode ? 3 : 1)) {
-        unsigned long long v = 0ull;
-        for (unsigned rk = 0; rk < C; rk++) v += cluster.map_shared_rank(&S.cnt[tid], rk)[0];
-        S.J.clk[level][7 + tid] += (long long)v;
-      }
-      cluster.sync();
-    }
-  }
   if (rank == 0) {
     block_copy(jobs + job, &S.J);
     for (int k = 0; k < K; k++) block_copy(views + S.J.view0 + k, &Vs[k]);
@@ -923,16 +568,17 @@ __global__ void __launch_bounds__(GT, CTAS_PER_SM) gn_level_kernel(
 
 size_t gn_level_static_smem() { return sizeof(LevelShared); }
 
-template <bool BOUNDED>
-static cudaError_t launch_gn_level_t(
+// The dense level kernel: any number of keyframes per job, every loss / scaler, Gauss-Newton or Levenberg-Marquardt.
+cudaError_t launch_gn_level(
   JobState * jobs, ViewState * views, int job0, int nJobs, int maxViewsPerJob, int clusterSize, SolverParams p, int level,
-  int maxEvals, double * trace, size_t traceJobStride, double * viewSums, int checkMode, cudaStream_t s)
+  int maxEvals, double * trace, size_t traceJobStride, double * viewSums, cudaStream_t s)
 {
+  if (nJobs <= 0) return cudaSuccess;
   const size_t dyn = level_dyn_smem(maxViewsPerJob);
-  cudaError_t e = cudaFuncSetAttribute(gn_level_kernel<BOUNDED>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
+  cudaError_t e = cudaFuncSetAttribute(gn_level_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
   if (e != cudaSuccess) return e;
   if (clusterSize > 8) {
-    e = cudaFuncSetAttribute(gn_level_kernel<BOUNDED>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+    e = cudaFuncSetAttribute(gn_level_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
     if (e != cudaSuccess) return e;
   }
   cudaLaunchConfig_t cfg = {};
@@ -948,37 +594,21 @@ static cudaError_t launch_gn_level_t(
   if (clusterSize > 8) {
     // 16-CTA clusters need a GPC with 16 SMs that can each take a CTA of this size: asked once per shared-memory size;
     // a device (or partition) that cannot co-schedule them falls back to the portable maximum
-    static int ok16[2] = {-1, -1};
-    static size_t dyn16[2] = {0, 0};
-    const int v = BOUNDED ? 1 : 0;
-    if (ok16[v] < 0 || dyn16[v] != dyn) {
+    static int ok16 = -1;
+    static size_t dyn16 = 0;
+    if (ok16 < 0 || dyn16 != dyn) {
       cfg.gridDim = dim3(16, 1, 1);
       at[0].val.clusterDim.x = 16;
       int n = 0;
-      const cudaError_t q = cudaOccupancyMaxActiveClusters(&n, gn_level_kernel<BOUNDED>, &cfg);
+      const cudaError_t q = cudaOccupancyMaxActiveClusters(&n, gn_level_kernel, &cfg);
       if (q != cudaSuccess) cudaGetLastError();
-      ok16[v] = (q == cudaSuccess && n >= 1) ? 1 : 0;
-      dyn16[v] = dyn;
+      ok16 = (q == cudaSuccess && n >= 1) ? 1 : 0;
+      dyn16 = dyn;
     }
-    if (!ok16[v]) clusterSize = 8;
+    if (!ok16) clusterSize = 8;
   }
   cfg.gridDim = dim3((unsigned)nJobs * clusterSize, 1, 1);
   at[0].val.clusterDim.x = clusterSize;
-  return cudaLaunchKernelEx(&cfg, gn_level_kernel<BOUNDED>, jobs, views, p, level, maxEvals, trace, traceJobStride, viewSums,
-                            job0, checkMode);
-}
-
-// bounded: the variant whose phase A re-evaluates only the points whose sampled pixel can have changed (bounds.cuh);
-// one keyframe per job, Gauss-Newton.  checkMode (tests): every point is re-evaluated and missed changes are counted.
-cudaError_t launch_gn_level(
-  JobState * jobs, ViewState * views, int job0, int nJobs, int maxViewsPerJob, int clusterSize, SolverParams p, int level,
-  int maxEvals, double * trace, size_t traceJobStride, double * viewSums, cudaStream_t s, bool bounded, int checkMode)
-{
-  if (nJobs <= 0) return cudaSuccess;
-  if (bounded)
-    return launch_gn_level_t<true>(jobs, views, job0, nJobs, maxViewsPerJob, clusterSize, p, level, maxEvals, trace,
-                                   traceJobStride, viewSums, checkMode, s);
-  return launch_gn_level_t<false>(jobs, views, job0, nJobs, maxViewsPerJob, clusterSize, p, level, maxEvals, trace,
-                                  traceJobStride, viewSums, 0, s);
+  return cudaLaunchKernelEx(&cfg, gn_level_kernel, jobs, views, p, level, maxEvals, trace, traceJobStride, viewSums, job0);
 }
 }  // namespace vb

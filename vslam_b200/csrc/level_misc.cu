@@ -51,6 +51,7 @@ __global__ void level_setup_kernel(
   V.fx32 = (float)V.fx;
   V.fy32 = (float)V.fy;
   V.nIp = 0;
+  for (int i = 0; i < JSTAT; i++) V.jstat[i] = 0u;
   V.scale = 1.0;
   V.offset = 0.0;
   V.se3 = se3_mul(J.pose, se3_inv(V.poseRef));
@@ -123,8 +124,7 @@ __global__ void scatter_rcode_kernel2(const ViewState * __restrict__ views, int 
 {
   const ViewState & V = views[view];
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < V.nIp; i += gridDim.x * blockDim.x) {
-    const uint32_t pk =
-      reinterpret_cast<const uint32_t *>(V.tiles + (size_t)(i / LIST_TILE) * LIST_TILE_BYTES + TILE_OFF_UVT)[i % LIST_TILE];
+    const uint32_t pk = V.rec[i].uvt;
     const int code = V.r[i];
     plane[(size_t)((pk >> 12) & 0xfff) * V.W + (pk & 0xfff)] = code == R_CODE_INVISIBLE ? R_INVISIBLE : (int16_t)(code - 255);
   }

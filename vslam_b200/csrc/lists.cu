@@ -92,17 +92,20 @@ __global__ void __launch_bounds__(256) list_scan_kernel(
     const int j = o % LIST_TILE;
     reinterpret_cast<float *>(tile + TILE_OFF_D)[j] = 1.f;
     reinterpret_cast<uint32_t *>(tile + TILE_OFF_UVT)[j] = 0u;
-    reinterpret_cast<uint32_t *>(tile + TILE_OFF_G)[j] = 0u;
-    reinterpret_cast<double *>(tile + TILE_OFF_ZI)[j] = 0.0;
+    ListRec z;
+    z.uvt = 0u;
+    z.g = 0u;
+    z.zi = 0.0;
+    V.rec[o] = z;
   }
 }
 
 __global__ void __launch_bounds__(LTHREADS) list_write_kernel(
-  const FrameDev * __restrict__ frames, const ViewState * __restrict__ views, const JobState * __restrict__ jobs,
+  const FrameDev * __restrict__ frames, ViewState * __restrict__ views, const JobState * __restrict__ jobs,
   int level, double minGradient2, const int * __restrict__ chunkOffsets, int maxChunks, int view0)
 {
   const int vi = view0 + blockIdx.y;
-  const ViewState & V = views[vi];
+  ViewState & V = views[vi];
   const int npx = V.W * V.H;
   const int base = blockIdx.x * LCHUNK;
   if (base >= npx) return;
@@ -110,8 +113,16 @@ __global__ void __launch_bounds__(LTHREADS) list_write_kernel(
   const int multi = jobs[V.job].multi;
   const int W = V.W;
   __shared__ int wsum[LTHREADS / 32];
+  __shared__ unsigned jmax[JSTAT];
+  if (threadIdx.x < JSTAT) jmax[threadIdx.x] = 0u;
   int running = chunkOffsets[vi * maxChunks + blockIdx.x];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  // bounds of the Jacobian components J_i = fxJ dIx P_i + fyJ dIy Q_i over the list (the moments kernel derives its
+  // fixed-point scales from them): max |dIx P_i|, max |dIy Q_i| in fp32
+  const float ifx = (float)V.ifx, ify = (float)V.ify, kx = (float)V.kx, ky = (float)V.ky;
+  float jm[JSTAT];
+#pragma unroll
+  for (int i = 0; i < JSTAT; i++) jm[i] = 0.f;
   for (int k = 0; k < LPER; k++) {
     const int i = base + k * LTHREADS + threadIdx.x;
     float d = 0.f;
@@ -132,14 +143,37 @@ __global__ void __launch_bounds__(LTHREADS) list_write_kernel(
       const int v = i / W, u = i - v * W;
       unsigned char * tile = V.tiles + (size_t)(o / LIST_TILE) * LIST_TILE_BYTES;
       const int j = o % LIST_TILE;
+      const uint32_t uvt = (uint32_t)u | ((uint32_t)v << 12) | ((uint32_t)f.I[level][i] << 24);
       reinterpret_cast<float *>(tile + TILE_OFF_D)[j] = d;
-      reinterpret_cast<uint32_t *>(tile + TILE_OFF_UVT)[j] = (uint32_t)u | ((uint32_t)v << 12) | ((uint32_t)f.I[level][i] << 24);
-      reinterpret_cast<uint32_t *>(tile + TILE_OFF_G)[j] = g;
-      reinterpret_cast<double *>(tile + TILE_OFF_ZI)[j] = 1.0 / (double)d;  // Warp.cpp:170
+      reinterpret_cast<uint32_t *>(tile + TILE_OFF_UVT)[j] = uvt;
+      ListRec rc;
+      rc.uvt = uvt;
+      rc.g = g;
+      rc.zi = 1.0 / (double)d;  // Warp.cpp:170
+      V.rec[o] = rc;
+      const float ax = fabsf((float)(int16_t)(g & 0xffff)), ay = fabsf((float)(int16_t)(g >> 16));
+      const float xn = fabsf(fmaf(ifx, (float)u, kx)), yn = fabsf(fmaf(ify, (float)v, ky)), zi = 1.f / d;
+      jm[0] = fmaxf(jm[0], ax * zi);
+      jm[2] = fmaxf(jm[2], ax * xn * zi);
+      jm[3] = fmaxf(jm[3], ax * xn * yn);
+      jm[4] = fmaxf(jm[4], ax * fmaf(xn, xn, 1.f));
+      jm[5] = fmaxf(jm[5], ax * yn);
+      jm[7] = fmaxf(jm[7], ay * zi);
+      jm[8] = fmaxf(jm[8], ay * yn * zi);
+      jm[9] = fmaxf(jm[9], ay * fmaf(yn, yn, 1.f));
+      jm[10] = fmaxf(jm[10], ay * xn * yn);
+      jm[11] = fmaxf(jm[11], ay * xn);
     }
     running += tot;
     __syncthreads();
   }
+#pragma unroll
+  for (int i = 0; i < JSTAT; i++) {
+    const unsigned m = __reduce_max_sync(0xffffffffu, __float_as_uint(jm[i]));  // non-negative floats order like their bits
+    if (lane == 0 && m) atomicMax(&jmax[i], m);
+  }
+  __syncthreads();
+  if (threadIdx.x < JSTAT && jmax[threadIdx.x]) atomicMax(&V.jstat[threadIdx.x], jmax[threadIdx.x]);
 }
 
 void launch_build_lists(const FrameDev * frames, ViewState * views, const JobState * jobs, int view0, int nViews, int level,
