@@ -42,6 +42,29 @@ def level_kernel(request, monkeypatch):
     return request.param
 
 
+def test_level_kernels_agree_and_repeat_on_a_multi_wave_batch(capi, synth):
+    """512 small jobs (more CTAs than the device holds at once, so SMs are shared between jobs in different phases): the
+    moment kernel and the dense kernel give the same iteration counts and poses, and the moment kernel is bit-identical
+    run to run.  (This is the case that exposed a stage refill overtaking the loads of the stage: see start_chunk.)"""
+    F, W, H = 513, 160, 120
+    cam = synth.cam_for(W, H)
+    gray, depth, _ = synth.make_sequence(F, W, H, seed=1234, cam=cam)
+    ident = np.array([0, 0, 0, 1, 0, 0, 0.0])
+    jobs = [dict(to=i + 1, to_pose=ident, frm=[i], from_poses=ident, multi=False) for i in range(F - 1)]
+    out = {}
+    for name, k, cl in (("dense", capi.KERNEL_DENSE, 0), ("moments", capi.KERNEL_MOMENTS, 1)):
+        c = capi.Context(capi.make_config(level_kernel=k, cluster_size=cl))
+        try:
+            c.upload(np.arange(F), gray, depth, cam, 1)
+            out[name] = [c.align(jobs) for _ in range(2)]
+        finally:
+            c.close()
+    for a, b, b2 in zip(out["dense"][0], out["moments"][0], out["moments"][1]):
+        assert list(a["iters"]) == list(b["iters"]) and list(a["stop"]) == list(b["stop"])
+        assert np.abs(a["pose"] - b["pose"]).max() < 1e-9
+        assert np.array_equal(b["pose"], b2["pose"])
+
+
 def _kernel_was_used(ctx, level_kernel, applicable=True):
     st = ctx.stats()
     m, d = st["moment_launches"], st["dense_launches"]
@@ -282,19 +305,21 @@ def test_batch_of_pairs_matches_oracle(ctx, capi, oracle, synth, level_kernel):
         assert dt < 0.01 and dr < 0.01, k
 
 
-def test_moment_kernel_stays_exact_under_many_changes(capi, oracle, synth):
+@pytest.mark.parametrize("cluster", [0, 1, 2, 4])
+def test_moment_kernel_stays_exact_under_many_changes(capi, oracle, synth, cluster):
     """The moment-based kernel moves the moments of every point whose residual changed from the old to the new cell;
     the fixed-point cells must stay exactly what a fresh build would give.  Pairs with a deliberately bad initial guess
     (large per-level motion: many points change per iteration), depth holes, every pyramid level: every iteration's normal
     equations against the oracle evaluated at the device's own iterate to 1e-9 (measured ~1e-14), and the count of moved
-    points reported by the kernel is non-zero."""
+    points reported by the kernel is non-zero.  cluster: CTAs per job (0 = the automatic choice, which is the 16-CTA
+    latency mode for this small batch; 1, 2, 4 are the slice sizes of the throughput batches)."""
     O, A = oracle, capi
     n, L = 4, 4
     pairs = [_pair(synth, 640, 480, 4321 + k, holes=(40 if k % 2 else 0)) for k in range(n)]
     gray = np.stack([x for p in pairs for x in (p["gray0"], p["gray1"])])
     depth = np.stack([x for p in pairs for x in (p["depth0"], p["depth1"])])
     kw = dict(max_iterations=40)
-    ctx = A.Context(A.make_config(level_kernel=A.KERNEL_MOMENTS, **kw))
+    ctx = A.Context(A.make_config(level_kernel=A.KERNEL_MOMENTS, cluster_size=cluster, **kw))
     try:
         ctx.upload(np.arange(2 * n), gray, depth, pairs[0]["cam"], L)
         bad = O.se3_exp(np.array([0.01, -0.008, 0.012, 0.004, -0.003, 0.005]))

@@ -331,8 +331,11 @@ __global__ void __launch_bounds__(GT, CTAS_PER_SM) gn_level_kernel(
           }
           const uint4 pk4 = *reinterpret_cast<const uint4 *>(st + A_OFF_UVT + lane * 16);
           const float4 dd4 = *reinterpret_cast<const float4 *>(st + A_OFF_D + lane * 16);
+          // the refill (an async-proxy write into the stage just read) is made to depend on the loaded registers: zero
+          // is 0, but the hardware has to wait for both loads to form it (see gn_mom.cu, start_chunk)
+          const int zero = (int)((pk4.x ^ __float_as_uint(dd4.x)) & (uint32_t)(p1 >> 31));
           __syncwarp();
-          if (lane == 0 && ch + NS < nCh) issue_chunk(S, ring, V, CHUNK_A, p0, p1, ch + NS, it + NS, warp, pol);
+          if (lane == 0 && ch + NS < nCh) issue_chunk(S, ring, V, CHUNK_A, p0, p1 + zero, ch + NS, it + NS, warp, pol);
           const uint32_t pk[4] = {pk4.x, pk4.y, pk4.z, pk4.w};
           const float dd[4] = {dd4.x, dd4.y, dd4.z, dd4.w};
           bool good[4];
@@ -458,8 +461,9 @@ __global__ void __launch_bounds__(GT, CTAS_PER_SM) gn_level_kernel(
             // tile) may hold anything: masked to a valid table index, and their Jacobian is exactly zero (lists.cu)
             rq[q] = (int)(*reinterpret_cast<const uint16_t *>(st + C_OFF_R + (q * 32 + lane) * 2)) & 0x1ff;
           }
+          const int zero = (int)((rc[0].x ^ rc[1].x ^ rc[2].x ^ rc[3].x ^ (uint32_t)(rq[0] ^ rq[1] ^ rq[2] ^ rq[3])) & (uint32_t)(p1 >> 31));
           __syncwarp();
-          if (lane == 0 && ch + NS < nCh) issue_chunk(S, ring, V, CHUNK_C, p0, p1, ch + NS, item + NS, warp, pol);
+          if (lane == 0 && ch + NS < nCh) issue_chunk(S, ring, V, CHUNK_C, p0, p1 + zero, ch + NS, item + NS, warp, pol);
 #pragma unroll
           for (int q = 0; q < 4; q++) {
             // branch-free: a point that is not visible gets weight 0, a padding entry has a zero Jacobian; both add

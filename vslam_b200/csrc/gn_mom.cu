@@ -166,83 +166,112 @@ __device__ __forceinline__ void jac_row(const JacConsts & c, const uint4 rc, dou
   J[5] = fma(b, xn, -a * yn) * c.s5;
 }
 
-// lane 0 streams tile `start / LIST_TILE` of the list (and, from the second evaluation on, its residual codes) into
-// stage (item % NS) of the warp's private ring
-__device__ __forceinline__ void issue_tile(
-  Shared & S, unsigned char * ring, const ViewState & V, bool withCodes, int p0, int p1, int c, uint32_t item, int warp,
-  uint64_t pol)
+// A warp's stream through its slice of the list: tile c of the warp is entries [w0 + c CH, w0 + c CH + 128) with
+// w0 = p0 + warp * 128; lane 0 brings it (and, from the second evaluation on, its residual codes) into stage
+// (item + c) % NS of the warp's private ring.  A warp refills a stage right after it has copied it into registers, so no
+// warp ever waits for another one (no "empty" barriers, no producer thread that can fall behind).
+struct Stream
 {
-  const int start = p0 + c * CH + warp * LIST_TILE;
-  uint64_t * bar = &S.full[warp][item % NS];
-  if (start >= p1) {  // nothing of the chunk belongs to this warp: keep the barrier's phase in step with `item`
+  const unsigned char * tiles;  // first tile of the warp
+  const int16_t * codes;        // its residual codes
+  unsigned char * ring;         // the warp's NS stages
+  uint64_t * bars;              // the warp's NS barriers
+  int w0, p1;
+};
+__device__ __forceinline__ Stream make_stream(Shared & S, unsigned char * ring, const ViewState & V, int p0, int p1, int warp)
+{
+  Stream t;
+  t.w0 = p0 + warp * LIST_TILE;
+  t.p1 = p1;
+  t.tiles = V.tiles + (size_t)(t.w0 / LIST_TILE) * LIST_TILE_BYTES;
+  t.codes = V.r + t.w0;
+  t.ring = ring + (size_t)warp * NS * ST_BYTES;
+  t.bars = &S.full[warp][0];
+  return t;
+}
+__device__ __forceinline__ void issue_tile(const Stream & t, bool withCodes, int c, int stage, uint64_t pol)
+{
+  uint64_t * bar = t.bars + stage;
+  if (t.w0 + c * CH >= t.p1) {  // nothing of the chunk belongs to this warp: keep the barrier's phase in step
     mbar_arrive(bar);
     return;
   }
-  unsigned char * st = ring + (size_t)(warp * NS + item % NS) * ST_BYTES;
+  unsigned char * st = t.ring + stage * ST_BYTES;
   mbar_expect_tx(bar, withCodes ? ST_TILE_BYTES + ST_R_BYTES : ST_TILE_BYTES);
-  bulk_g2s_stream(st, V.tiles + (size_t)(start / LIST_TILE) * LIST_TILE_BYTES, ST_TILE_BYTES, bar, pol);
-  if (withCodes) bulk_g2s(st + ST_R, V.r + start, ST_R_BYTES, bar);
+  bulk_g2s_stream(st, t.tiles + (size_t)c * (MW * LIST_TILE_BYTES), ST_TILE_BYTES, bar, pol);
+  if (withCodes) bulk_g2s(st + ST_R, t.codes + (size_t)c * CH, ST_R_BYTES, bar);
 }
 
+// What a chunk leaves in flight between its two pipeline halves: the four gathered target pixels (preset to 256 + T so
+// that a point that is not visible - no gather - comes out as the not-visible code 511 without a select), the four
+// template values and the four stored residual codes.
 struct Pend
 {
-  int g, pix[4], val[4];
-  uint32_t T[4];
-  uint2 old;  // the four stored residual codes
+  int val[4];
+  uint32_t T;  // four bytes
+  uint2 old;
 };
 
 // first half of a chunk's pipeline: list entries out of the ring, warp, gathers issued
 template <bool FIRST>
 __device__ __forceinline__ void start_chunk(
-  Shared & S, unsigned char * ring, const ViewState & V, const WarpConsts & c, const uint8_t * __restrict__ I, int p0, int p1,
-  int nCh, int ch, uint32_t item, int tid, uint64_t pol, Pend & P)
+  const Stream & t, const ViewState & V, const WarpConsts & c, const uint8_t * __restrict__ I, int nCh, int ch, int stage,
+  uint32_t parity, int lane, uint64_t pol, Pend & P)
 {
-  const int lane = tid & 31, warp = tid >> 5;
-  const uint32_t it = item + ch;
-  P.g = p0 + ch * CH + 4 * tid;
-  const unsigned char * st = ring + (size_t)(warp * NS + it % NS) * ST_BYTES;
-  mbar_wait(&S.full[warp][it % NS], (it / NS) & 1);
-  if (p0 + ch * CH + warp * LIST_TILE >= p1) {  // warp-uniform: nothing of this chunk belongs to the warp
-    if (lane == 0 && ch + NS < nCh) issue_tile(S, ring, V, !FIRST, p0, p1, ch + NS, it + NS, warp, pol);
+  const unsigned char * st = t.ring + stage * ST_BYTES;
+  mbar_wait(t.bars + stage, parity);
+  const int g = t.w0 + ch * CH + 4 * lane;
+  if (t.w0 + ch * CH >= t.p1) {  // warp-uniform: nothing of this chunk belongs to the warp
+    if (lane == 0 && ch + NS < nCh) issue_tile(t, !FIRST, ch + NS, stage, pol);
 #pragma unroll
-    for (int q = 0; q < 4; q++) P.pix[q] = -1, P.val[q] = 0, P.T[q] = 0;
+    for (int q = 0; q < 4; q++) P.val[q] = 256;
+    P.T = 0u;
     P.old = make_uint2(R_CODE_INVISIBLE * 0x10001u, R_CODE_INVISIBLE * 0x10001u);
     return;
   }
   const uint4 pk4 = *reinterpret_cast<const uint4 *>(st + ST_UVT + lane * 16);
   const float4 dd4 = *reinterpret_cast<const float4 *>(st + ST_D + lane * 16);
   if (!FIRST) P.old = *reinterpret_cast<const uint2 *>(st + ST_R + lane * 8);
+  // The refill below is an async-proxy write into the stage these generic-proxy loads read, and nothing orders the two
+  // proxies: the loads can sit in the shared-memory queue behind another warp's conflicted atomics for longer than the
+  // bulk copy takes to arrive (seen: wrong residual codes in a few chunks per thousand jobs).  So the refill is made to
+  // depend on the loaded registers: `zero` is 0 (p1 >= 0), but the hardware has to wait for all three loads to form it.
+  // (A fence.proxy.async here would also wait for the gathers in flight and serialise the software pipeline: +15 %.)
+  const uint32_t zero = (pk4.x ^ __float_as_uint(dd4.x) ^ (FIRST ? 0u : P.old.x)) & (uint32_t)(t.p1 >> 31);
   __syncwarp();
-  if (lane == 0 && ch + NS < nCh) issue_tile(S, ring, V, !FIRST, p0, p1, ch + NS, it + NS, warp, pol);
+  if (lane == 0 && ch + NS < nCh) issue_tile(t, !FIRST, ch + NS, stage + (int)zero, pol);
   const uint32_t pk[4] = {pk4.x, pk4.y, pk4.z, pk4.w};
   const float dd[4] = {dd4.x, dd4.y, dd4.z, dd4.w};
   bool good[4];
+  int pix[4];
   WarpEval ev[4];
 #pragma unroll
-  for (int q = 0; q < 4; q++) {
-    P.T[q] = pk[q] >> 24;
-    ev[q] = warp_eval(c, pk[q], dd[q]);  // padding lanes compute on stale ring data: harmless
-  }
+  for (int q = 0; q < 4; q++) ev[q] = warp_eval(c, pk[q], dd[q]);  // padding lanes compute on stale ring data: harmless
   if (__all_sync(0xffffffffu, ev[0].interior && ev[1].interior && ev[2].interior && ev[3].interior)) {
 #pragma unroll
-    for (int q = 0; q < 4; q++) P.pix[q] = warp_pick_interior(c, ev[q], good[q]);
+    for (int q = 0; q < 4; q++) pix[q] = warp_pick_interior(c, ev[q], good[q]);
   } else {
 #pragma unroll
-    for (int q = 0; q < 4; q++) P.pix[q] = warp_pick_ring(c, ev[q], good[q]);
+    for (int q = 0; q < 4; q++) pix[q] = warp_pick_ring(c, ev[q], good[q]);
   }
   if (!(good[0] && good[1] && good[2] && good[3])) {
 #pragma unroll
     for (int q = 0; q < 4; q++)
-      if (!good[q]) P.pix[q] = warp_exact(V, pk[q] & 0xfff, (pk[q] >> 12) & 0xfff, dd[q]);
+      if (!good[q]) pix[q] = warp_exact(V, pk[q] & 0xfff, (pk[q] >> 12) & 0xfff, dd[q]);
   }
-  if (P.g + 3 >= p1) {  // only in the last tile of the slice: entries past the end of the list take no part
+  if (g + 3 >= t.p1) {  // only in the last tile of the slice: entries past the end of the list take no part
 #pragma unroll
-    for (int q = 0; q < 4; q++) P.pix[q] = P.g + q < p1 ? P.pix[q] : -1;
+    for (int q = 0; q < 4; q++) pix[q] = g + q < t.p1 ? pix[q] : -1;
   }
+  P.T = __byte_perm(__byte_perm(pk[0], pk[1], 0x0073), __byte_perm(pk[2], pk[3], 0x0073), 0x5410);
 #pragma unroll
-  for (int q = 0; q < 4; q++) P.val[q] = P.pix[q] >= 0 ? (int)__ldg(I + P.pix[q]) : 0;
+  for (int q = 0; q < 4; q++) {
+    P.val[q] = 256 + (int)(pk[q] >> 24);
+    if (pix[q] >= 0) P.val[q] = (int)__ldg(I + pix[q]);
+  }
 }
-
+// residual code of point q of a finished chunk: r + 255, or 511 when the point is not visible
+__device__ __forceinline__ uint32_t code_of(const Pend & P, int q) { return (uint32_t)(P.val[q] - (int)((P.T >> (8 * q)) & 0xff) + 255); }
 
 __device__ __forceinline__ int thread_id()
 {
@@ -272,27 +301,38 @@ __device__ __forceinline__ WarpConsts warp_consts(const ViewState & V)
 static __device__ __noinline__ void phase_a_first(
   Shared & S, unsigned char * ring, const ViewState & V, int p0, int p1, int nCh, uint32_t item, uint64_t pol)
 {
-  const int tid = thread_id();
+  const int tid = thread_id(), lane = tid & 31;
   const WarpConsts c = warp_consts(V);
+  const Stream t = make_stream(S, ring, V, p0, p1, tid >> 5);
   const uint8_t * __restrict__ I = V.I;
   uint2 * __restrict__ r4 = reinterpret_cast<uint2 *>(V.r);
-  Pend P, Pn;
-#pragma unroll 1
-  for (int ch = 0; ch <= nCh; ch++) {
-    if (ch < nCh) start_chunk<true>(S, ring, V, c, I, p0, p1, nCh, ch, item, tid, pol, Pn);
-    if (ch > 0) {
-      uint32_t rr[4];
+  int stage = (int)(item % NS);
+  uint32_t parity = (item / NS) & 1;
+  auto start = [&](int ch, Pend & P) {
+    start_chunk<true>(t, V, c, I, nCh, ch, stage, parity, lane, pol, P);
+    if (++stage == NS) stage = 0, parity ^= 1;
+  };
+  auto finish = [&](int ch, const Pend & P) {
+    uint32_t rr[4];
 #pragma unroll
-      for (int q = 0; q < 4; q++) {
-        const int r = P.val[q] - (int)P.T[q];
-        rr[q] = P.pix[q] >= 0 ? (uint32_t)(r + 255) : (uint32_t)R_CODE_INVISIBLE;  // residual code
-        atomicAdd(&S.hist[rr[q]], 1);  // branch-free: invisible points land in bin 511, which nobody reads
-      }
-      // every entry of a tile that holds part of the slice gets a code (entries past the end: not visible), so the
-      // later evaluations never see an unwritten code
-      if (P.g - 4 * (tid & 31) < p1) r4[P.g >> 2] = make_uint2(rr[0] | (rr[1] << 16), rr[2] | (rr[3] << 16));
+    for (int q = 0; q < 4; q++) {
+      rr[q] = code_of(P, q);
+      atomicAdd(&S.hist[rr[q]], 1);  // branch-free: invisible points land in bin 511, which nobody reads
     }
-    P = Pn;
+    // every entry of a tile that holds part of the slice gets a code (entries past the end: not visible), so the
+    // later evaluations never see an unwritten code
+    const int g = t.w0 + ch * CH;
+    if (g < p1) r4[(g >> 2) + lane] = make_uint2(rr[0] | (rr[1] << 16), rr[2] | (rr[3] << 16));
+  };
+  // Software pipeline over two register sets (no copies: a copy of a register with a load in flight would wait for
+  // it): the gathers of a chunk are consumed after the next chunk has been started
+  Pend A, B;
+#pragma unroll 1
+  for (int ch = 0; ch <= nCh; ch += 2) {
+    if (ch < nCh) start(ch, A);
+    if (ch > 0) finish(ch - 1, B);
+    if (ch + 1 < nCh) start(ch + 1, B);
+    if (ch < nCh) finish(ch, A);
   }
 }
 
@@ -452,59 +492,69 @@ static __device__ __noinline__ unsigned phase_a_inc(
 {
   const int tid = thread_id(), lane = tid & 31;
   const WarpConsts c = warp_consts(V);
+  const Stream t = make_stream(S, ring, V, p0, p1, tid >> 5);
   const uint8_t * __restrict__ I = V.I;
   int16_t * __restrict__ rcode = V.r;
   const unsigned ltmask = (1u << lane) - 1u;
+  int stage = (int)(item % NS);
+  uint32_t parity = (item / NS) & 1;
   int qh = 0, qe = 0;  // queue head and fill (warp-uniform)
   unsigned nChanged = 0;
-  Pend P, Pn;
-#pragma unroll 1
-  for (int ch = 0; ch <= nCh; ch++) {
-    if (ch < nCh) start_chunk<false>(S, ring, V, c, I, p0, p1, nCh, ch, item, tid, pol, Pn);
-    if (ch > 0) {
-      // entries past the end of the slice are not visible now (pix < 0) and were stored as not visible by the first
-      // evaluation: they never change
-      const uint32_t oc[4] = {P.old.x & 0xffff, P.old.x >> 16, P.old.y & 0xffff, P.old.y >> 16};
-      uint32_t nc[4];
-      int cn = 0;
+  auto start = [&](int ch, Pend & P) {
+    start_chunk<false>(t, V, c, I, nCh, ch, stage, parity, lane, pol, P);
+    if (++stage == NS) stage = 0, parity ^= 1;
+  };
+  auto finish = [&](int ch, const Pend & P) {
+    // entries past the end of the slice are not visible now and were stored as not visible by the first
+    // evaluation: they never change
+    const uint32_t oc[4] = {P.old.x & 0xffff, P.old.x >> 16, P.old.y & 0xffff, P.old.y >> 16};
+    uint32_t nc[4];
+    int cn = 0;
 #pragma unroll
-      for (int q = 0; q < 4; q++) {
-        const int r = P.val[q] - (int)P.T[q];
-        nc[q] = P.pix[q] >= 0 ? (uint32_t)(r + 255) : (uint32_t)R_CODE_INVISIBLE;
-        cn += nc[q] != oc[q] ? 1 : 0;
+    for (int q = 0; q < 4; q++) {
+      nc[q] = code_of(P, q);
+      cn += nc[q] != oc[q] ? 1 : 0;
+    }
+    if (__any_sync(0xffffffffu, cn != 0)) {
+      const int g = t.w0 + ch * CH + 4 * lane;
+      // per-lane counts 0..4 -> warp prefix through three ballots
+      const unsigned b0 = __ballot_sync(0xffffffffu, cn & 1), b1 = __ballot_sync(0xffffffffu, cn & 2),
+                     b2 = __ballot_sync(0xffffffffu, cn & 4);
+      const int tot = __popc(b0) + 2 * __popc(b1) + 4 * __popc(b2);
+      while (qe + tot > QN) {  // make room (only when most of a tile changed)
+        const int m = min(qe, QB);
+        move_moments(S, V, Mlo, Mhi, queue, qh, m);
+        qh = (qh + m) & (QN - 1);
+        qe -= m;
       }
-      if (__any_sync(0xffffffffu, cn != 0)) {
-        // per-lane counts 0..4 -> warp prefix through three ballots
-        const unsigned b0 = __ballot_sync(0xffffffffu, cn & 1), b1 = __ballot_sync(0xffffffffu, cn & 2),
-                       b2 = __ballot_sync(0xffffffffu, cn & 4);
-        const int tot = __popc(b0) + 2 * __popc(b1) + 4 * __popc(b2);
-        while (qe + tot > QN) {  // make room (only when most of a tile changed)
-          const int m = min(qe, QB);
-          move_moments(S, V, Mlo, Mhi, queue, qh, m);
-          qh = (qh + m) & (QN - 1);
-          qe -= m;
-        }
-        if (cn) {
-          int pos = qh + qe + __popc(b0 & ltmask) + 2 * __popc(b1 & ltmask) + 4 * __popc(b2 & ltmask);
+      if (cn) {
+        int pos = qh + qe + __popc(b0 & ltmask) + 2 * __popc(b1 & ltmask) + 4 * __popc(b2 & ltmask);
 #pragma unroll
-          for (int q = 0; q < 4; q++)
-            if (nc[q] != oc[q]) {
-              queue[(pos++) & (QN - 1)] = make_uint2((uint32_t)(P.g + q), oc[q] | (nc[q] << 16));
-              rcode[P.g + q] = (int16_t)nc[q];
-              atomicSub(&S.hist[oc[q]], 1);  // bin 511 (not visible) collects garbage and is never read
-              atomicAdd(&S.hist[nc[q]], 1);
-            }
-        }
-        qe += tot;
-        nChanged += tot;
-        while (qe >= QB) {
-          move_moments(S, V, Mlo, Mhi, queue, qh, QB);
-          qh = (qh + QB) & (QN - 1);
-          qe -= QB;
-        }
+        for (int q = 0; q < 4; q++)
+          if (nc[q] != oc[q]) {
+            queue[(pos++) & (QN - 1)] = make_uint2((uint32_t)(g + q), oc[q] | (nc[q] << 16));
+            rcode[g + q] = (int16_t)nc[q];
+            atomicSub(&S.hist[oc[q]], 1);  // bin 511 (not visible) collects garbage and is never read
+            atomicAdd(&S.hist[nc[q]], 1);
+          }
+      }
+      qe += tot;
+      nChanged += tot;
+      while (qe >= QB) {
+        move_moments(S, V, Mlo, Mhi, queue, qh, QB);
+        qh = (qh + QB) & (QN - 1);
+        qe -= QB;
       }
     }
-    P = Pn;
+  };
+  // software pipeline over two register sets (see phase_a_first)
+  Pend A, B;
+#pragma unroll 1
+  for (int ch = 0; ch <= nCh; ch += 2) {
+    if (ch < nCh) start(ch, A);
+    if (ch > 0) finish(ch - 1, B);
+    if (ch + 1 < nCh) start(ch + 1, B);
+    if (ch < nCh) finish(ch, A);
   }
   if (qe > 0) move_moments(S, V, Mlo, Mhi, queue, qh, qe);
   return nChanged;
@@ -653,8 +703,9 @@ __global__ void __launch_bounds__(MT, CTAS_PER_SM) gn_mom_kernel(
   int evals = 0;
   unsigned myChanged = 0;  // warp-uniform
 
+  const Stream strm = make_stream(S, ring, V, p0, p1, warp);
   if (lane == 0)  // prologue of the first phase A
-    for (int c = 0; c < min(NS, nCh); c++) issue_tile(S, ring, V, false, p0, p1, c, item + c, warp, pol);
+    for (int c = 0; c < min(NS, nCh); c++) issue_tile(strm, false, c, (int)((item + c) % NS), pol);
 
   long long tc = clock64();
   auto lap = [&](int slot) {
@@ -683,7 +734,7 @@ __global__ void __launch_bounds__(MT, CTAS_PER_SM) gn_mom_kernel(
     asm volatile("fence.proxy.async;" ::: "memory");
     __syncwarp();
     if (lane == 0)
-      for (int cc = 0; cc < min(NS, nCh); cc++) issue_tile(S, ring, V, true, p0, p1, cc, item + cc, warp, pol);
+      for (int cc = 0; cc < min(NS, nCh); cc++) issue_tile(strm, true, cc, (int)((item + cc) % NS), pol);
     // ------------------------------------------------------------------ the view's histogram, scale, weights, chi2
     __syncthreads();
     cluster.sync();
