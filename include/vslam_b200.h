@@ -50,9 +50,11 @@ enum { VSLAMB200_SOLVER_GN = 0, VSLAMB200_SOLVER_LM = 1 };
  * EXTENSION (forward formulation: bilinear sampling, Jacobians at the warped point every iteration, optional depth
  * residual; semantics of lukas_kanade/src/ForwardAdditive.cpp:52-137, defined by oracle/vslam_oracle.cpp) */
 enum { VSLAMB200_SAMPLING_NEAREST = 0, VSLAMB200_SAMPLING_BILINEAR = 1 };
-/* level_kernel: AUTO picks the moment-based kernel (csrc/gn_mom.cu) wherever it applies - scalers without offset
- * (identity, t-distribution), at most 8 keyframes per job, the same number in every job of the call - and the dense
- * kernel (csrc/gn_level.cu) otherwise; DENSE forces the dense kernel; MOMENTS is AUTO (tests assert which one ran) */
+/* level_kernel: which Gauss-Newton level kernel runs the nearest-sampling path.  AUTO: the dense kernel
+ * (csrc/gn_level.cu) for jobs with one keyframe, the moment-based kernel (csrc/gn_mom.cu: keyframes side by side) for
+ * stacked jobs where it applies - scalers without offset (identity, t-distribution), at most 8 keyframes per job, the
+ * same number in every job of the call; DENSE: always the dense kernel; MOMENTS: the moment kernel wherever it applies
+ * (also with one keyframe).  Results agree to rounding (the sums are formed in another order). */
 enum { VSLAMB200_KERNEL_AUTO = 0, VSLAMB200_KERNEL_DENSE = 1, VSLAMB200_KERNEL_MOMENTS = 2 };
 
 typedef struct vslamb200_ctx vslamb200_ctx;

@@ -31,9 +31,12 @@ namespace cg = cooperative_groups;
 
 namespace vb
 {
-constexpr int GT = 128;              // threads per CTA
+#ifndef DENSE_GT
+#define DENSE_GT 128
+#endif
+constexpr int GT = DENSE_GT;         // threads per CTA (256 x 2 per SM measured the same as 128 x 4)
 constexpr int BPT = HIST_BINS / GT;  // histogram bins per thread
-constexpr int CTAS_PER_SM = 4;
+constexpr int CTAS_PER_SM = 512 / GT;
 
 __device__ __forceinline__ double block_sum(double v, double * sm /* >= GT/32 doubles */)
 {

@@ -1,14 +1,18 @@
-// Moment-based Gauss-Newton level kernel: the default for nearest-pixel sampling with a scaler without offset
-// (identity, t-distribution), i.e. the reference's LossTDistribution(ScalerTDistribution) configuration.
+// Moment-based Gauss-Newton level kernel: nearest-pixel sampling with a scaler without offset (identity, t-distribution),
+// i.e. the reference's LossTDistribution(ScalerTDistribution) configuration.  The default for STACKED alignment
+// (SE3Alignment.cpp:106-146): the cluster's CTAs are split among the job's keyframes, so the views run side by side
+// (1 frame against 8 keyframes at 1280x720: 478 alignments/s against 185 with the dense kernel, which walks the views one
+// after the other).  For one keyframe per job the dense kernel (gn_level.cu) is faster and stays
+// the default; vslamb200_config.level_kernel = VSLAMB200_KERNEL_MOMENTS selects this kernel there too.
 //
 // One launch per pyramid level; a thread-block CLUSTER per alignment job runs the whole GaussNewton::solve loop of that
 // level on device (GaussNewton.cpp:33-102 over InverseCompositional::computeNormalEquations,
 // InverseCompositional.cpp:105-154, stacked over the job's keyframes, InverseCompositionalStacked.cpp:39-48).
 //
-// What makes it cheap.  The inverse-compositional Jacobian of a point is fixed for the level
-// (InverseCompositional.cpp:63-93) and the target is sampled at the NEAREST pixel (:119-120), so the residual of a point
-// is an integer in [-255, 255] and, between two iterations, only the few points whose rounded target moved change it,
-// while the robust scale - and with it every weight - changes every time.  Both facts are used exactly:
+// The inverse-compositional Jacobian of a point is fixed for the level (InverseCompositional.cpp:63-93) and the target is
+// sampled at the NEAREST pixel (:119-120), so the residual of a point is an integer in [-255, 255] and, between two
+// iterations, only the few points whose rounded target moved change it (1 - 3 % per iteration), while the robust scale -
+// and with it every weight - changes every time.  Both facts are used exactly:
 //   * MOMENTS.  Per residual magnitude c = |r| the CTA keeps, for its slice of the interest list,
 //         M[c][i,j] = sum_{k: |r_k| = c} J_ki J_kj  (21 terms)       M[c][21+i] = sum_{k: |r_k| = c} sign(r_k) J_ki  (6 terms)
 //     so that for any weight that is a function of |r| (NormalEquations.cpp:53-61)
@@ -18,17 +22,16 @@
 //     (bit-identical run to run, no floating-point atomics) and a point's old contribution is removed exactly.
 //   * FIRST EVALUATION of a level: dense warp + sample of every point (residual codes, histogram), then the moments are
 //     built by a counting sort of the slice by residual code and a pass in which every thread accumulates a run of
-//     equal-code points in registers (one flush per code run instead of 27 atomics per point).
+//     equal-code points in registers (one flush per code run instead of 54 atomics per point).
 //   * LATER EVALUATIONS: warp + sample of every point (filtered fp32 evaluation, exact fp64 fallback: warp_filter.cuh),
-//     compare with the stored code; the points that changed (0.5 - 3 % per iteration) are queued per warp and move their
-//     moments from the old to the new cell, 16 points at a time.
+//     compare with the stored code; the points that changed are queued per warp and move their moments from the old to
+//     the new cell, 32 points at a time (one per lane).
 //   * EVERY EVALUATION: the view's histogram (summed over its CTAs through distributed shared memory) gives the scale
 //     (Scaler.cpp:49-67), the weight table (Loss.cpp:51-92) and chi2; every CTA folds its moments into 27 partial sums;
 //     the cluster adds them in rank order and every CTA runs the 6x6 solve redundantly (solve.cuh).
-// Stacked alignment (SE3Alignment.cpp:106-146): the cluster's CTAs are split among the job's keyframes, so the views
-// run side by side and every CTA holds the moments of exactly one view.
 // Two cluster barriers per iteration.  The interest list streams through per-warp shared-memory rings filled by TMA
-// bulk copies (cp.async.bulk + mbarrier complete_tx), 10 B per point and iteration: d, (u, v, T) and the old code.
+// bulk copies (cp.async.bulk + mbarrier complete_tx), 10 B per point and iteration: d, (u, v, T) and the old code; the
+// target pixels are gathered with asynchronous copies (cp.async) into per-lane shared-memory slots.
 #include <cooperative_groups.h>
 
 #include "robust.cuh"
@@ -48,11 +51,11 @@ constexpr int CTAS_PER_SM = 2;
 constexpr int NC = 256;            // residual magnitudes 0..255
 constexpr int NTERM = 27;          // moments per magnitude: 21 (upper A) + 6 (b)
 constexpr int CH = 4 * MT;         // interest points per chunk (4 per thread); a warp's share is one list tile
-constexpr int NS = 3;              // ring stages per warp
+constexpr int NS = 3;              // ring stages per warp (4 measured the same)
 constexpr int ST_D = 0, ST_UVT = 512, ST_R = 1024, ST_TILE_BYTES = 1024, ST_R_BYTES = 256, ST_BYTES = 1280;
 static_assert(CH / MW == LIST_TILE && TILE_OFF_D == ST_D && TILE_OFF_UVT == ST_UVT && LIST_TILE_BYTES == ST_TILE_BYTES, "tile layout");
 constexpr int QB = 32;             // changed points whose moments move together: one per lane
-constexpr int QN = 128;            // queue entries per warp (circular): < QB left over + one tile of 128 new ones at most
+constexpr int QN = 64;            // queue entries per warp (circular): < QB left over + 32 new ones (more: see finish)
 constexpr int NROW = NC + 1;       // moment rows: magnitudes 0..255 and a row that absorbs the not-visible code
 constexpr double MAGIC = 6755399441055744.0;          // 1.5 * 2^52: x + MAGIC has the integer round(x) in its low mantissa bits
 constexpr long long MAGIC_BITS = 0x4338000000000000ll;
@@ -79,14 +82,15 @@ struct Shared
   alignas(8) uint64_t full[MW][NS];  // per warp and stage: the TMA bytes have landed
   unsigned long long nChanged;
 };
-// dynamic shared memory: Mlo u32[NROW][NTERM] | Mhi u32[NROW][NTERM] | ring | scratch | queue | ViewState[K] | partial[32] | sums[K][28]
+// dynamic shared memory: Mlo u32[NROW][NTERM] | Mhi u32[NROW][NTERM] | ring | scratch | queue | gather slots | ViewState[K] | partial[32] | sums[K][28]
 constexpr size_t OFF_MHI = (size_t)NROW * NTERM * 4;
 constexpr size_t OFF_RING = (2 * OFF_MHI + 127) / 128 * 128;
 constexpr size_t OFF_SCRATCH = OFF_RING + (size_t)MW * NS * ST_BYTES;
 constexpr size_t SCRATCH_BYTES = 2 * NC * 8;   // bucket cursors (build) | weight tables (fold)
 static_assert(SCRATCH_BYTES >= HIST_BINS * 4, "scratch aliases");
 constexpr size_t OFF_QUEUE = OFF_SCRATCH + SCRATCH_BYTES;
-constexpr size_t OFF_VIEWS = OFF_QUEUE + (size_t)MW * QN * 8;
+constexpr size_t OFF_SLOTS = OFF_QUEUE + (size_t)MW * QN * 8;   // gathered words: [warp][register set][lane] x 16 bytes
+constexpr size_t OFF_VIEWS = OFF_SLOTS + (size_t)MW * 2 * 32 * 16;
 constexpr int PARTIAL_DOUBLES = 32;  // 28 terms + {scale, offset}
 __host__ __device__ inline size_t dyn_smem(int K)
 {
@@ -202,31 +206,39 @@ __device__ __forceinline__ void issue_tile(const Stream & t, bool withCodes, int
   if (withCodes) bulk_g2s(st + ST_R, t.codes + (size_t)c * CH, ST_R_BYTES, bar);
 }
 
-// What a chunk leaves in flight between its two pipeline halves: the four gathered target pixels (preset to 256 + T so
-// that a point that is not visible - no gather - comes out as the not-visible code 511 without a select), the four
-// template values and the four stored residual codes.
+// What a chunk leaves in flight between its two pipeline halves.  The gathered target pixels are NOT held in registers:
+// each lane gathers the aligned 32-bit words that hold its four target pixels into a 16-byte shared-memory slot with
+// asynchronous copies (cp.async, LDGSTS), so nothing waits for them while the next chunk's arithmetic runs - a register
+// with a load in flight would be spilled by the compiler under this loop's register pressure, and a spill waits.
 struct Pend
 {
-  int val[4];
-  uint32_t T;  // four bytes
-  uint2 old;
+  uint32_t T;    // the four template values, one byte each
+  uint32_t sel;  // per point q, bits 4q..4q+2: byte of the gathered word | 4 when the point is visible
+  uint2 old;     // the four stored residual codes
 };
+__device__ __forceinline__ void cp_async4(void * smemDst, const void * gsrc)
+{
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(smemDst)), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+// all but the most recently committed group of this thread have landed
+__device__ __forceinline__ void cp_async_wait_but_one() { asm volatile("cp.async.wait_group 1;" ::: "memory"); }
 
 // first half of a chunk's pipeline: list entries out of the ring, warp, gathers issued
 template <bool FIRST>
 __device__ __forceinline__ void start_chunk(
   const Stream & t, const ViewState & V, const WarpConsts & c, const uint8_t * __restrict__ I, int nCh, int ch, int stage,
-  uint32_t parity, int lane, uint64_t pol, Pend & P)
+  uint32_t parity, int lane, uint64_t pol, Pend & P, uint32_t * slot /* this lane's four words for this register set */)
 {
   const unsigned char * st = t.ring + stage * ST_BYTES;
   mbar_wait(t.bars + stage, parity);
   const int g = t.w0 + ch * CH + 4 * lane;
   if (t.w0 + ch * CH >= t.p1) {  // warp-uniform: nothing of this chunk belongs to the warp
     if (lane == 0 && ch + NS < nCh) issue_tile(t, !FIRST, ch + NS, stage, pol);
-#pragma unroll
-    for (int q = 0; q < 4; q++) P.val[q] = 256;
     P.T = 0u;
+    P.sel = 0u;
     P.old = make_uint2(R_CODE_INVISIBLE * 0x10001u, R_CODE_INVISIBLE * 0x10001u);
+    cp_async_commit();  // an empty group: the group count stays in step with the chunks
     return;
   }
   const uint4 pk4 = *reinterpret_cast<const uint4 *>(st + ST_UVT + lane * 16);
@@ -264,14 +276,30 @@ __device__ __forceinline__ void start_chunk(
     for (int q = 0; q < 4; q++) pix[q] = g + q < t.p1 ? pix[q] : -1;
   }
   P.T = __byte_perm(__byte_perm(pk[0], pk[1], 0x0073), __byte_perm(pk[2], pk[3], 0x0073), 0x5410);
+  uint32_t sel = 0u;
+#pragma unroll
+  for (int q = 0; q < 4; q++)
+    if (pix[q] >= 0) {
+      cp_async4(slot + q, I + (pix[q] & ~3));  // the plane is 256-byte aligned (api.cu, layout_frame)
+      sel |= (uint32_t)((pix[q] & 3) | 4) << (4 * q);
+    }
+  cp_async_commit();
+  P.sel = sel;
+}
+// Second half: the residual codes of a chunk whose gathers have landed (r + 255, or 511 when the point is not visible).
+// Call after cp_async_wait_but_one() with exactly one younger group committed.
+__device__ __forceinline__ void codes_of(const Pend & P, const uint32_t * slot, uint32_t (&nc)[4])
+{
+  const uint4 w4 = *reinterpret_cast<const uint4 *>(slot);
+  const uint32_t w[4] = {w4.x, w4.y, w4.z, w4.w};
 #pragma unroll
   for (int q = 0; q < 4; q++) {
-    P.val[q] = 256 + (int)(pk[q] >> 24);
-    if (pix[q] >= 0) P.val[q] = (int)__ldg(I + pix[q]);
+    const uint32_t s4 = P.sel >> (4 * q);
+    const uint32_t val = (w[q] >> (8 * (s4 & 3))) & 0xff;
+    const uint32_t T = (P.T >> (8 * q)) & 0xff;
+    nc[q] = (s4 & 4) ? val - T + 255u : (uint32_t)R_CODE_INVISIBLE;
   }
 }
-// residual code of point q of a finished chunk: r + 255, or 511 when the point is not visible
-__device__ __forceinline__ uint32_t code_of(const Pend & P, int q) { return (uint32_t)(P.val[q] - (int)((P.T >> (8 * q)) & 0xff) + 255); }
 
 __device__ __forceinline__ int thread_id()
 {
@@ -299,40 +327,43 @@ __device__ __forceinline__ WarpConsts warp_consts(const ViewState & V)
 // first evaluation of a level: every point of the slice, dense; residual codes and histogram
 // ---------------------------------------------------------------------------------------------------------------------
 static __device__ __noinline__ void phase_a_first(
-  Shared & S, unsigned char * ring, const ViewState & V, int p0, int p1, int nCh, uint32_t item, uint64_t pol)
+  Shared & S, unsigned char * ring, uint32_t * slots, const ViewState & V, int p0, int p1, int nCh, uint32_t item, uint64_t pol)
 {
   const int tid = thread_id(), lane = tid & 31;
   const WarpConsts c = warp_consts(V);
   const Stream t = make_stream(S, ring, V, p0, p1, tid >> 5);
   const uint8_t * __restrict__ I = V.I;
   uint2 * __restrict__ r4 = reinterpret_cast<uint2 *>(V.r);
+  uint32_t * slotA = slots + ((tid >> 5) * 2 * 32 + lane) * 4, * slotB = slotA + 32 * 4;
   int stage = (int)(item % NS);
   uint32_t parity = (item / NS) & 1;
-  auto start = [&](int ch, Pend & P) {
-    start_chunk<true>(t, V, c, I, nCh, ch, stage, parity, lane, pol, P);
+  auto start = [&](int ch, Pend & P, uint32_t * slot) {
+    start_chunk<true>(t, V, c, I, nCh, ch, stage, parity, lane, pol, P, slot);
     if (++stage == NS) stage = 0, parity ^= 1;
   };
-  auto finish = [&](int ch, const Pend & P) {
+  auto finish = [&](int ch, const Pend & P, const uint32_t * slot) {
+    cp_async_wait_but_one();
     uint32_t rr[4];
+    codes_of(P, slot, rr);
 #pragma unroll
-    for (int q = 0; q < 4; q++) {
-      rr[q] = code_of(P, q);
-      atomicAdd(&S.hist[rr[q]], 1);  // branch-free: invisible points land in bin 511, which nobody reads
-    }
+    for (int q = 0; q < 4; q++) atomicAdd(&S.hist[rr[q]], 1);  // branch-free: invisible points land in bin 511, which nobody reads
     // every entry of a tile that holds part of the slice gets a code (entries past the end: not visible), so the
     // later evaluations never see an unwritten code
     const int g = t.w0 + ch * CH;
     if (g < p1) r4[(g >> 2) + lane] = make_uint2(rr[0] | (rr[1] << 16), rr[2] | (rr[3] << 16));
   };
-  // Software pipeline over two register sets (no copies: a copy of a register with a load in flight would wait for
-  // it): the gathers of a chunk are consumed after the next chunk has been started
+  // Software pipeline over two register sets / gather slots: a chunk's gathers are consumed after the next chunk has
+  // been started (every start commits one cp.async group, an empty one when there is nothing left to start).
+  // (Measured: one instance of each half with a register copy between them is 14 % slower.)
   Pend A, B;
 #pragma unroll 1
   for (int ch = 0; ch <= nCh; ch += 2) {
-    if (ch < nCh) start(ch, A);
-    if (ch > 0) finish(ch - 1, B);
-    if (ch + 1 < nCh) start(ch + 1, B);
-    if (ch < nCh) finish(ch, A);
+    if (ch < nCh) start(ch, A, slotA);
+    else cp_async_commit();
+    if (ch > 0) finish(ch - 1, B, slotB);
+    if (ch + 1 < nCh) start(ch + 1, B, slotB);
+    else cp_async_commit();
+    if (ch < nCh) finish(ch, A, slotA);
   }
 }
 
@@ -487,76 +518,87 @@ static __device__ __noinline__ void move_moments(
 
 // returns the number of points of this warp whose residual changed
 static __device__ __noinline__ unsigned phase_a_inc(
-  Shared & S, unsigned char * ring, uint2 * queue, uint32_t * Mlo, uint32_t * Mhi, const ViewState & V, int p0, int p1, int nCh,
-  uint32_t item, uint64_t pol)
+  Shared & S, unsigned char * ring, uint32_t * slots, uint2 * queue, uint32_t * Mlo, uint32_t * Mhi, const ViewState & V, int p0,
+  int p1, int nCh, uint32_t item, uint64_t pol)
 {
   const int tid = thread_id(), lane = tid & 31;
   const WarpConsts c = warp_consts(V);
   const Stream t = make_stream(S, ring, V, p0, p1, tid >> 5);
   const uint8_t * __restrict__ I = V.I;
   int16_t * __restrict__ rcode = V.r;
+  uint32_t * slotA = slots + ((tid >> 5) * 2 * 32 + lane) * 4, * slotB = slotA + 32 * 4;
   const unsigned ltmask = (1u << lane) - 1u;
   int stage = (int)(item % NS);
   uint32_t parity = (item / NS) & 1;
   int qh = 0, qe = 0;  // queue head and fill (warp-uniform)
   unsigned nChanged = 0;
-  auto start = [&](int ch, Pend & P) {
-    start_chunk<false>(t, V, c, I, nCh, ch, stage, parity, lane, pol, P);
+  auto start = [&](int ch, Pend & P, uint32_t * slot) {
+    start_chunk<false>(t, V, c, I, nCh, ch, stage, parity, lane, pol, P, slot);
     if (++stage == NS) stage = 0, parity ^= 1;
   };
-  auto finish = [&](int ch, const Pend & P) {
+  auto flush = [&](int m) {
+    move_moments(S, V, Mlo, Mhi, queue, qh, m);
+    qh = (qh + m) & (QN - 1);
+    qe -= m;
+  };
+  auto record = [&](int g, uint32_t o, uint32_t n, int pos) {
+    queue[pos & (QN - 1)] = make_uint2((uint32_t)g, o | (n << 16));
+    rcode[g] = (int16_t)n;
+    atomicSub(&S.hist[o], 1);  // bin 511 (not visible) collects garbage and is never read
+    atomicAdd(&S.hist[n], 1);
+  };
+  auto finish = [&](int ch, const Pend & P, const uint32_t * slot) {
+    cp_async_wait_but_one();
     // entries past the end of the slice are not visible now and were stored as not visible by the first
     // evaluation: they never change
     const uint32_t oc[4] = {P.old.x & 0xffff, P.old.x >> 16, P.old.y & 0xffff, P.old.y >> 16};
     uint32_t nc[4];
+    codes_of(P, slot, nc);
     int cn = 0;
 #pragma unroll
-    for (int q = 0; q < 4; q++) {
-      nc[q] = code_of(P, q);
-      cn += nc[q] != oc[q] ? 1 : 0;
-    }
+    for (int q = 0; q < 4; q++) cn += nc[q] != oc[q] ? 1 : 0;
     if (__any_sync(0xffffffffu, cn != 0)) {
       const int g = t.w0 + ch * CH + 4 * lane;
       // per-lane counts 0..4 -> warp prefix through three ballots
       const unsigned b0 = __ballot_sync(0xffffffffu, cn & 1), b1 = __ballot_sync(0xffffffffu, cn & 2),
                      b2 = __ballot_sync(0xffffffffu, cn & 4);
       const int tot = __popc(b0) + 2 * __popc(b1) + 4 * __popc(b2);
-      while (qe + tot > QN) {  // make room (only when most of a tile changed)
-        const int m = min(qe, QB);
-        move_moments(S, V, Mlo, Mhi, queue, qh, m);
-        qh = (qh + m) & (QN - 1);
-        qe -= m;
-      }
-      if (cn) {
-        int pos = qh + qe + __popc(b0 & ltmask) + 2 * __popc(b1 & ltmask) + 4 * __popc(b2 & ltmask);
+      if (qe + tot <= QN) {
+        if (cn) {
+          int pos = qh + qe + __popc(b0 & ltmask) + 2 * __popc(b1 & ltmask) + 4 * __popc(b2 & ltmask);
 #pragma unroll
-        for (int q = 0; q < 4; q++)
-          if (nc[q] != oc[q]) {
-            queue[(pos++) & (QN - 1)] = make_uint2((uint32_t)(g + q), oc[q] | (nc[q] << 16));
-            rcode[g + q] = (int16_t)nc[q];
-            atomicSub(&S.hist[oc[q]], 1);  // bin 511 (not visible) collects garbage and is never read
-            atomicAdd(&S.hist[nc[q]], 1);
-          }
+          for (int q = 0; q < 4; q++)
+            if (nc[q] != oc[q]) record(g + q, oc[q], nc[q], pos++);
+        }
+        qe += tot;
+      } else {
+        // more changes than the queue has room for (a large step): one point per lane at a time
+#pragma unroll 1
+        for (int q = 0; q < 4; q++) {
+          const uint32_t o = q == 0 ? oc[0] : q == 1 ? oc[1] : q == 2 ? oc[2] : oc[3];
+          const uint32_t n = q == 0 ? nc[0] : q == 1 ? nc[1] : q == 2 ? nc[2] : nc[3];
+          const unsigned m = __ballot_sync(0xffffffffu, n != o);
+          if (qe + __popc(m) > QN) flush(qe >= QB ? QB : qe);
+          if (n != o) record(g + q, o, n, qh + qe + __popc(m & ltmask));
+          qe += __popc(m);
+        }
       }
-      qe += tot;
       nChanged += tot;
-      while (qe >= QB) {
-        move_moments(S, V, Mlo, Mhi, queue, qh, QB);
-        qh = (qh + QB) & (QN - 1);
-        qe -= QB;
-      }
+      while (qe >= QB) flush(QB);
     }
   };
-  // software pipeline over two register sets (see phase_a_first)
+  // software pipeline over two gather slots (see phase_a_first)
   Pend A, B;
 #pragma unroll 1
   for (int ch = 0; ch <= nCh; ch += 2) {
-    if (ch < nCh) start(ch, A);
-    if (ch > 0) finish(ch - 1, B);
-    if (ch + 1 < nCh) start(ch + 1, B);
-    if (ch < nCh) finish(ch, A);
+    if (ch < nCh) start(ch, A, slotA);
+    else cp_async_commit();
+    if (ch > 0) finish(ch - 1, B, slotB);
+    if (ch + 1 < nCh) start(ch + 1, B, slotB);
+    else cp_async_commit();
+    if (ch < nCh) finish(ch, A, slotA);
   }
-  if (qe > 0) move_moments(S, V, Mlo, Mhi, queue, qh, qe);
+  if (qe > 0) flush(qe);
   return nChanged;
 }
 
@@ -650,6 +692,7 @@ __global__ void __launch_bounds__(MT, CTAS_PER_SM) gn_mom_kernel(
   unsigned char * ring = dyn + OFF_RING;
   unsigned char * scratch = dyn + OFF_SCRATCH;
   uint2 * queue = reinterpret_cast<uint2 *>(dyn + OFF_QUEUE) + warp * QN;
+  uint32_t * slots = reinterpret_cast<uint32_t *>(dyn + OFF_SLOTS);
 
   block_copy(&S.J, jobs + job);
   __syncthreads();
@@ -718,13 +761,13 @@ __global__ void __launch_bounds__(MT, CTAS_PER_SM) gn_mom_kernel(
 
   for (;;) {
     if (evals == 0) {
-      phase_a_first(S, ring, V, p0, p1, nCh, item, pol);
+      phase_a_first(S, ring, slots, V, p0, p1, nCh, item, pol);
       __syncthreads();
       lap(7);
       build_moments(S, scratch, Mlo, Mhi, V, p0, p1);
       lap(8);
     } else {
-      myChanged += phase_a_inc(S, ring, queue, Mlo, Mhi, V, p0, p1, nCh, item, pol);
+      myChanged += phase_a_inc(S, ring, slots, queue, Mlo, Mhi, V, p0, p1, nCh, item, pol);
       lap(0);
     }
     item += nCh;
