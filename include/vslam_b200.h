@@ -197,6 +197,25 @@ int vslamb200_set_timing(vslamb200_ctx * ctx, int enable);
 /* block until everything queued on the context's stream has finished */
 int vslamb200_synchronize(vslamb200_ctx * ctx);
 
+/* NO COUNTERPART IN THE REFERENCE - added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid allocation).  The interest-point list of ONE
+ * pyramid level - the candidate mask of SE3Alignment.cpp:83-94 / :123-130, dIx^2 + dIy^2 >= min_gradient^2 and depth > 0
+ * and finite, compacted in row-major order exactly like the lists vslamb200_align builds internally - computed by a
+ * single kernel that allocates NOTHING: its scratch (one record per 2048 pixels) is a static device array inside the
+ * library sized for VSLAMB200_NOALLOC_MAX_PIXELS, about 33 KB per GPU held until exit; larger images are rejected with
+ * VSLAMB200_EINVAL.  All pointers are DEVICE pointers on the current device: d_dIx, d_dIy (int16) and d_depth (float)
+ * are row-major width x height planes (e.g. what vslamb200_frame_download returns, copied back to the device; pass
+ * depth_sf for the single-frame overload, depth for the multi-frame one); d_points receives up to width * height pixel
+ * indices v * width + u, d_count their number.  The work is queued on cuda_stream (a cudaStream_t passed as void*; NULL =
+ * the default stream) and is complete when that stream reaches this point; the function does not synchronise.  Every call
+ * shares the one scratch array and clears the part it uses first: calls that overlap on the GPU (two streams, two host
+ * threads) race - serialise them.  The first call on a device resolves the array's address (cudaGetSymbolAddress); make
+ * that call outside a graph capture.  Errors: vslamb200_last_error(). */
+#define VSLAMB200_NOALLOC_MAX_PIXELS (4096 * 4096)
+int vslamb200_interest_points_noalloc(
+  const int16_t * d_dIx, const int16_t * d_dIy, const float * d_depth, int width, int height, double min_gradient,
+  uint32_t * d_points, int * d_count, void * cuda_stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -7,7 +7,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, "csrc")
 LIBDIR = os.path.join(_HERE, "lib")
 LIB = os.path.join(LIBDIR, "libvslam_b200.so")
-SOURCES = ["preprocess.cu", "lists.cu", "level_misc.cu", "gn_level.cu", "gn_mom.cu", "ext.cu", "api.cu"]
+SOURCES = ["preprocess.cu", "lists.cu", "level_misc.cu", "gn_level.cu", "gn_mom.cu", "ext.cu", "noalloc.cu", "api.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",

@@ -57,8 +57,10 @@ EXPORTS = [
     "vslamb200_frame_release",
     "vslamb200_frame_release_all", "vslamb200_frame_dims", "vslamb200_frame_download", "vslamb200_align",
     "vslamb200_set_trace", "vslamb200_get_trace", "vslamb200_evaluate", "vslamb200_get_stats",
-    "vslamb200_reset_stats", "vslamb200_set_timing", "vslamb200_synchronize",
+    "vslamb200_reset_stats", "vslamb200_set_timing", "vslamb200_synchronize", "vslamb200_frames_upload_async",
+    "vslamb200_interest_points_noalloc",
 ]
+NOALLOC_MAX_PIXELS = 4096 * 4096
 
 _lib = None
 
@@ -99,6 +101,7 @@ def lib():
         L.vslamb200_reset_stats.argtypes = [vp]
         L.vslamb200_set_timing.argtypes = [vp, i]
         L.vslamb200_synchronize.argtypes = [vp]
+        L.vslamb200_interest_points_noalloc.argtypes = [vp, vp, vp, i, i, C.c_double, vp, vp, vp]
         _lib = L
     return _lib
 

@@ -79,6 +79,11 @@ size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 constexpr int kMinJobsPerPart = 96;  // below this a half batch no longer fills the GPU
 }  // namespace
 
+namespace vb
+{
+int set_last_error(int code, const char * msg) { return fail(code, msg); }
+}  // namespace vb
+
 struct vslamb200_ctx
 {
   int device = 0;

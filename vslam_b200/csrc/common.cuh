@@ -271,6 +271,8 @@ __device__ __forceinline__ int reflect101(int i, int n)
 // ------------------------------------------------------------------------------------------------
 // host-side launchers (each defined next to its kernels)
 // ------------------------------------------------------------------------------------------------
+// api.cu: sets the message vslamb200_last_error() returns (for entry points defined in other files); returns code
+int set_last_error(int code, const char * msg);
 // preprocess.cu
 void launch_ingest(const uint8_t * stagedGray, const void * stagedDepth, int depthType, int layout, int W, int H,
                    const FrameDev * frames, const int * slots, int n, cudaStream_t s);
