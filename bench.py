@@ -2,15 +2,16 @@
 """Benchmark of the dense RGB-D direct-alignment hot path (BASELINE.json metric: aligned frame pairs/sec at
 640x480 RGB-D, 4 pyramid levels).
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--frames F] [--impl ours|reference]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload pairs|sequence] [--pairs P] [--impl ours|reference]
 
-Workload (BASELINE.json configs[1]): a synthetic TUM-shape 640x480 odometry sequence, frame-to-frame
-alignment of every consecutive pair in ONE batched call, LossTDistribution(ScalerTDistribution(nu=5)),
-GaussNewton(1e-7, 100), minGradient 30, 4 levels.  A step = one pass over the whole sequence: pyramid +
-gradients of every frame, then the alignment of all F-1 pairs.  `value` is timed with the raw frames already in
-HBM; `e2e` is the same step through the C ABI with pinned HOST buffers (H2D of all frames and D2H of the poses
-inside the timed region).  Under torchrun every rank runs its own sequence (weak scaling, no data-path
-collective; poses are gathered once with all_gather).
+Default workload (BASELINE.json configs[2], SURVEY.md 8(d)'s throughput configuration): P = 4096 independent synthetic
+640x480 frame pairs (seeds 1234 ... 1234 + P - 1), LossTDistribution(ScalerTDistribution(nu=5)), GaussNewton(1e-7, 100),
+minGradient 30, 4 levels.  A step = one pass over the whole batch: pyramid + gradients of every frame, the alignment of
+every pair in ONE batched call per GPU, and the gather of the poses.  Under torchrun the P pairs are dealt round-robin
+over the ranks (vslam_b200/shard.py: STRONG scaling, no data-path collective); the only exchange is the all_gather of the
+7-double poses over NCCL, inside the timed region.  `value` is timed with the raw frames already in HBM; `e2e` is the
+same step through the C ABI with pinned HOST buffers (H2D of all frames and D2H of the results inside the timed region).
+--workload sequence: BASELINE configs[1], a 1000-frame TUM-shape sequence per GPU, frame to frame (weak scaling, replicas).
 """
 import argparse
 import ctypes as C
@@ -27,16 +28,17 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 W, H, LEVELS = 640, 480, 4
+DEPTH_DIVISOR = 5000.0
 ALGO_BYTES_PER_PIXEL_ITER = 10  # T u8 + dIx s16 + dIy s16 + depth f32 + gathered I u8
 
 
-def load_traffic(frames):
+def load_traffic(workload, pairs_this_gpu):
     """dram__bytes_read.sum + dram__bytes_write.sum of the level-0 launch from the committed ncu --set full capture
-    (profiles/traffic.json); only valid for the batch size it was captured on."""
+    (profiles/traffic.json); only valid for the workload and batch size it was captured on."""
     p = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(p):
         t = json.load(open(p))
-        if t.get("frames") == frames:
+        if t.get("workload") == workload and t.get("pairs_this_gpu") == pairs_this_gpu:
             return t.get("dram_bytes_per_launch")
     return None
 
@@ -105,58 +107,106 @@ def dist_env():
     return rank, world, local
 
 
-def make_jobs(capi, n_frames, id0=0):
-    ident = (C.c_double * 7)(0, 0, 0, 1, 0, 0, 0)
-    n = n_frames - 1
-    jobs = (capi.Job * n)()
-    ids = np.arange(id0, id0 + n_frames, dtype=np.uint64)
-    poses = np.tile(np.array([0, 0, 0, 1, 0, 0, 0], np.float64), (n, 1))
-    for i in range(n):
-        jobs[i].to = id0 + i + 1
+IDENT7 = np.array([0, 0, 0, 1, 0, 0, 0], np.float64)
+WORKLOAD_TEXT = {
+    "pairs": "BASELINE configs[2]: {P} independent synthetic 640x480 frame pairs (seeds 1234..{last}), dealt round-robin over "
+             "the GPUs, t-distribution weights, 4 levels, GaussNewton(1e-7,100), minGradient 30, start at identity",
+    "sequence": "BASELINE configs[1]: synthetic TUM-shape 640x480 sequence of {F} frames per GPU, frame-to-frame alignment "
+                "({P} pairs per batch), t-distribution weights, 4 levels, GaussNewton(1e-7,100), minGradient 30",
+}
+
+
+def render_pairs(synth, indices, cam):
+    """Frames of the independent pairs `indices` (pair k: seed 1234 + k), stored ref, cur, ref, cur, ...; ground truth."""
+    m = len(indices)
+    gray = np.empty((2 * m, H, W), np.uint8)
+    depth = np.empty((2 * m, H, W), np.float32)
+    gt = np.empty((m, 7))
+    for j, k in enumerate(indices):
+        p = synth.make_pair(W, H, 1234 + int(k), cam=cam)
+        gray[2 * j], gray[2 * j + 1] = p["gray0"], p["gray1"]
+        depth[2 * j], depth[2 * j + 1] = p["depth0"], p["depth1"]
+        gt[j] = p["pose1"]
+    return gray, depth, gt
+
+
+def quantise_depth(depth):
+    """Sensor depth: 16-bit in units of 1 / 5000 m; returned as the f32 the aligners consume."""
+    k16 = np.clip(np.rint(depth.astype(np.float64) * DEPTH_DIVISOR), 0, 65535).astype(np.uint16)
+    return (k16.astype(np.float64) / DEPTH_DIVISOR).astype(np.float32)
+
+
+def make_jobs(capi, n_jobs, stride, id0=0):
+    """Job i aligns frame id0 + i * stride + 1 against frame id0 + i * stride, both starting at identity."""
+    ident = (C.c_double * 7)(*IDENT7)
+    jobs = (capi.Job * n_jobs)()
+    ids = np.arange(id0, id0 + n_jobs * stride + 2, dtype=np.uint64)
+    poses = np.tile(IDENT7, (n_jobs, 1))
+    for i in range(n_jobs):
+        jobs[i].to = id0 + i * stride + 1
         jobs[i].to_pose = ident
         jobs[i].n_from = 1
         jobs[i].multi = 0
-        jobs[i].from_ = C.cast(ids[i:].ctypes.data, C.POINTER(C.c_uint64))
+        jobs[i].from_ = C.cast(ids[i * stride:].ctypes.data, C.POINTER(C.c_uint64))
         jobs[i].from_poses = C.cast(poses[i:].ctypes.data, C.POINTER(C.c_double))
     return jobs, (ids, poses)
 
 
-def cpu_leg(n_pairs, threads, gray, depth, cam):
-    """Times the CPU oracle (frame preparation + alignment) on the first n_pairs pairs."""
+def result_poses(capi, results, n):
+    """(n, 7) poses out of a ctypes Result array, without a Python loop."""
+    raw = np.frombuffer(results, dtype=np.uint8).reshape(len(results), C.sizeof(capi.Result))
+    return raw[:n, :56].copy().view(np.float64).reshape(n, 7)
+
+
+def cpu_leg(n_pairs, threads, gray, depth, cam, stride):
+    """Times the CPU oracle (frame preparation + alignment) on the first n_pairs pairs of the frame array."""
     from oracle import oracle as O
     O.build()
     cfg = O.make_config()  # tdist / tdist nu=5, GaussNewton(1e-7,100), minGradient 30, prior off
     t0 = time.perf_counter()
-    poses, iters = O.baseline_sequence(cfg, gray[:n_pairs + 1], depth[:n_pairs + 1], *cam, LEVELS, threads)
+    poses, iters = O.baseline_batch(cfg, gray, depth, *cam, LEVELS, threads, stride=stride, n_pairs=n_pairs)
     dt = time.perf_counter() - t0
     return n_pairs / dt, dt, poses, iters
 
 
+REFERENCE_SAMPLE_PAIRS = 128  # the same sample on every box (the CPU arm's value is per pair)
+
+
 def run_reference(args, rank, world):
-    """--impl reference: the reference's CPU aligner (oracle port; the reference itself cannot be built in this
-    image) on the host cores, all threads, on a bounded sample of the same workload per step."""
+    """--impl reference: the reference's CPU aligner on the host cores (the oracle port: the reference itself cannot be
+    built in this image - see DESIGN.md), all threads, on a bounded, FIXED sample of the same workload per step: the
+    first 128 pairs.  The 1-core figure (the reference aligner is single-threaded) is measured once on 8 pairs."""
     if rank != 0:
         return
     from vslam_b200 import synth
     threads = os.cpu_count() or 1
-    n_pairs = max(4 * threads, 16)
+    n_pairs = REFERENCE_SAMPLE_PAIRS
     cam = synth.cam_for(W, H)
-    gray, depth, _ = synth.make_sequence(n_pairs + 1, W, H, seed=1234, cam=cam)
+    if args.workload == "pairs":
+        gray, depth, _ = render_pairs(synth, range(n_pairs), cam)
+        stride = 2
+    else:
+        gray, depth, _ = synth.make_sequence(n_pairs + 1, W, H, seed=1234, cam=cam)
+        stride = 1
+    depth = quantise_depth(depth)
     for _ in range(args.warmup):
-        cpu_leg(min(n_pairs, threads), threads, gray, depth, cam)
+        cpu_leg(min(n_pairs, max(threads, 8)), threads, gray, depth, cam, stride)
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        cpu_leg(n_pairs, threads, gray, depth, cam)
+        cpu_leg(n_pairs, threads, gray, depth, cam, stride)
     dt = time.perf_counter() - t0
     v = n_pairs * args.steps / dt
-    sample = f"first {n_pairs} pairs of the {args.frames}-frame sequence per step, pair-parallel OpenMP"
+    v1, dt1, _, _ = cpu_leg(8, 1, gray, depth, cam, stride)
+    P = args.pairs if args.workload == "pairs" else args.frames - 1
+    text = WORKLOAD_TEXT[args.workload].format(P=P, last=1234 + P - 1, F=args.frames)
+    sample = f"the first {n_pairs} pairs of the workload per step, pair-parallel OpenMP over {threads} threads"
     print(json.dumps({
         "impl": "reference", "metric": "aligned frame pairs/sec at 640x480 RGB-D", "value": v, "unit": "pairs/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": f"synthetic TUM-shape 640x480 sequence, frame-to-frame, t-distribution weights, "
-                               f"{LEVELS} levels (sample of {n_pairs} pairs)"},
-        "cpu_baseline": {"value": v, "unit": "pairs/s", "cores": threads, "kind": "port", "sample": sample},
+        "higher_is_better": True, "scaling": "strong" if args.workload == "pairs" else "weak", "vs_baseline": None,
+        "dtype": "f64", "data": "synthetic", "config": {"workload": text},
+        "cpu_baseline": {"value": v, "unit": "pairs/s", "cores": threads, "kind": "port", "sample": sample,
+                         "one_core": {"value": v1, "pairs": 8, "seconds": dt1}},
         "e2e": {"value": v, "unit": "pairs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }))
 
@@ -166,20 +216,21 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--frames", type=int, default=1000)
+    ap.add_argument("--workload", choices=["pairs", "sequence"], default="pairs")
+    ap.add_argument("--pairs", type=int, default=4096, help="pairs workload: pairs of the whole job (all GPUs together)")
+    ap.add_argument("--frames", type=int, default=1000, help="sequence workload: frames per GPU")
     ap.add_argument("--impl", default="ours")
-    ap.add_argument("--cpu-pairs", type=int, default=32, help="pairs timed on the host cores for cpu_baseline")
+    ap.add_argument("--cpu-pairs", type=int, default=32, help="pairs timed on ONE host core for cpu_baseline")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--distinct-sequences", action="store_true",
-                    help="every rank renders its own sequence (seed 1234 + rank) instead of the same one; the sequences "
-                         "differ in Gauss-Newton iteration count by up to 30 %, so the per-GPU work is then not fixed")
+                    help="sequence workload: every rank renders its own sequence (seed 1234 + rank) instead of the same one")
     args = ap.parse_args()
     rank, world, local = dist_env()
     if args.impl == "reference":
         return run_reference(args, rank, world)
 
     import torch
-    from vslam_b200 import build, capi, synth
+    from vslam_b200 import build, capi, shard, synth
     if not os.path.exists(capi.LIB_PATH):
         build.build_all()
     if not torch.cuda.is_available():
@@ -190,47 +241,70 @@ def main():
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
-    F = args.frames
     cam = synth.cam_for(W, H)
-    # weak scaling = fixed work per GPU: every rank aligns the same sequence (the result gather still moves every rank's
-    # poses).  Sequences rendered from different seeds need different numbers of Gauss-Newton iterations (measured: rank
-    # 3's takes 27 % longer than rank 0's on identical GPUs), which would time the data instead of the scaling.
-    gray, depth, gt = synth.make_sequence(F, W, H, seed=1234 + (rank if args.distinct_sequences else 0), cam=cam)
+    if args.workload == "pairs":
+        P = args.pairs
+        mine = shard.deal_pairs(P, world, rank)           # strong scaling: the P pairs are dealt over the ranks
+        gray, depth, gt = render_pairs(synth, mine, cam)
+        n_jobs, stride, n_frames = len(mine), 2, 2 * len(mine)
+        pairs_per_step, scaling, cap = P, "strong", (P + world - 1) // world
+        text = WORKLOAD_TEXT["pairs"].format(P=P, last=1234 + P - 1)
+    else:
+        F = args.frames
+        gray, depth, _ = synth.make_sequence(F, W, H, seed=1234 + (rank if args.distinct_sequences else 0), cam=cam)
+        gt, mine = None, np.arange(F - 1)
+        n_jobs, stride, n_frames = F - 1, 1, F
+        pairs_per_step, scaling, cap = (F - 1) * world, "weak", F - 1
+        text = WORKLOAD_TEXT["sequence"].format(P=F - 1, F=F)
+    # The frames are what an RGB-D sensor delivers: 8-bit grey and 16-bit depth in units of 1 / 5000 m (the TUM convention,
+    # test_alignment_se3.cpp:99).  The resident leg and the CPU oracle get the same values as f32 (k / 5000.0 in double,
+    # narrowed), the end-to-end leg ships the 16-bit planes and converts on the device.
+    k16 = np.clip(np.rint(depth.astype(np.float64) * DEPTH_DIVISOR), 0, 65535).astype(np.uint16)
+    depth = (k16.astype(np.float64) / DEPTH_DIVISOR).astype(np.float32)
     h_gray = torch.from_numpy(gray).pin_memory()
-    h_depth = torch.from_numpy(depth).pin_memory()
+    h_k16 = torch.from_numpy(k16.view(np.int16)).pin_memory()
     d_gray = h_gray.cuda()
-    d_depth = h_depth.cuda()
-    ids = np.arange(F, dtype=np.uint64)
-    cams = np.tile(np.array(cam, np.float64), (F, 1))
+    d_depth = torch.from_numpy(depth).cuda()
+    ids = np.arange(n_frames, dtype=np.uint64)
+    cams = np.tile(np.array(cam, np.float64), (n_frames, 1))
     ctx = capi.Context(capi.make_config(), device=local)
     stream = torch.cuda.Stream()
     capi.check(capi.lib().vslamb200_set_stream(ctx.h, C.c_void_p(stream.cuda_stream)))
-    jobs, _keep = make_jobs(capi, F)
-    results = (capi.Result * (F - 1))()
+    jobs, _keep = make_jobs(capi, n_jobs, stride)
+    results = (capi.Result * n_jobs)()
+    # the only collective of the path: every rank's poses (7 f64 per pair, shards padded to the largest one), all_gather
+    # over NCCL on the alignment's stream, inside the timed region
+    d_mine = torch.zeros((cap, 7), dtype=torch.float64, device="cuda")
+    d_all = torch.zeros((world * cap, 7), dtype=torch.float64, device="cuda")
+
+    def gather():
+        if use_dist:
+            d_mine[:n_jobs].copy_(torch.from_numpy(result_poses(capi, results, n_jobs)))
+            dist.all_gather_into_tensor(d_all, d_mine)
 
     def step_resident():
-        ctx.upload_device(ids, d_gray.data_ptr(), d_depth.data_ptr(), F, W, H, cams, LEVELS)
-        ctx.align_raw(jobs, F - 1, results)
+        ctx.upload_device(ids, d_gray.data_ptr(), d_depth.data_ptr(), n_frames, W, H, cams, LEVELS)
+        ctx.align_raw(jobs, n_jobs, results)
+        gather()
 
     # End to end through the C ABI with pinned HOST buffers.  Successive steps (batches) alternate between two sets of
     # frame ids: the upload of the next step's frames (copy stream) is queued before this step's alignment is called, so
-    # in steady state the PCIe transfer hides under the kernels.  Every step's upload, including the first one, and
-    # every step's result read-back are inside the timed region.
-    ids2 = [ids, ids + np.uint64(F)]
-    jobs2, keep2 = [jobs], [_keep]
-    j1, k1 = make_jobs(capi, F, id0=F)
-    jobs2.append(j1)
-    keep2.append(k1)
+    # in steady state the PCIe transfer hides under the kernels.  Every step's upload, including the first one, every
+    # step's result read-back and every step's gather are inside the timed region.
+    ids2 = [ids, ids + np.uint64(n_frames)]
+    j1, k1 = make_jobs(capi, n_jobs, stride, id0=n_frames)
+    jobs2, _keep2 = [jobs, j1], [_keep, k1]
 
     def upload_set(q):
-        ctx.upload_async(ids2[q], h_gray.data_ptr(), h_depth.data_ptr(), F, W, H, cams, LEVELS)
+        ctx.upload_u16_async(ids2[q], h_gray.data_ptr(), h_k16.data_ptr(), DEPTH_DIVISOR, n_frames, W, H, cams, LEVELS)
 
     def run_e2e(steps):
         upload_set(0)
         for st_ in range(steps):
             if st_ + 1 < steps:
                 upload_set((st_ + 1) & 1)
-            ctx.align_raw(jobs2[st_ & 1], F - 1, results)
+            ctx.align_raw(jobs2[st_ & 1], n_jobs, results)
+            gather()
 
     def timed(fn, steps, loop=True):
         if use_dist:
@@ -253,8 +327,9 @@ def main():
             dist.barrier()
         return float(ms.item())
 
-    for _ in range(args.warmup):
-        step_resident()
+    with torch.cuda.stream(stream):
+        for _ in range(args.warmup):
+            step_resident()
     sampler = ClockSampler(local)
     sampler.start()
     ctx.reset_stats()
@@ -262,111 +337,136 @@ def main():
     own_ms = timed.own_ms
     st = ctx.stats()
     clocks = sampler.stop()
-    pairs = (F - 1) * args.steps * world
-    value = pairs / (ms * 1e-3)
+    value = pairs_per_step * args.steps / (ms * 1e-3)
+    resident_poses = result_poses(capi, results, n_jobs)
+    all_poses = d_all.cpu().numpy() if use_dist else None
 
-    # end to end through the C ABI with host buffers
-    resident_poses = np.array([list(r.pose) for r in results])
-    run_e2e(2)
+    # end to end through the C ABI with host buffers (the raw device copies of the resident leg are no longer needed)
+    del d_gray, d_depth
+    torch.cuda.empty_cache()
+    with torch.cuda.stream(stream):
+        run_e2e(2)
     ms_e2e = timed(run_e2e, args.steps, loop=False)
-    e2e_diff = float(np.abs(np.array([list(r.pose) for r in results]) - resident_poses).max())
-    e2e = pairs / (ms_e2e * 1e-3)
-    h2d = F * W * H * 5
-    d2h = (F - 1) * C.sizeof(capi.Result)
+    e2e_diff = float(np.abs(result_poses(capi, results, n_jobs) - resident_poses).max())
+    e2e = pairs_per_step * args.steps / (ms_e2e * 1e-3)
+    h2d = n_frames * W * H * 3  # u8 grey + u16 depth
+    d2h = n_jobs * C.sizeof(capi.Result)
 
-    # p50 / p95 latency of ONE alignment (BASELINE.json metric, second half): batch size 1, the first pair
-    # of the sequence (frames resident), back-to-back calls, wall time from the host's submit to the result on the host
+    # p50 / p95 latency of ONE alignment (BASELINE.json metric, second half): batch size 1, this rank's first
+    # pair (frames resident), back-to-back calls, wall time from the host's submit to the result on the host
     lat = None
     if rank == 0:
         one = (capi.Result * 1)()
         for _ in range(50):
-            ctx.align_raw(jobs, 1, one)
+            ctx.align_raw(jobs2[(args.steps - 1) & 1], 1, one)
         ts = []
         for _ in range(300):
             t0 = time.perf_counter()
-            ctx.align_raw(jobs, 1, one)
+            ctx.align_raw(jobs2[(args.steps - 1) & 1], 1, one)
             ts.append((time.perf_counter() - t0) * 1e3)
         # a single job runs on larger clusters than a throughput batch (latency mode), so its sums are added in another
         # order: the same pose up to rounding, not bit for bit
-        lat_diff = float(np.max(np.abs(np.array(list(one[0].pose)) - np.array(list(resident_poses[0])))))
+        lat_diff = float(np.max(np.abs(np.array(list(one[0].pose)) - resident_poses[0])))
         assert lat_diff < 1e-9, "single-pair call differs from the batched result"
-        lat = {"p50_ms": float(np.percentile(ts, 50)), "p95_ms": float(np.percentile(ts, 95)), "calls": len(ts), "max_pose_diff_vs_batched": lat_diff,
+        lat = {"p50_ms": float(np.percentile(ts, 50)), "p95_ms": float(np.percentile(ts, 95)), "calls": len(ts),
+               "max_pose_diff_vs_batched": lat_diff,
                "what": "one 640x480 pair, 4 levels, frames resident, host submit -> pose on host"}
 
-    # per-kernel timing pass (events around every residual / accumulate launch; separate from the timed runs)
+    # per-kernel timing pass (events around every level launch; separate from the timed runs, one stream)
     capi.check(capi.lib().vslamb200_set_timing(ctx.h, 1))
     ctx.reset_stats()
-    step_resident()
+    ctx.align_raw(jobs2[(args.steps - 1) & 1], n_jobs, results)
     tst = ctx.stats()
     capi.check(capi.lib().vslamb200_set_timing(ctx.h, 0))
     peak, peak_kind = load_peaks()
-    # dominant kernel: gn_level_kernel at level 0 (one launch per step); algorithmic bytes = 10 B per template pixel
-    # and Gauss-Newton evaluation x the pixel-evaluations that launch processed
+    # dominant kernel: gn_level_kernel at level 0 (one launch per step and GPU); algorithmic bytes = 10 B per template
+    # pixel and Gauss-Newton evaluation x the pixel-evaluations that launch processed
     l0_ms = tst["ms_gn_level"][0]
     l0_bytes = ALGO_BYTES_PER_PIXEL_ITER * tst["pixel_iterations_level"][0]
     all_ms = sum(tst["ms_gn_level"])
     achieved = l0_bytes / (l0_ms * 1e-3) / 1e9 if l0_ms > 0 else 0.0
+    traffic = load_traffic(args.workload, n_jobs)
     roofline = {
-        "bound": "hbm", "kernel": "gn_level_kernel (level 0: all Gauss-Newton iterations of 640x480 for the batch)",
+        "bound": "hbm", "kernel": "gn_level_kernel (level 0: all Gauss-Newton iterations of 640x480 for this GPU's share of the batch)",
         "achieved": achieved, "peak": peak, "peak_kind": peak_kind, "unit": "GB/s", "frac": achieved / peak,
-        "traffic": load_traffic(F),
+        "traffic": traffic, "traffic_over_algorithmic": (traffic / l0_bytes) if traffic and l0_bytes else None,
         "algorithmic_bytes_per_launch": l0_bytes, "ms_per_launch": l0_ms,
         "all_levels": {"ms": tst["ms_gn_level"][:LEVELS], "pixel_iterations": tst["pixel_iterations_level"][:LEVELS],
                        "achieved": ALGO_BYTES_PER_PIXEL_ITER * tst["pixel_iterations"] / (all_ms * 1e-3) / 1e9 if all_ms > 0 else 0.0},
-        "ms_lists": tst["ms_lists"],
-        "point_iterations": tst["point_iterations"],
+        "ms_lists": tst["ms_lists"], "point_iterations": tst["point_iterations"],
         "interest_density": tst["point_iterations"] / max(1, tst["pixel_iterations"]),
+        "level_kernel_launches": {"dense": int(tst["dense_launches"]), "moments": int(tst["moment_launches"])},
     }
-    iters_per_pair = np.mean([sum(r.iters[:LEVELS]) for r in results])
+    iters_per_pair = float(np.mean([sum(r.iters[:LEVELS]) for r in results]))
+    assert all(r.status == 0 and sum(r.iters[:LEVELS]) > 0 for r in results), "a job did not run"
 
     ranks = None
     if use_dist:
-        # per-rank step time, clocks and throttle reasons (the reported time is the maximum over the ranks)
+        # per-rank step time, work, clocks and throttle reasons (the reported time is the maximum over the ranks)
         ranks = [None] * world
-        dist.all_gather_object(ranks, {"rank": rank, "ms_per_step": own_ms / args.steps, "sm_mhz": clocks.get("sm_mhz"),
-                                       "reasons": clocks.get("reasons"),
+        dist.all_gather_object(ranks, {"rank": rank, "pairs": n_jobs, "ms_per_step": own_ms / args.steps,
+                                       "gn_iterations": int(st["gn_iterations"] // max(1, args.steps)),
+                                       "sm_mhz": clocks.get("sm_mhz"), "reasons": clocks.get("reasons"),
                                        "ms_gn_level": [round(x, 3) for x in tst["ms_gn_level"][:LEVELS]],
-                                       "ms_lists": round(tst["ms_lists"], 3), "ms_preprocess": round(tst["ms_preprocess"], 3)})
-        # the only collective of the path: gather the poses (7 f64 per pair) of every rank
-        mine = torch.tensor([list(r.pose) for r in results], device="cuda", dtype=torch.float64)
-        allp = [torch.empty_like(mine) for _ in range(world)]
-        dist.all_gather(allp, mine)
+                                       "ms_lists": round(tst["ms_lists"], 3)})
+
+    checks = {}
+    if rank == 0 and args.workload == "pairs":
+        # every pair of the whole batch (all ranks: the gathered array) recovers its ground-truth motion to the accuracy
+        # the reference's own alignment tests ask for (test_alignment_se3.cpp:119: 0.01)
+        from oracle import oracle as O
+        allp = resident_poses if not use_dist else np.stack(
+            [all_poses[(k % world) * cap + k // world] for k in range(args.pairs)])
+        errs = np.empty(args.pairs)
+        for k in range(args.pairs):
+            xi = synth.pair_twist(1234 + k)
+            Rk, tk = synth.se3_exp(xi)
+            d = O.se3_log(O.se3_mul(allp[k], O.se3_inv(synth.pose7(Rk, tk))))
+            errs[k] = max(float(np.linalg.norm(d[:3])), float(np.linalg.norm(d[3:])))
+        # (a Gauss-Newton run can stop in a local minimum; whether the GPU's answer is the reference algorithm's answer is
+        # what the comparison with the CPU oracle below and the parity tests check)
+        checks["error_vs_ground_truth"] = {"max": float(errs.max()), "median": float(np.median(errs)),
+                                           "pairs_within_0.01": int((errs < 0.01).sum()), "pairs": int(args.pairs),
+                                           "worst_pair": int(errs.argmax())}
+        assert (errs < 0.01).mean() > 0.99, checks
 
     cpu = None
     if rank == 0 and not args.no_cpu:
-        v1, dt1, cposes, _ = cpu_leg(args.cpu_pairs, 1, gray, depth, cam)
-        thr = os.cpu_count() or 1
-        vN, dtN, _, _ = cpu_leg(max(args.cpu_pairs, thr), thr, gray, depth, cam)
         from oracle import oracle as O
-        perr = max(np.linalg.norm(O.se3_log(O.se3_mul(np.array(results[i].pose), O.se3_inv(cposes[i]))))
-                   for i in range(args.cpu_pairs))
-        # spot checks across the whole batch (middle and last pair) against the oracle, and every job must have iterated
-        for m in ((F - 1) // 2, F - 2):
-            pm, _ = O.baseline_sequence(O.make_config(), gray[m:m + 2], depth[m:m + 2], *cam, LEVELS, 1)
-            perr = max(perr, np.linalg.norm(O.se3_log(O.se3_mul(np.array(results[m].pose), O.se3_inv(pm[0])))))
-        assert all(r.status == 0 and sum(r.iters[:LEVELS]) > 0 for r in results), "a job did not run"
+        v1, dt1, _, _ = cpu_leg(args.cpu_pairs, 1, gray, depth, cam, stride)
+        thr = os.cpu_count() or 1
+        nN = min(n_jobs, REFERENCE_SAMPLE_PAIRS)
+        vN, dtN, cposes, citers = cpu_leg(nN, thr, gray, depth, cam, stride)
+        # The GPU's results for the CPU sample: the same iteration counts per level and the same pose.  A pair may differ
+        # where GaussNewton.cpp:70's test "chi2 increased" meets an exact tie (unchanged residual histogram: the GPU's
+        # histogram-based chi2 is then bit-identical, a point-order sum differs in the last bit and stops one step
+        # earlier) - such pairs are counted, not hidden
+        same = [list(results[i].iters[:LEVELS]) == list(citers[i]) for i in range(nN)]
+        perr = max([np.linalg.norm(O.se3_log(O.se3_mul(resident_poses[i], O.se3_inv(cposes[i])))) for i in range(nN) if same[i]] + [0.0])
+        ties = [int(mine[i]) for i in range(nN) if not same[i]]
+        assert perr < 1e-4 and len(ties) <= max(1, nN // 50), (perr, ties)
         cpu = {"value": v1, "unit": "pairs/s", "cores": 1, "kind": "port",
-               "sample": f"first {args.cpu_pairs} pairs of the sequence, frame preparation included ({dt1:.1f} s)",
-               "all_cores": {"value": vN, "cores": thr, "pairs": max(args.cpu_pairs, thr)},
-               "max_pose_diff_vs_gpu": perr}
+               "sample": f"this GPU's first {args.cpu_pairs} pairs, frame preparation included ({dt1:.1f} s)",
+               "all_cores": {"value": vN, "cores": thr, "pairs": nN, "seconds": dtN},
+               "max_pose_diff_vs_gpu": float(perr), "pairs_checked": nN, "pairs_with_equal_iteration_counts": int(sum(same)),
+               "chi2_tie_pairs": ties}
     if rank == 0:
         print(json.dumps({
             "metric": "aligned frame pairs/sec at 640x480 RGB-D", "value": value, "unit": "pairs/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
-            "data": "synthetic",
-            "config": {"workload": f"synthetic TUM-shape 640x480 sequence of {F} frames per GPU, frame-to-frame "
-                                   f"alignment ({F - 1} pairs per batch), t-distribution weights, {LEVELS} levels, "
-                                   "GaussNewton(1e-7,100), minGradient 30",
-                       "sequences": ("one per rank, seeds 1234 + rank" if args.distinct_sequences else
-                                     "the same sequence (seed 1234) on every rank: fixed work per GPU"),
-                       "l2_policy": "inputs (1.5 GB of frames per step) are larger than the 126 MB L2",
-                       "mean_gn_iterations_per_pair": float(iters_per_pair)},
+            "higher_is_better": True, "scaling": scaling, "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": text, "pairs_per_step": pairs_per_step, "pairs_this_gpu": n_jobs,
+                       "collective": ("all_gather of the poses (7 f64 per pair) over NCCL, inside the timed region"
+                                      if use_dist else "none (one GPU)"),
+                       "l2_policy": f"inputs ({n_frames * W * H * 5 / 1e9:.1f} GB of level-0 planes per step and GPU) are larger than the 126 MB L2",
+                       "mean_gn_iterations_per_pair": iters_per_pair},
             "e2e": {"value": e2e, "unit": "pairs/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": ms_e2e / args.steps, "max_pose_diff_vs_resident": e2e_diff,
-                    "pipeline": "upload of step s+1 (copy stream) overlaps the alignment of step s; all uploads timed"},
+                    "pipeline": "host frames are u8 grey + u16 depth (3 B per pixel, vslamb200_frames_upload_u16_async); "
+                                "the upload of step s+1 (copy stream) overlaps the alignment of step s; all uploads timed; "
+                                "bytes are per GPU"},
             "gpu_launches": int(st["kernel_launches"]),
-            "latency": lat, "clocks": clocks, "ranks": ranks, "roofline": roofline, "cpu_baseline": cpu,
+            "latency": lat, "clocks": clocks, "ranks": ranks, "roofline": roofline, "cpu_baseline": cpu, "checks": checks,
         }))
     ctx.close()
     if use_dist:

@@ -151,6 +151,12 @@ int vslamb200_frames_upload(
 int vslamb200_frames_upload_async(
   vslamb200_ctx * ctx, int n, const uint64_t * ids, int width, int height, const uint8_t * gray, size_t gray_stride,
   const void * depth, int depth_type, size_t depth_stride, int layout, const double * cams, int n_levels);
+/* vslamb200_frames_upload_async for what an RGB-D sensor delivers: row-major 8-bit grey and 16-bit depth, tightly packed,
+ * depth = value / depth_divisor in double (loadDepth(...) / 5000.0, odometry/test/test_alignment_se3.cpp:99; 0 = no
+ * measurement).  3 bytes per pixel cross the bus instead of 5; the conversion runs on the device behind the copy. */
+int vslamb200_frames_upload_u16_async(
+  vslamb200_ctx * ctx, int n, const uint64_t * ids, int width, int height, const uint8_t * gray, const uint16_t * depth,
+  double depth_divisor, const double * cams, int n_levels);
 /* same as vslamb200_frames_upload, gray / depth already resident on the context's device (row-major u8 / f32) */
 int vslamb200_frames_upload_device(
   vslamb200_ctx * ctx, int n, const uint64_t * ids, int W, int H, const uint8_t * d_gray, const float * d_depth,

@@ -9,6 +9,13 @@ import pytest
 
 pytestmark = pytest.mark.gpu
 
+import ctypes as _C
+
+
+def C_void(p):
+    return _C.c_void_p(p)
+
+
 NE_TOL = 1e-4
 POSE_TOL = 1e-4
 
@@ -517,6 +524,44 @@ def test_async_upload_pipeline_is_identical_to_the_synchronous_path(capi, oracle
         f1 = oracle.Frame(gray[1], depth[1].astype(np.float64), *cam, L)
         assert np.array_equal(lv["I"], f1.level(1)["I"])
         ctx.synchronize()
+    finally:
+        ctx.close()
+
+
+@pytest.mark.gpu
+def test_u16_depth_async_upload_matches_the_reference_ingestion(capi, oracle, synth):
+    """vslamb200_frames_upload_u16_async: 16-bit sensor depth / 5000 (test_alignment_se3.cpp:99) converted on the device;
+    every pyramid level equals the oracle's frame built from oracle.depth_ingest of the same values, the alignment is
+    bit-identical to uploading the converted f32 depth, and a second upload re-uses the staging buffer."""
+    import torch
+    F, W, H, L = 5, 320, 240, 3
+    cam = synth.cam_for(W, H)
+    gray, depth, _ = synth.make_sequence(F, W, H, seed=21, cam=cam)
+    k16 = np.clip(np.rint(depth.astype(np.float64) * 5000.0), 0, 65535).astype(np.uint16)
+    k16[:, 50:60, 70:90] = 0  # no measurement
+    d32 = np.stack([oracle.depth_ingest(k16[i], 5000.0) for i in range(F)]).astype(np.float32)
+    assert np.array_equal(d32, (k16.astype(np.float64) / 5000.0).astype(np.float32))
+    ident = oracle.IDENTITY
+    jobs = [dict(to=i + 1, to_pose=ident, frm=[i], from_poses=ident, multi=False) for i in range(F - 1)]
+    ctx = capi.Context(capi.make_config(max_iterations=30))
+    try:
+        ctx.upload(np.arange(F), gray, d32, cam, L)
+        want = ctx.align(jobs)
+        hg = torch.from_numpy(gray).pin_memory()
+        hk = torch.from_numpy(k16.view(np.int16)).pin_memory()
+        for rep in range(2):
+            ctx.upload_u16_async(np.arange(F), hg.data_ptr(), hk.data_ptr(), 5000.0, F, W, H, cam, L)
+            got = ctx.align(jobs)
+            for a, b in zip(got, want):
+                assert np.array_equal(a["pose"], b["pose"]) and list(a["iters"]) == list(b["iters"])
+        for i in (0, F - 1):
+            fr = oracle.Frame(gray[i], d32[i].astype(np.float64), *cam, L)
+            for l in range(L):
+                lv, ref = ctx.download(i, l), fr.level(l)
+                assert np.array_equal(lv["Z"].astype(np.float64), ref["Z"]) and np.array_equal(lv["I"], ref["I"])
+        assert capi.lib().vslamb200_frames_upload_u16_async(ctx.h, 1, capi.ptr(np.arange(1, dtype=np.uint64)), W, H,
+                                                            C_void(hg.data_ptr()), C_void(hk.data_ptr()), 0.0,
+                                                            capi.ptr(np.array(cam, np.float64)), L) == -1
     finally:
         ctx.close()
 

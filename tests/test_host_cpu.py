@@ -104,6 +104,38 @@ def test_pair_ranges_partition_the_sequence():
         shard.pair_range(10, 2, 2)
 
 
+def test_dealt_pairs_partition_the_batch():
+    from vslam_b200 import shard
+    for n in (0, 1, 7, 8, 4096):
+        for world in (1, 2, 3, 8):
+            got = [shard.deal_pairs(n, world, r) for r in range(world)]
+            assert sorted(np.concatenate(got).tolist()) == list(range(n))
+            assert max(len(g) for g in got) - min(len(g) for g in got) <= 1
+    with pytest.raises(ValueError):
+        shard.deal_pairs(10, 2, -1)
+
+
+def test_oracle_batch_of_independent_pairs_matches_single_alignments(oracle, synth):
+    """vo_baseline_batch (the CPU arm of bench.py) against oracle.align pair by pair, stride 2 and stride 1."""
+    O = oracle
+    W, H, L = 96, 64, 2
+    pairs = [synth.make_pair(W, H, 1234 + k) for k in range(3)]
+    gray = np.stack([x for p in pairs for x in (p["gray0"], p["gray1"])])
+    depth = np.stack([x for p in pairs for x in (p["depth0"], p["depth1"])])
+    cam = pairs[0]["cam"]
+    cfg = O.make_config(max_iterations=20)
+    poses, iters = O.baseline_batch(cfg, gray, depth, *cam, L, n_threads=2, stride=2)
+    assert poses.shape == (3, 7) and iters.shape == (3, L)
+    for k, p in enumerate(pairs):
+        f0 = O.Frame(p["gray0"], p["depth0"].astype(np.float64), *cam, L)
+        f1 = O.Frame(p["gray1"], p["depth1"].astype(np.float64), *cam, L)
+        ref = O.align(cfg, f0, O.IDENTITY, f1, O.IDENTITY)
+        assert np.array_equal(poses[k], ref["pose"]) and list(iters[k]) == list(ref["iters"])
+    seq, _ = O.baseline_sequence(cfg, gray, depth, *cam, L, 1)
+    p1, _ = O.baseline_batch(cfg, gray, depth, *cam, L, n_threads=1, stride=1)
+    assert np.array_equal(seq, p1)
+
+
 def test_chain_trajectory_composes_relative_motions(oracle):
     from vslam_b200 import shard
     rng = np.random.default_rng(3)
@@ -130,6 +162,11 @@ lo, hi = shard.pair_range(n_pairs, world, rank)
 local = np.stack([fake_pose(i) for i in range(lo, hi)]) if hi > lo else np.zeros((0, 7))
 allp = shard.gather_poses(local, n_pairs, dist)
 want = np.stack([fake_pose(i) for i in range(n_pairs)])
+assert allp.shape == (n_pairs, 7) and np.array_equal(allp, want), rank
+# independent pairs dealt round-robin (BASELINE configs[2])
+mine = shard.deal_pairs(n_pairs, world, rank)
+local = np.stack([fake_pose(i) for i in mine]) if len(mine) else np.zeros((0, 7))
+allp = shard.gather_dealt(local, n_pairs, dist)
 assert allp.shape == (n_pairs, 7) and np.array_equal(allp, want), rank
 dist.barrier()
 dist.destroy_process_group()

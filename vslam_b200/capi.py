@@ -58,7 +58,7 @@ EXPORTS = [
     "vslamb200_frame_release_all", "vslamb200_frame_dims", "vslamb200_frame_download", "vslamb200_align",
     "vslamb200_set_trace", "vslamb200_get_trace", "vslamb200_evaluate", "vslamb200_get_stats",
     "vslamb200_reset_stats", "vslamb200_set_timing", "vslamb200_synchronize", "vslamb200_frames_upload_async",
-    "vslamb200_interest_points_noalloc",
+    "vslamb200_interest_points_noalloc", "vslamb200_frames_upload_u16_async",
 ]
 NOALLOC_MAX_PIXELS = 4096 * 4096
 
@@ -87,6 +87,7 @@ def lib():
         L.vslamb200_set_stream.argtypes = [vp, vp]
         L.vslamb200_frames_upload.argtypes = [vp, i, vp, i, i, vp, sz, vp, i, sz, i, vp, i]
         L.vslamb200_frames_upload_async.argtypes = [vp, i, vp, i, i, vp, sz, vp, i, sz, i, vp, i]
+        L.vslamb200_frames_upload_u16_async.argtypes = [vp, i, vp, i, i, vp, vp, C.c_double, vp, i]
         L.vslamb200_frames_upload_device.argtypes = [vp, i, vp, i, i, vp, vp, vp, i]
         L.vslamb200_frames_ingest_rgbd.argtypes = [vp, i, vp, i, i, vp, i, vp, i, C.c_double, vp, i]
         L.vslamb200_frame_release.argtypes = [vp, u64]
@@ -178,6 +179,14 @@ class Context:
         cams = np.ascontiguousarray(np.broadcast_to(np.asarray(cams, np.float64).reshape(-1, 4), (n, 4)))
         check(lib().vslamb200_frames_upload_async(self.h, n, ptr(ids), W, H, C.c_void_p(gray_ptr), 0,
                                                   C.c_void_p(depth_ptr), DEPTH_F32, 0, ROW_MAJOR, ptr(cams), n_levels))
+
+    def upload_u16_async(self, ids, gray_ptr, depth_u16_ptr, depth_divisor, n, W, H, cams, n_levels):
+        """Queues the upload of n row-major u8 grey / u16 depth frames (depth = value / depth_divisor) from (pinned) host
+        memory and returns; the buffers must stay untouched until the next align() / synchronize()."""
+        ids = np.ascontiguousarray(np.atleast_1d(ids), np.uint64)
+        cams = np.ascontiguousarray(np.broadcast_to(np.asarray(cams, np.float64).reshape(-1, 4), (n, 4)))
+        check(lib().vslamb200_frames_upload_u16_async(self.h, n, ptr(ids), W, H, C.c_void_p(gray_ptr), C.c_void_p(depth_u16_ptr),
+                                                      float(depth_divisor), ptr(cams), n_levels))
 
     def ingest_rgbd(self, ids, rgb, depth, cams, n_levels, bgr=False, depth_divisor=1.0):
         """Node-side ingestion (NodeRgbdAlignment.cpp:177-199): rgb (n,H,W,3) u8, depth (n,H,W) f32 / f64 / u16."""

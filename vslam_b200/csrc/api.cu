@@ -94,7 +94,7 @@ struct vslamb200_ctx
   std::vector<int> freeSlots;
   std::vector<Arena> arenas;
   DevBuf dFrames;  // FrameDev table
-  DevBuf stageGray, stageDepth, slotsBuf;
+  DevBuf stageGray, stageDepth, stageU16, slotsBuf;
   // alignment workspace
   DevBuf jobs, views, chunkCounts, partials, lists, trace, plane, ext;
   int traceEnabled = 0, timing = 0;
@@ -305,7 +305,9 @@ int wait_frame_ready(vslamb200_ctx * c, int slot)
 }
 
 // pyramid + gradients for uploaded level-0 planes; queued on `stream`, host-synchronised only if asked
-int preprocess(vslamb200_ctx * c, const std::vector<int> & slots, int nLevels, bool sync, cudaStream_t stream)
+// stagedU16 != nullptr: the level-0 depth planes are first filled from 16-bit sensor depth staged on the device
+int preprocess(vslamb200_ctx * c, const std::vector<int> & slots, int nLevels, bool sync, cudaStream_t stream,
+               const uint16_t * stagedU16 = nullptr, double divisor = 1.0)
 {
   const int n = (int)slots.size();
   const unsigned ring = c->slotsNext++ % vslamb200_ctx::kSlotRing;
@@ -324,6 +326,10 @@ int preprocess(vslamb200_ctx * c, const std::vector<int> & slots, int nLevels, b
   const vb::FrameDev & f = c->frames[slots[0]].dev;
   const vb::FrameDev * table = c->dFrames.as<vb::FrameDev>();
   if (c->timing) CK(cudaEventRecord(c->ev[0], stream));
+  if (stagedU16) {
+    vb::launch_depth_u16(stagedU16, divisor, f.W[0], f.H[0], table, dSlots, n, stream);
+    c->stats.kernel_launches += 1;
+  }
   for (int l = 1; l < nLevels; l++) {
     vb::launch_pyramid_level(table, dSlots, n, l, f.W[l], f.H[l], f.Wd[l], f.Hd[l], f.W[l - 1], f.H[l - 1], f.Wd[l - 1],
                              f.Hd[l - 1], stream);
@@ -436,7 +442,7 @@ void vslamb200_destroy(vslamb200_ctx * c)
     if (a.ready) cudaEventDestroy(a.ready);
     if (a.ptr) cudaFree(a.ptr);
   }
-  DevBuf * bufs[] = {&c->dFrames, &c->stageGray, &c->stageDepth, &c->slotsBuf, &c->jobs, &c->views,
+  DevBuf * bufs[] = {&c->dFrames, &c->stageGray, &c->stageDepth, &c->stageU16, &c->slotsBuf, &c->jobs, &c->views,
                      &c->chunkCounts, &c->partials, &c->lists, &c->trace, &c->plane, &c->ext};
   for (auto b : bufs) b->release();
   if (c->copyStream) {
@@ -556,6 +562,37 @@ int vslamb200_frames_upload_async(
   // pyramids and gradients follow the copies on the copy stream, so the compute stream is not held up by an upload
   // it does not depend on; whoever reads these frames first waits for the arena's event
   if (int e = preprocess(c, slots, nLevels, false, c->copyStream)) return e;
+  Arena & a = c->arenas[c->frames[slots[0]].arena];
+  if (!a.ready) CK(cudaEventCreateWithFlags(&a.ready, cudaEventDisableTiming));
+  CK(cudaEventRecord(a.ready, c->copyStream));
+  a.pending = true;
+  return 0;
+}
+
+int vslamb200_frames_upload_u16_async(
+  vslamb200_ctx * c, int n, const uint64_t * ids, int W, int H, const uint8_t * gray, const uint16_t * depth, double depthDivisor,
+  const double * cams, int nLevels)
+{
+  if (!c || !gray || !depth) return fail(VSLAMB200_EINVAL, "frames_upload_u16_async: null argument");
+  if (!(depthDivisor > 0.0) || !std::isfinite(depthDivisor)) return fail(VSLAMB200_EINVAL, "frames_upload_u16_async: bad depth_divisor");
+  CK(cudaSetDevice(c->device));
+  std::vector<int> slots;
+  if (int e = make_frames(c, n, ids, W, H, cams, nLevels, slots)) return e;
+  const size_t npx = (size_t)W * H;
+  const vb::FrameDev & f0 = c->frames[slots[0]].dev;
+  const size_t frameStride = n > 1 ? (size_t)((uint8_t *)c->frames[slots[1]].dev.I[0] - (uint8_t *)f0.I[0]) : npx * 4;
+  // the 16-bit planes land in a staging buffer of the context (grown once; the copy stream orders its reuse), the grey
+  // planes go straight into the frames; conversion, pyramids and gradients follow on the copy stream
+  if (npx * 2 * (size_t)n > c->stageU16.cap) {
+    CK(cudaStreamSynchronize(c->copyStream));
+    CK(c->stageU16.ensure(npx * 2 * (size_t)n));
+  }
+  CK(cudaEventRecord(c->computeMark, c->stream));
+  CK(cudaStreamWaitEvent(c->copyStream, c->computeMark, 0));
+  CK(cudaMemcpy2DAsync(f0.I[0], frameStride, gray, npx, npx, n, cudaMemcpyHostToDevice, c->copyStream));
+  CK(cudaMemcpyAsync(c->stageU16.p, depth, npx * 2 * (size_t)n, cudaMemcpyHostToDevice, c->copyStream));
+  c->stats.h2d_bytes += (uint64_t)n * npx * 3;
+  if (int e = preprocess(c, slots, nLevels, false, c->copyStream, c->stageU16.as<uint16_t>(), depthDivisor)) return e;
   Arena & a = c->arenas[c->frames[slots[0]].arena];
   if (!a.ready) CK(cudaEventCreateWithFlags(&a.ready, cudaEventDisableTiming));
   CK(cudaEventRecord(a.ready, c->copyStream));

@@ -278,6 +278,8 @@ void launch_ingest(const uint8_t * stagedGray, const void * stagedDepth, int dep
                    const FrameDev * frames, const int * slots, int n, cudaStream_t s);
 void launch_ingest_rgbd(const uint8_t * stagedRgb, const void * stagedDepth, int depthType, int bgr, double divisor, int W,
                         int H, const FrameDev * frames, const int * slots, int n, cudaStream_t s);
+void launch_depth_u16(const uint16_t * staged, double divisor, int W, int H, const FrameDev * frames, const int * slots, int n,
+                      cudaStream_t s);
 void launch_pyramid_level(const FrameDev * frames, const int * slots, int n, int level, int W, int H, int Wd, int Hd,
                           int Wp, int Hp, int Wdp, int Hdp, cudaStream_t s);
 void launch_gradients(const FrameDev * frames, const int * slots, int n, int level, int W, int H, cudaStream_t s);

@@ -110,6 +110,42 @@ void launch_ingest_rgbd(const uint8_t * stagedRgb, const void * stagedDepth, int
     ingest_rgbd_kernel<float><<<grid, 256, 0, s>>>(stagedRgb, (const float *)stagedDepth, bgr, divisor, npx, frames, slots);
 }
 
+// 16-bit sensor depth -> level-0 depth plane: k / divisor in double, narrowed to the f32 plane (the depth half of the
+// ingestion above; loadDepth(...) / 5000.0, odometry/test/test_alignment_se3.cpp:99).  Eight pixels per thread.
+__global__ void __launch_bounds__(256) depth_u16_kernel(
+  const uint16_t * __restrict__ staged, double divisor, size_t npx, const FrameDev * __restrict__ frames,
+  const int * __restrict__ slots)
+{
+  const FrameDev & f = frames[slots[blockIdx.y]];
+  const uint16_t * d = staged + (size_t)blockIdx.y * npx;
+  float * __restrict__ z = f.Z[0];
+  const bool vec = (npx & 7) == 0;
+  for (size_t i = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) * 8; i < npx; i += (size_t)gridDim.x * blockDim.x * 8) {
+    if (vec) {
+      const uint4 w = *reinterpret_cast<const uint4 *>(d + i);
+      const uint32_t ww[4] = {w.x, w.y, w.z, w.w};
+      float o[8];
+#pragma unroll
+      for (int k = 0; k < 4; k++) {
+        o[2 * k] = (float)((double)(ww[k] & 0xffff) / divisor);
+        o[2 * k + 1] = (float)((double)(ww[k] >> 16) / divisor);
+      }
+      *reinterpret_cast<float4 *>(z + i) = make_float4(o[0], o[1], o[2], o[3]);
+      *reinterpret_cast<float4 *>(z + i + 4) = make_float4(o[4], o[5], o[6], o[7]);
+    } else {
+      for (int k = 0; k < 8 && i + k < npx; k++) z[i + k] = (float)((double)d[i + k] / divisor);
+    }
+  }
+}
+
+void launch_depth_u16(const uint16_t * staged, double divisor, int W, int H, const FrameDev * frames, const int * slots, int n,
+                      cudaStream_t s)
+{
+  const size_t npx = (size_t)W * H;
+  dim3 grid((unsigned)std::min<size_t>(148 * 2, (npx / 8 + 255) / 256), n);
+  depth_u16_kernel<<<grid, 256, 0, s>>>(staged, divisor, npx, frames, slots);
+}
+
 // ------------------------------------------------------------------------------------------------
 // K1a + K1b: one pyramid step for intensity (cv::pyrDown: 5x5 binomial, reflect-101, (s+128)>>8, even
 // rows/cols; Frame.cpp:264) and depth (3x3 masked median at (2i,2j) with zero border, even-count rule

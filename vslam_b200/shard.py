@@ -2,7 +2,7 @@
 
 The path partitions by frame pair: pair i aligns frame i+1 against frame i and depends on nothing else, so ranks
 take contiguous pair ranges (each also needs the first frame of its range: one frame of overlap) and there is no
-data-path collective.  The only exchange is the gather of the 7-double relative poses at the end
+data-path collective.  Batches of independent pairs (BASELINE configs[2]) are dealt round-robin instead (deal_pairs).  The only exchange is the gather of the 7-double relative poses at the end
 (torch.distributed all_gather: NCCL on GPUs, gloo in the CPU tests)."""
 import numpy as np
 
@@ -20,6 +20,40 @@ def frame_range(n_pairs, world, rank):
     """[lo, hi) of the frames rank must hold: its pairs plus the leading keyframe (empty if it owns no pair)."""
     lo, hi = pair_range(n_pairs, world, rank)
     return (lo, hi + 1) if hi > lo else (lo, lo)
+
+
+def deal_pairs(n_pairs, world, rank):
+    """Indices of the pairs rank owns when independent pairs are dealt round-robin (pair k goes to rank k mod world).
+    The alignments of a batch need different numbers of Gauss-Newton iterations; dealing them like cards evens the
+    per-rank work out where contiguous blocks of a sorted or correlated batch would not."""
+    if world < 1 or not 0 <= rank < world:
+        raise ValueError("bad world/rank")
+    return np.arange(rank, n_pairs, world)
+
+
+def gather_dealt(local, n_pairs, dist=None, device="cpu"):
+    """all_gather of per-rank (n_local, 7) pose arrays of round-robin dealt pairs (deal_pairs) into the (n_pairs, 7)
+    array of the whole batch, in pair order, on every rank."""
+    import torch
+    local = np.ascontiguousarray(local, np.float64).reshape(-1, 7)
+    if dist is None or not dist.is_initialized() or dist.get_world_size() == 1:
+        if len(local) != n_pairs:
+            raise ValueError("single rank must hold every pair")
+        return local.copy()
+    world, rank = dist.get_world_size(), dist.get_rank()
+    if len(local) != len(deal_pairs(n_pairs, world, rank)):
+        raise ValueError(f"rank {rank} holds {len(local)} poses, expected {len(deal_pairs(n_pairs, world, rank))}")
+    cap = (n_pairs + world - 1) // world
+    buf = torch.zeros((cap, 7), dtype=torch.float64, device=device)
+    if len(local):
+        buf[:len(local)] = torch.from_numpy(local).to(device)
+    parts = [torch.empty_like(buf) for _ in range(world)]
+    dist.all_gather(parts, buf)
+    out = np.empty((n_pairs, 7))
+    for r, p in enumerate(parts):
+        idx = deal_pairs(n_pairs, world, r)
+        out[idx] = p[:len(idx)].cpu().numpy()
+    return out
 
 
 def gather_poses(local, n_pairs, dist=None, device="cpu"):
