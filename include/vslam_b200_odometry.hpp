@@ -25,109 +25,7 @@
 
 namespace vslam_b200
 {
-using Vec6d = std::array<double, 6>;
-
-// ------------------------------------------------------------------------------------------------
-// SE3 algebra with Sophus' conventions: tangent [upsilon; omega], storage unit quaternion (x y z w) + translation
-// ------------------------------------------------------------------------------------------------
-namespace se3
-{
-inline void rotate(const double * q, const double * p, double * o)
-{
-  // o = R(q) p through t = 2 q_v x p:  o = p + w t + q_v x t
-  const double x = q[0], y = q[1], z = q[2], w = q[3];
-  const double tx = 2 * (y * p[2] - z * p[1]), ty = 2 * (z * p[0] - x * p[2]), tz = 2 * (x * p[1] - y * p[0]);
-  o[0] = p[0] + w * tx + (y * tz - z * ty);
-  o[1] = p[1] + w * ty + (z * tx - x * tz);
-  o[2] = p[2] + w * tz + (x * ty - y * tx);
-}
-inline SE3d mul(const SE3d & a, const SE3d & b)
-{
-  SE3d o;
-  const double * p = a.data();
-  const double * r = b.data();
-  double q[4] = {p[3] * r[0] + p[0] * r[3] + p[1] * r[2] - p[2] * r[1], p[3] * r[1] + p[1] * r[3] + p[2] * r[0] - p[0] * r[2],
-                 p[3] * r[2] + p[2] * r[3] + p[0] * r[1] - p[1] * r[0], p[3] * r[3] - p[0] * r[0] - p[1] * r[1] - p[2] * r[2]};
-  const double n = std::sqrt(q[0] * q[0] + q[1] * q[1] + q[2] * q[2] + q[3] * q[3]);
-  for (int i = 0; i < 4; i++) o.data()[i] = q[i] / n;
-  double rt[3];
-  rotate(p, r + 4, rt);
-  for (int i = 0; i < 3; i++) o.data()[4 + i] = rt[i] + p[4 + i];
-  return o;
-}
-inline SE3d inverse(const SE3d & a)
-{
-  SE3d o;
-  o.data()[0] = -a.data()[0];
-  o.data()[1] = -a.data()[1];
-  o.data()[2] = -a.data()[2];
-  o.data()[3] = a.data()[3];
-  double rt[3];
-  rotate(o.data(), a.data() + 4, rt);
-  for (int i = 0; i < 3; i++) o.data()[4 + i] = -rt[i];
-  return o;
-}
-inline void cross(const double * a, const double * b, double * o)
-{
-  o[0] = a[1] * b[2] - a[2] * b[1];
-  o[1] = a[2] * b[0] - a[0] * b[2];
-  o[2] = a[0] * b[1] - a[1] * b[0];
-}
-inline SE3d exp(const Vec6d & xi)
-{
-  const double * u = xi.data();
-  const double * w = xi.data() + 3;
-  const double th2 = w[0] * w[0] + w[1] * w[1] + w[2] * w[2], th = std::sqrt(th2);
-  double imag, real, B, C;
-  if (th2 < 1e-20) {
-    imag = 0.5 - th2 / 48.0 + th2 * th2 / 3840.0;
-    real = 1.0 - th2 / 8.0 + th2 * th2 / 384.0;
-    B = 0.5;
-    C = 1.0 / 6.0;
-  } else {
-    imag = std::sin(0.5 * th) / th;
-    real = std::cos(0.5 * th);
-    B = (1.0 - std::cos(th)) / th2;
-    C = (th - std::sin(th)) / (th2 * th);
-  }
-  SE3d o;
-  for (int i = 0; i < 3; i++) o.data()[i] = imag * w[i];
-  o.data()[3] = real;
-  double c1[3], c2[3];
-  cross(w, u, c1);
-  cross(w, c1, c2);
-  for (int i = 0; i < 3; i++) o.data()[4 + i] = u[i] + B * c1[i] + C * c2[i];  // V(omega) upsilon
-  return o;
-}
-inline Vec6d log(const SE3d & T)
-{
-  const double * q = T.data();
-  const double n2 = q[0] * q[0] + q[1] * q[1] + q[2] * q[2], n = std::sqrt(n2), w = q[3];
-  double f;
-  if (n2 < 1e-20)
-    f = 2.0 / w - 2.0 / 3.0 * n2 / (w * w * w);
-  else if (std::fabs(w) < 1e-10)
-    f = (w > 0 ? M_PI : -M_PI) / n;
-  else
-    f = 2.0 * std::atan(n / w) / n;
-  const double om[3] = {f * q[0], f * q[1], f * q[2]};
-  const double th2 = om[0] * om[0] + om[1] * om[1] + om[2] * om[2], th = std::sqrt(th2);
-  double c;
-  if (th2 < 1e-12)
-    c = 1.0 / 12.0;
-  else
-    c = (1.0 - th * std::cos(0.5 * th) / (2.0 * std::sin(0.5 * th))) / th2;
-  double c1[3], c2[3];
-  cross(om, q + 4, c1);
-  cross(om, c1, c2);
-  Vec6d xi;
-  for (int i = 0; i < 3; i++) {
-    xi[i] = q[4 + i] - 0.5 * c1[i] + c * c2[i];  // V^-1(omega) t
-    xi[3 + i] = om[i];
-  }
-  return xi;
-}
-}  // namespace se3
+// (Vec6d and the SE3 algebra, namespace se3, live in vslam_b200.hpp: the least-squares problem of the aligner uses them too)
 
 namespace algorithm
 {
@@ -284,30 +182,32 @@ public:
     _trackKeyFrame(false)
   {
   }
+  // Behaviour of Odometry.cpp:31-62.  Which frames the new one is aligned against:
+  //   key frame AND last frame (stacked) when both exist and differ and key frames are included (the default);
+  //   the key frame alone in key-frame tracking mode; otherwise the last frame.
+  // Without a previous frame, or when the aligner throws (the reference logs e.what() and carries on), the frame's own
+  // pose - the motion model's prediction - is the estimate and the speed is the identity.
   void update(Frame::ConstShPtr frame) override
   {
-    if (_map->lastFrame()) {
+    _pose = nullptr;
+    const Frame::ConstShPtr last = _map->lastFrame(), key = _map->lastKf();
+    if (last) {
       try {
-        if (_includeKeyFrame && _map->lastKf() && _map->lastKf() != _map->lastFrame()) {
-          _pose = _aligner->align(std::vector<Frame::ConstShPtr>{_map->lastKf(), _map->lastFrame()}, frame);
-        } else if (_trackKeyFrame && _map->lastKf()) {
-          _pose = _aligner->align(_map->lastKf(), frame);
-        } else {
-          _pose = _aligner->align(_map->lastFrame(), frame);
-        }
-        const double dT = static_cast<double>(frame->t() - _map->lastFrame()->t()) / 1e9;
-        Vec6d x = se3::log(algorithm::computeRelativeTransform(_map->lastFrame()->pose().pose(), _pose->pose()));
-        for (double & v : x) v /= dT;
-        _speed = std::make_shared<PoseWithCovariance>(se3::exp(x), _pose->cov());
-      } catch (const std::runtime_error & e) {  // Odometry.cpp:52-56: log, fall back to the predicted pose
+        _pose = alignAgainst(last, key, frame);
+      } catch (const std::runtime_error & e) {
         _lastError = e.what();
-        _pose = std::make_shared<PoseWithCovariance>(frame->pose());
-        _speed = std::make_shared<PoseWithCovariance>();
       }
-    } else {
+    }
+    if (!_pose) {
       _pose = std::make_shared<PoseWithCovariance>(frame->pose());
       _speed = std::make_shared<PoseWithCovariance>();
+      return;
     }
+    // speed = exp(log(motion since the last frame) / elapsed seconds), with the covariance of the new pose
+    const double seconds = static_cast<double>(frame->t() - last->t()) / 1e9;
+    Vec6d twist = se3::log(algorithm::computeRelativeTransform(last->pose().pose(), _pose->pose()));
+    for (double & v : twist) v /= seconds;
+    _speed = std::make_shared<PoseWithCovariance>(se3::exp(twist), _pose->cov());
   }
   PoseWithCovariance::ConstShPtr pose() const override { return _pose; }
   PoseWithCovariance::ConstShPtr speed() const override { return _speed; }
@@ -316,6 +216,13 @@ public:
   const std::string & lastError() const { return _lastError; }
 
 protected:
+  PoseWithCovariance::ConstShPtr alignAgainst(const Frame::ConstShPtr & last, const Frame::ConstShPtr & key,
+                                              const Frame::ConstShPtr & frame) const
+  {
+    if (_includeKeyFrame && key && key != last) return _aligner->align(std::vector<Frame::ConstShPtr>{key, last}, frame);
+    if (_trackKeyFrame && key) return _aligner->align(key, frame);
+    return _aligner->align(last, frame);
+  }
   const std::shared_ptr<const SE3Alignment> _aligner;
   const Map::ConstShPtr _map;
   const bool _includeKeyFrame, _trackKeyFrame;
@@ -331,51 +238,72 @@ protected:
 // ------------------------------------------------------------------------------------------------
 namespace utils
 {
+namespace detail
+{
+inline std::vector<std::string> split(const std::string & text, char sep)
+{
+  std::vector<std::string> out;
+  size_t from = 0;
+  for (;;) {
+    const size_t to = text.find(sep, from);
+    out.push_back(text.substr(from, to == std::string::npos ? std::string::npos : to - from));
+    if (to == std::string::npos) return out;
+    from = to + 1;
+  }
+}
+// "1305031102.1758" -> nanoseconds.  The digits behind the point count units of 1e-4 s whatever their number (TUM ground
+// truth has four decimals), and the sum goes through a double - both as utils.cpp:104-112 has it.
+inline Timestamp stampFromTum(const std::string & field)
+{
+  const std::vector<std::string> parts = split(field, '.');
+  const unsigned long long whole = std::stoull(parts[0]);
+  const unsigned long long frac = parts.size() > 1 ? std::stoull(parts[1]) * 100000ull : 0ull;
+  return static_cast<Timestamp>(whole * 1e9 + frac);
+}
+// nanoseconds -> "sec.nanosec" without zero padding of the fraction (utils.cpp:150-152)
+inline std::string stampToTum(Timestamp ns)
+{
+  const Timestamp whole = static_cast<Timestamp>(static_cast<double>(ns) / 1e9);
+  const Timestamp rest = static_cast<Timestamp>(static_cast<double>(ns) - static_cast<double>(whole) * 1e9);
+  return std::to_string(whole) + "." + std::to_string(rest);
+}
+}  // namespace detail
+
+// One pose per line: "timestamp tx ty tz qx qy qz qw", '#' lines are comments.
 inline std::map<Timestamp, SE3d> loadTrajectory(const std::string & path)
 {
-  std::ifstream gtFile(path);
-  if (!gtFile.is_open()) throw Exception("Could not open file at: " + path);  // the reference builds the exception but never throws it
-  std::map<Timestamp, SE3d> poses;
-  std::string line;
-  while (std::getline(gtFile, line)) {
-    std::vector<std::string> elements;
-    std::string s;
-    std::istringstream lines(line);
-    while (std::getline(lines, s, ' ')) elements.push_back(s);
-    if (elements.empty() || elements[0] == "#" || elements[0].empty() || elements[0][0] == '#') continue;
-    if (elements.size() < 8) throw Exception("loadTrajectory: malformed line: " + line);
+  std::ifstream in(path);
+  if (!in.is_open()) throw Exception("Could not open file at: " + path);  // the reference builds the exception but never throws it
+  std::map<Timestamp, SE3d> trajectory;
+  for (std::string row; std::getline(in, row);) {
+    const std::vector<std::string> f = detail::split(row, ' ');
+    if (f[0].empty() || f[0][0] == '#') continue;
+    if (f.size() < 8) throw Exception("loadTrajectory: malformed line: " + row);
+    double v[7];  // tx ty tz qx qy qz qw
+    for (int i = 0; i < 7; i++) v[i] = std::stod(f[1 + i]);
+    const double qn = std::sqrt(v[3] * v[3] + v[4] * v[4] + v[5] * v[5] + v[6] * v[6]);  // Sophus normalises the quaternion
     SE3d T;
-    for (int i = 0; i < 3; i++) T.data()[4 + i] = std::stod(elements[1 + i]);
-    double q[4] = {std::stod(elements[4]), std::stod(elements[5]), std::stod(elements[6]), std::stod(elements[7])};
-    const double n = std::sqrt(q[0] * q[0] + q[1] * q[1] + q[2] * q[2] + q[3] * q[3]);  // Sophus normalises the quaternion
-    for (int i = 0; i < 4; i++) T.data()[i] = q[i] / n;
-    std::vector<std::string> tElements;
-    std::string st;
-    std::istringstream tLine(elements[0]);
-    while (std::getline(tLine, st, '.')) tElements.push_back(st);
-    const auto sec = std::stoull(tElements[0]);
-    const auto nanosec = tElements.size() > 1 ? std::stoull(tElements[1]) * 100000 : 0ull;
-    poses.insert({static_cast<Timestamp>(sec * 1e9 + nanosec), T});
+    for (int i = 0; i < 4; i++) T.data()[i] = v[3 + i] / qn;
+    for (int i = 0; i < 3; i++) T.data()[4 + i] = v[i];
+    trajectory.emplace(detail::stampFromTum(f[0]), T);
   }
-  return poses;
+  return trajectory;
 }
 
+// Three header lines, then one pose per line in the order above (optionally followed by the 36 covariance entries).
 inline void writeTrajectory(const std::map<Timestamp, PoseWithCovariance::ConstShPtr> & traj, const std::string & path,
                             bool writeCovariance = false)
 {
-  std::ofstream algoFile(path);
-  if (!algoFile.is_open()) throw Exception("Could not open file at: " + path);
-  algoFile << "# Algorithm Trajectory\n";
-  algoFile << "# file: \"" << path << "\"\n";
-  algoFile << "# timestamp tx ty tz qx qy qz qw\n";
-  for (const auto & pose : traj) {
-    const Timestamp sec = static_cast<Timestamp>(static_cast<double>(pose.first) / 1e9);
-    const double * d = pose.second->pose().data();
-    algoFile << sec << "." << static_cast<Timestamp>(static_cast<double>(pose.first) - static_cast<double>(sec) * 1e9) << " " << d[4]
-             << " " << d[5] << " " << d[6] << " " << d[0] << " " << d[1] << " " << d[2] << " " << d[3];
+  std::ofstream out(path);
+  if (!out.is_open()) throw Exception("Could not open file at: " + path);
+  out << "# Algorithm Trajectory\n# file: \"" << path << "\"\n# timestamp tx ty tz qx qy qz qw\n";
+  static const int order[7] = {4, 5, 6, 0, 1, 2, 3};  // translation first, then the quaternion
+  for (const auto & entry : traj) {
+    out << detail::stampToTum(entry.first);
+    for (int k : order) out << " " << entry.second->pose().data()[k];
     if (writeCovariance)
-      for (int i = 0; i < 36; i++) algoFile << " " << pose.second->cov()[i];
-    algoFile << "\n";
+      for (double c : entry.second->cov()) out << " " << c;
+    out << "\n";
   }
 }
 }  // namespace utils

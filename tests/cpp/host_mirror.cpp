@@ -4,6 +4,8 @@
 // (column-major u8 intensity, column-major double depth) so that the transposing ingest path is covered.
 //   usage: host_mirror W H seed levels [multi]
 // prints "pose qx qy qz qw tx ty tz" (and "batch ..." lines); exit 3 + message when no CUDA device exists.
+#include <algorithm>
+#include <cmath>
 #include <cstdio>
 #include <cstdlib>
 
@@ -96,6 +98,59 @@ int main(int argc, char ** argv)
         fprintf(stderr, "re-uploaded frame gives a different result\n");
         return 1;
       }
+    // ---- the least-squares interfaces (Solver.h:22-63): solver->solve(problem) on ONE level drives the device path
+    // iteration by iteration and reproduces the iterates of SE3Alignment::align on frames with a one-level pyramid
+    for (int withPrior = 0; withPrior < 2; withPrior++) {
+      auto g0 = make_frame(W, H, cam, I3, z3, seed, 1);
+      auto g1 = make_frame(W, H, cam, R, t, seed, 1);
+      const size_t maxIt = 6;
+      auto gn = std::make_shared<least_squares::GaussNewton>(1e-7, maxIt);
+      SE3Alignment one(30.0, gn, loss, withPrior != 0);
+      check(vslamb200_set_trace(one.context(), 1));
+      auto viaAlign = one.align(g0, g1);
+      std::vector<double> tr(maxIt * VSLAMB200_TRACE_STRIDE);
+      check(vslamb200_get_trace(one.context(), 0, tr.data()));
+      size_t nTrace = 0;
+      while (nTrace < maxIt && tr[nTrace * VSLAMB200_TRACE_STRIDE] == 1.0) nTrace++;
+      least_squares::Prior::ConstShPtr prior;
+      if (withPrior) prior = std::make_shared<MotionPrior>(g1->pose(), g0->pose());
+      auto problem = std::make_shared<lukas_kanade::InverseCompositional>(one, g0, g1, 0, SE3d(), prior);
+      std::shared_ptr<least_squares::Solver> solver = gn;
+      auto res = solver->solve(problem);
+      double worst = 0.0;
+      for (size_t i = 0; i < std::min(nTrace, res->nSteps()); i++) {
+        const double * rec = &tr[i * VSLAMB200_TRACE_STRIDE];
+        for (int k = 0; k < 6; k++) worst = std::max(worst, std::fabs(res->x(i, k) - rec[6 + k]));
+        worst = std::max(worst, std::fabs(res->chi2[i] - rec[2]) / std::fabs(rec[2]));
+        worst = std::max(worst, std::fabs(res->stepSize[i] - rec[3]));
+        for (int a = 0; a < 6; a++)
+          for (int b = 0; b < 6; b++)
+            worst = std::max(worst, std::fabs(res->normalEquations[i]->A()(a, b) - rec[18 + 6 * a + b]) / std::fabs(rec[18]));
+      }
+      double poseDiff = 0.0;
+      for (int k = 0; k < 7; k++) poseDiff = std::max(poseDiff, std::fabs(problem->se3().data()[k] - viaAlign->pose().data()[k]));
+      printf("solve%d %zu %zu %.3g %.3g %d\n", withPrior, res->nSteps(), nTrace, worst, poseDiff, res->stop);
+    }
+    // ---- per-level accessors of a resident frame (Frame.h:45-83): checksums for the Python test
+    {
+      printf("levels");
+      for (size_t l = 0; l < levels; l++) {
+        const Image & I = f1->intensity(l);
+        const auto & gx = f1->dIx(l);
+        const auto & gy = f1->dIy(l);
+        const DepthMap & Z = f1->depth(l);
+        double sI = 0, sx = 0, sy = 0, sZ = 0;
+        for (auto v : I.data) sI += v;
+        for (auto v : gx.data) sx += std::fabs(v);
+        for (auto v : gy.data) sy += std::fabs(v);
+        for (auto v : Z.data) sZ += v;
+        const auto pc = f1->pcl(l);
+        const size_t mid = pc.size() / 2 + (size_t)Z.cols / 3;
+        printf(" %d %d %.17g %.17g %.17g %.17g %.17g %.17g %.17g %.17g", I.cols, I.rows, sI, sx, sy, sZ, f1->camera(l)->fx(),
+               pc[mid][0], pc[mid][1], pc[mid][2]);
+      }
+      printf("\n");
+    }
     printf("ok\n");
   } catch (const std::runtime_error & e) {
     fprintf(stderr, "runtime_error: %s\n", e.what());

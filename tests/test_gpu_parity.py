@@ -481,6 +481,27 @@ def test_cpp_host_mirror_matches_oracle(oracle, synth, capi):
     refm = O.align(cfg, [f0], [O.IDENTITY], f1, O.IDENTITY, multi=True)
     dt, dr = pose_err(O, gotm, refm["pose"])
     assert dt < POSE_TOL and dr < POSE_TOL
+    # solver->solve(problem) (least_squares::Problem / Solver::Results, Solver.h:22-63) reproduces align's iterates on one
+    # level, without and with the motion prior: same number of steps, x / chi2 / step size / A per iteration, final pose
+    for key in ("solve0", "solve1"):
+        n_solve, n_trace, worst, pose_diff, stop = lines[key]
+        assert int(n_solve) == int(n_trace) > 1, lines[key]
+        assert float(worst) < 1e-9 and float(pose_diff) < 1e-9, lines[key]
+    # Frame::intensity(l) / dIx(l) / dIy(l) / depth(l) / camera(l) / pcl(l) of a resident frame against the oracle's frame
+    lv = [float(x) for x in lines["levels"]]
+    for l in range(L):
+        Wl, Hl, sI, sx, sy, sZ, fx, px, py, pz = lv[10 * l:10 * l + 10]
+        ref_l = f1.level(l)
+        assert (Wl, Hl) == (ref_l["I"].shape[1], ref_l["I"].shape[0])
+        assert sI == float(ref_l["I"].astype(np.float64).sum())
+        assert sx == float(np.abs(ref_l["dIx"].astype(np.float64)).sum()) and sy == float(np.abs(ref_l["dIy"].astype(np.float64)).sum())
+        assert abs(sZ - float(ref_l["Z"].sum())) <= 1e-9 * abs(sZ)
+        assert fx == p["cam"][0] * 0.5 ** l
+        idx = (int(Wl) * int(Hl)) // 2 + int(Wl) // 3
+        v, u = divmod(idx, int(Wl))
+        d = float(ref_l["Z"][v, u])
+        cam_l = [c * 0.5 ** l for c in p["cam"]]
+        assert np.allclose([px, py, pz], [(u - cam_l[2]) / cam_l[0] * d, (v - cam_l[3]) / cam_l[1] * d, d], rtol=1e-12)
 
 
 @pytest.mark.gpu

@@ -256,3 +256,68 @@ def test_odometry_host_mirror_algebra_rings_prediction_and_trajectory_files(orac
     text = out.read_text().splitlines()
     assert text[0] == "# Algorithm Trajectory" and text[2] == "# timestamp tx ty tz qx qy qz qw"
     assert text[4].split()[1:] == ["1.5", "-0.25", "0.125", "0", "0", "0", "1"]
+
+
+def test_least_squares_mirror_scalers_losses_normal_equations_and_gauss_newton(oracle):
+    """The least-squares half of include/vslam_b200.hpp on the host (tests/cpp/host_least_squares.cpp): scalers
+    (Scaler.cpp:21-67) and loss weights (Loss.cpp:23-100) against independent numpy restatements, the reference's
+    constructor signatures and defaults (Loss.h:70,87,101), NormalEquations (NormalEquations.cpp:53-76) against J^T W J,
+    the 6x6 helpers against numpy.linalg, and GaussNewton::solve (GaussNewton.cpp:33-102) on a linear problem."""
+    import subprocess
+    from vslam_b200 import build, capi as A
+    exe = build.build_host_least_squares()
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=60)
+    assert r.returncode == 0 and r.stdout.strip().endswith("ok"), r.stdout[-500:] + r.stderr[-500:]
+    rows = [ln.split() for ln in r.stdout.strip().splitlines()]
+    first = {}
+    for row in rows:
+        first.setdefault(row[0], row)
+    res = np.array([((k * 37) % 101 - 50) * 0.37 for k in range(200)])
+    sc = np.array([float(v) for v in first["scale"][1:]])
+    srt = np.sort(res)
+    med = (srt[99] + srt[101]) / 2            # the reference's even-count rule: v[n/2-1], v[n/2+1]
+    assert list(sc[:2]) == [0.0, 1.0]
+    assert np.allclose(sc[2:4], [med, np.sqrt(np.abs(res - med).sum() / 199)], rtol=1e-14)
+    assert np.allclose(sc[4:6], [res.mean(), np.sqrt(np.abs(res - res.mean()).sum() / 199)], rtol=1e-13, atol=1e-15)
+    sigma = 1.0
+    for _ in range(30):
+        nxt = np.sqrt(np.mean(res * res * 6.0 / (5.0 + (res / sigma) ** 2)))
+        step, sigma = abs(sigma - nxt), nxt
+        if not step > 1e-5:
+            break
+    assert sc[6] == 0.0 and abs(sc[7] - sigma) < 1e-12 * sigma
+    assert [float(first["median4"][i]) for i in (1, 3, 5)] == [3.0, 5.0, 3.0]  # (1+3)/2... v[1], v[3] of 1 2 3 4 -> 3
+    kinds = [int(v) for v in first["kinds"][1:8]]
+    scalers = [int(v) for v in first["kinds"][9:16]]
+    assert kinds == [A.LOSS_TUKEY, A.LOSS_HUBER, A.LOSS_HUBER, A.LOSS_HUBER, A.LOSS_TDIST, A.LOSS_TDIST, A.LOSS_QUADRATIC]
+    # defaults of the reference: Tukey / Huber / LossTDistribution default to the MedianScaler (Loss.h:70,87,101)
+    assert scalers == [A.SCALER_MEDIAN, A.SCALER_MEDIAN, A.SCALER_MEAN, A.SCALER_MEDIAN, A.SCALER_MEDIAN, A.SCALER_TDIST,
+                       A.SCALER_IDENTITY]
+    assert float(first["kinds"][17]) == float(np.float32(1.345)) and float(first["kinds"][18]) == 10.0
+    for row in (rw for rw in rows if rw[0] == "w"):
+        x, wt, wh, wd, wq, rt, rh, rq = [float(v) for v in row[1:] if v != "rho"]
+        C = 4.6851
+        assert abs(wt - ((1 - (x / C) ** 2) ** 2 if abs(x) < C else 0.0)) < 1e-15
+        assert abs(wh - (1.0 if abs(x) < 10 else 1.0 / abs(x))) < 1e-15       # 1/|r|, not c/|r| (Loss.cpp:65-72)
+        assert abs(wd - 6.0 / (5.0 + x * x)) < 1e-15 and wq == 1.0 and rq == 0.5 * x * x
+        assert abs(rt - (C / 6 * (1 - (1 - (x / C) ** 2) ** 3) if abs(x) < C else C / 6)) < 1e-15
+        assert abs(rh - (0.5 * x * x if abs(x) < 10 else 10 * abs(x) - 0.5 * x * x)) < 1e-12
+    assert [float(v) for v in first["lossscale"][1:]] == [sc[6], sc[7]]
+    k = np.arange(40)
+    J = np.sin(0.7 * k[:, None] + 1.3 * np.arange(6)[None, :]) + 1.5 * (np.arange(6)[None, :] == (k % 6)[:, None])
+    y = np.cos(0.31 * k) * 2.0
+    w = 0.5 + (k % 5) * 0.25
+    ne = np.array([float(v) for v in first["ne"][1:]])
+    assert ne[0] == 40 and abs(ne[1] - (w * y * y).sum()) < 1e-12
+    assert np.allclose(ne[2:8], J.T @ (w * y), rtol=1e-13, atol=1e-13)
+    Aw = J.T @ (w[:, None] * J)
+    assert np.allclose(ne[8:44].reshape(6, 6), Aw, rtol=1e-13, atol=1e-13)
+    cb = [float(v) for v in first["combine"][1:]]
+    assert cb[0] == 80 and abs(cb[1] - 2 * ne[1]) < 1e-12 and abs(cb[2] - cb[3]) < 1e-12
+    assert abs(float(first["det"][1]) - np.linalg.det(Aw)) < 1e-9 * abs(np.linalg.det(Aw))
+    assert np.allclose([float(v) for v in first["solve"][1:]], np.linalg.solve(Aw, J.T @ (w * y)), rtol=1e-11)
+    gn = [float(v) for v in first["gn"][1:]]
+    assert gn[0] == 2 and gn[1] == 1 and gn[2] == A.STOP_NAMES.index("converged")
+    assert abs(gn[3] - (y * y).sum()) < 1e-12                                  # chi2 at x = 0
+    assert np.allclose(gn[4:10], np.linalg.lstsq(J, y, rcond=None)[0], rtol=1e-10, atol=1e-12)
+    assert first["throws"][1:] == ["1", "1"]

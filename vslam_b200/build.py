@@ -94,6 +94,21 @@ def build_host_algebra(force=False):
     return HOST_ALGEBRA
 
 
+HOST_LEAST_SQUARES = os.path.join(LIBDIR, "host_least_squares")
+
+
+def build_host_least_squares(force=False):
+    """g++ build of tests/cpp/host_least_squares.cpp (least-squares half of include/vslam_b200.hpp; no GPU needed)."""
+    root = os.path.join(_HERE, "..")
+    src = os.path.join(root, "tests", "cpp", "host_least_squares.cpp")
+    inc = os.path.join(root, "include")
+    deps = [src] + [os.path.join(inc, h) for h in ("vslam_b200.hpp", "vslam_b200.h")]
+    if force or _stale(HOST_LEAST_SQUARES, deps):
+        subprocess.check_call(["/usr/bin/g++", "-std=c++17", "-O2", "-Wall", "-Wextra", "-Werror", "-I", inc, src, "-o",
+                               HOST_LEAST_SQUARES, "-L", LIBDIR, "-lvslam_b200", "-Wl,-rpath,$ORIGIN", "-lpthread"])
+    return HOST_LEAST_SQUARES
+
+
 def build_all(force=False):
     from . import synth
     synth.build(force)
@@ -101,6 +116,7 @@ def build_all(force=False):
     build_host_mirror(force)
     build_odometry_mirror(force)
     build_host_algebra(force)
+    build_host_least_squares(force)
     return lib
 
 
