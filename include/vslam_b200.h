@@ -50,6 +50,17 @@ enum { VSLAMB200_SOLVER_GN = 0, VSLAMB200_SOLVER_LM = 1 };
  * EXTENSION (forward formulation: bilinear sampling, Jacobians at the warped point every iteration, optional depth
  * residual; semantics of lukas_kanade/src/ForwardAdditive.cpp:52-137, defined by oracle/vslam_oracle.cpp) */
 enum { VSLAMB200_SAMPLING_NEAREST = 0, VSLAMB200_SAMPLING_BILINEAR = 1 };
+/* chi2 of one view's normal equations (GaussNewton.cpp:55-61 stops a level when it rises, :86 when it stalls).
+ * REFERENCE (0, the default of a zeroed config): w_0 * sum_k r_k^2 - what NormalEquations.cpp:58,
+ *   `_chi2 = (r * w).transpose() * r` with r and w both column vectors, evaluates to in the reference's Release build:
+ *   Eigen only asserts a product's inner dimension (NDEBUG removes the assertion) and takes it from the left factor,
+ *   1 here, so (r * w)(k) = r(k) * w(0), the weight of the FIRST interest point (row-major order; 0 while that point
+ *   projects outside the image) times the unweighted sum of squared residuals.  This is what oracle/_ref - the
+ *   reference's own sources compiled against the stand-in headers of oracle/ref_shim - computes; whenever w_0 = 0 every
+ *   chi2 is 0 and each level ends "converged" after its second step.
+ * WEIGHTED (1): sum_k w_k r_k^2, the r^T W r that NormalEquations.h documents.
+ * The bilinear extension always uses the weighted sum. */
+enum { VSLAMB200_CHI2_REFERENCE = 0, VSLAMB200_CHI2_WEIGHTED = 1 };
 /* level_kernel: which Gauss-Newton level kernel runs the nearest-sampling path.  AUTO: the dense kernel
  * (csrc/gn_level.cu) for jobs with one keyframe, the moment-based kernel (csrc/gn_mom.cu: keyframes side by side) for
  * stacked jobs where it applies - scalers without offset (identity, t-distribution), at most 8 keyframes per job, the
@@ -77,6 +88,7 @@ typedef struct vslamb200_config
   double lm_down;        /* LM only: lambda *= lm_down after an accepted step (0 < lm_down <= 1) */
   int sampling;          /* VSLAMB200_SAMPLING_* */
   double depth_weight;   /* BILINEAR only: weight of the depth residual Z_to(u',v') - q_z against the photometric one; 0 = off */
+  int chi2_mode;         /* VSLAMB200_CHI2_*: the chi2 of a view's normal equations that drives the solver's stops (NEAREST only) */
   /* execution choices (results do not depend on them beyond rounding); 0 = automatic */
   int level_kernel;      /* VSLAMB200_KERNEL_*: which Gauss-Newton level kernel runs the nearest-sampling path */
   int cluster_size;      /* CTAs per alignment job of the level kernels (1, 2, 4, 8 or 16) */

@@ -547,7 +547,10 @@ private:
   const double _v;
 };
 
-// NormalEquations.h:26-59, NormalEquations.cpp:19-87: A = J^T W J, b = J^T W r, chi2 = r^T W r, nConstraints = rows.
+// NormalEquations.h:26-59, NormalEquations.cpp:19-87: A = J^T W J, b = J^T W r, nConstraints = rows.  chi2: the header
+// documents r^T W r, and addConstraint accumulates that; the (J, r, w) constructor's `(r * w).transpose() * r`
+// (NormalEquations.cpp:58) is a product of two column vectors, which the reference's Release build evaluates as
+// w[0] * sum r_k^2 (see VSLAMB200_CHI2_REFERENCE in vslam_b200.h) - reproduced here, as on the device.
 class NormalEquations
 {
 public:
@@ -569,6 +572,8 @@ public:
   NormalEquations(const MatXd & J, const VecXd & r, const VecXd & w) : NormalEquations(J.cols())
   {
     for (size_t k = 0; k < J.rows(); k++) accumulate(J.row(k), r[k], w[k]);
+    _chi2 = 0.0;
+    for (size_t k = 0; k < r.size(); k++) _chi2 += (r[k] * w[0]) * r[k];
     _nConstraints = r.size();
   }
   void addConstraint(const VecXd & J, double r, double w)
@@ -839,7 +844,8 @@ public:
 
   SE3Alignment(double minGradient, least_squares::Solver::ShPtr solver, least_squares::Loss::ShPtr loss,
                bool includePrior = false, int device = 0, int sampling = VSLAMB200_SAMPLING_NEAREST,
-               double depthWeight = 0.0)  // the last two: extension (bilinear sampling, depth residual), see vslam_b200.h
+               double depthWeight = 0.0,  // these two: extension (bilinear sampling, depth residual), see vslam_b200.h
+               int chi2Mode = VSLAMB200_CHI2_REFERENCE)  // NormalEquations.cpp:58 as built, or r^T W r (vslam_b200.h)
   : _solver(std::move(solver)), _loss(std::move(loss))
   {
     if (!_solver) throw Exception("SE3Alignment: solver is null");
@@ -861,6 +867,7 @@ public:
     cfg.lm_down = _solver->down();
     cfg.sampling = sampling;
     cfg.depth_weight = depthWeight;
+    cfg.chi2_mode = chi2Mode;
     check(vslamb200_create(&cfg, device, &_ctx));
   }
   ~SE3Alignment() override { vslamb200_destroy(_ctx); }

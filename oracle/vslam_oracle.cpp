@@ -569,6 +569,13 @@ struct Config
   // per-iteration Jacobians at the warped point, optionally with a depth residual weighted by depthWeight
   int sampling;
   double depthWeight;
+  // chi2 of one view's normal equations.  1: sum_k w_k r_k^2, the r^T W r that NormalEquations.h documents.
+  // 0: w_0 * sum_k r_k^2, what NormalEquations.cpp:58 `(r * w).transpose() * r` evaluates to in a Release build: r and w
+  // are both column vectors, Eigen only ASSERTS the inner dimension of a product (compiled out by NDEBUG) and takes it
+  // from the left factor, whose column count is 1, so (r * w)(k) = r(k) * w(0) - the weight of the FIRST interest point
+  // (0 when it is invisible) times the unweighted sum of squares.  Derived from Eigen's product rules, and what
+  // oracle/_ref (the reference's sources against oracle/ref_shim) computes; it cannot be measured against real Eigen here.
+  int chi2Mode;
 };
 
 struct Scale
@@ -820,6 +827,11 @@ static NE view_normal_equations(View & V, const Config & cfg, int16_t * rcode)
       b[i] += wj * rk;
     }
     chi2 += rk * wk * rk;
+  }
+  if (cfg.chi2Mode == 0) {
+    chi2 = 0;
+    const double w0 = N ? V.w[0] : 0.0;
+    for (size_t k = 0; k < N; k++) chi2 += (V.r[k] * w0) * V.r[k];
   }
   int idx = 0;
   for (int i = 0; i < 6; i++)
@@ -1241,13 +1253,14 @@ struct vo_config
   double lm_lambda0, lm_up, lm_down;
   int sampling;
   double depth_weight;
+  int chi2_mode;
 };
 
 static vo::Config to_cfg(const vo_config * c)
 {
   return {c->min_gradient, c->loss_kind, c->huber_c, c->loss_v, c->scaler_kind, c->scaler_v,
           c->min_step_size, c->max_iterations, c->include_prior, c->f32_storage, c->solver_kind, c->lm_lambda0, c->lm_up,
-          c->lm_down, c->sampling, c->depth_weight};
+          c->lm_down, c->sampling, c->depth_weight, c->chi2_mode};
 }
 static vo::SE3 to_se3(const double * p)
 {

@@ -308,12 +308,14 @@ def test_least_squares_mirror_scalers_losses_normal_equations_and_gauss_newton(o
     y = np.cos(0.31 * k) * 2.0
     w = 0.5 + (k % 5) * 0.25
     ne = np.array([float(v) for v in first["ne"][1:]])
-    assert ne[0] == 40 and abs(ne[1] - (w * y * y).sum()) < 1e-12
+    # NormalEquations.cpp:58 as the reference's Release build evaluates it: w[0] * sum r^2 (vslam_b200.h, CHI2_REFERENCE)
+    assert ne[0] == 40 and abs(ne[1] - w[0] * (y * y).sum()) < 1e-12
     assert np.allclose(ne[2:8], J.T @ (w * y), rtol=1e-13, atol=1e-13)
     Aw = J.T @ (w[:, None] * J)
     assert np.allclose(ne[8:44].reshape(6, 6), Aw, rtol=1e-13, atol=1e-13)
     cb = [float(v) for v in first["combine"][1:]]
-    assert cb[0] == 80 and abs(cb[1] - 2 * ne[1]) < 1e-12 and abs(cb[2] - cb[3]) < 1e-12
+    # the second part was built with addConstraint, which accumulates r^T W r (NormalEquations.cpp:66)
+    assert cb[0] == 80 and abs(cb[1] - (ne[1] + (w * y * y).sum())) < 1e-12 and abs(cb[2] - cb[3]) < 1e-12
     assert abs(float(first["det"][1]) - np.linalg.det(Aw)) < 1e-9 * abs(np.linalg.det(Aw))
     assert np.allclose([float(v) for v in first["solve"][1:]], np.linalg.solve(Aw, J.T @ (w * y)), rtol=1e-11)
     gn = [float(v) for v in first["gn"][1:]]

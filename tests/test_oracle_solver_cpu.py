@@ -114,11 +114,23 @@ def _normal_equations_numpy(J, r, w, vis):
     return (J * w[:, None]).T @ J / n, (J * w[:, None]).T @ r / n, np.sum(w * r * r) / n
 
 
+def _check_chi2(oracle, cfg, f0, f1, r, w, vis, weighted, tol):
+    """The configuration's default is CHI2_REFERENCE_RELEASE: w[0] * sum r^2, what NormalEquations.cpp:58
+    `(r * w).transpose() * r` gives in a Release build (w[0] = 0 when the first interest point is not visible);
+    CHI2_WEIGHTED is the documented r^T W r."""
+    cfg.chi2_mode = oracle.CHI2_WEIGHTED
+    assert abs(oracle.evaluate(cfg, f0, f1, 0)["chi2"] - weighted) <= tol * weighted
+    cfg.chi2_mode = oracle.CHI2_REFERENCE_RELEASE
+    expect = np.where(vis, w, 0.0)[0] * np.sum(r * r) / len(r)
+    assert abs(oracle.evaluate(cfg, f0, f1, 0)["chi2"] - expect) <= tol * max(expect, 1e-300)
+
+
 def test_tdistribution_scale_and_weights(oracle, synth):
     p = _small_pair(synth)
     f0, f1 = _frames(oracle, p, 1)
     v = 5.0
-    ev = oracle.evaluate(oracle.make_config(v=v), f0, f1, 0, want_J=True)
+    cfg = oracle.make_config(v=v)
+    ev = oracle.evaluate(cfg, f0, f1, 0, want_J=True)
     r, vis = _residual_vector(oracle, ev)
     assert ev["n"] == len(r) > 1000 and 0 < vis.sum() < len(r)
     sigma = _tdist_scale_numpy(r, v)
@@ -128,7 +140,7 @@ def test_tdistribution_scale_and_weights(oracle, synth):
     A, b, chi2 = _normal_equations_numpy(ev["J"], r, (v + 1.0) / (v + (r / sigma) ** 2), vis)
     assert np.allclose(ev["A"], A, rtol=1e-10, atol=1e-10 * np.abs(A).max())
     assert np.allclose(ev["b"], b, rtol=1e-10, atol=1e-10 * np.abs(b).max())
-    assert abs(ev["chi2"] - chi2) < 1e-10 * chi2
+    _check_chi2(oracle, cfg, f0, f1, r, (v + 1.0) / (v + (r / sigma) ** 2), vis, chi2, 1e-10)
 
 
 @pytest.mark.parametrize("loss,scaler", [("QUADRATIC", "IDENTITY"), ("HUBER", "MEDIAN"), ("TUKEY", "MEDIAN"),
@@ -164,17 +176,24 @@ def test_other_losses_and_scalers(oracle, synth, loss, scaler):
     A, b, chi2 = _normal_equations_numpy(ev["J"], r, w, vis)
     assert np.allclose(ev["A"], A, rtol=1e-9, atol=1e-10 * np.abs(A).max())
     assert np.allclose(ev["b"], b, rtol=1e-9, atol=1e-10 * np.abs(b).max())
-    assert abs(ev["chi2"] - chi2) <= 1e-9 * chi2
+    _check_chi2(oracle, cfg, f0, f1, r, w, vis, chi2, 1e-9)
 
 
 def test_align_recovers_the_synthetic_motion(oracle, synth):
     """End to end on a rendered pair: the estimated relative pose is the one the scene was rendered with."""
     p = synth.make_pair(320, 240, 1234)
     f0, f1 = _frames(oracle, p, 3)
-    res = oracle.align(oracle.make_config(max_iterations=50), f0, oracle.IDENTITY, f1, oracle.IDENTITY)
+    res = oracle.align(oracle.make_config(max_iterations=50, chi2_mode=oracle.CHI2_WEIGHTED), f0, oracle.IDENTITY, f1,
+                       oracle.IDENTITY)
     d = oracle.se3_log(oracle.se3_mul(res["pose"], oracle.se3_inv(p["pose1"])))
     assert np.linalg.norm(d[:3]) < 5e-3 and np.linalg.norm(d[3:]) < 5e-3, d
     assert res["status"] == 0
+    # The reference's Release-build chi2 (w[0] * sum r^2, vslam_b200.h) follows the unweighted sum of squares scaled by
+    # the first interest point's weight: it stops the levels earlier, a little further from the rendered motion.
+    ref = oracle.align(oracle.make_config(max_iterations=50), f0, oracle.IDENTITY, f1, oracle.IDENTITY)
+    assert ref["status"] == 0 and sum(ref["iters"]) < sum(res["iters"])
+    dr = oracle.se3_log(oracle.se3_mul(ref["pose"], oracle.se3_inv(p["pose1"])))
+    assert np.linalg.norm(dr[:3]) < 1.5e-2 and np.linalg.norm(dr[3:]) < 1e-2, dr
     assert all(1 <= i <= 50 for i in res["iters"])
     # covariance is the inverse of a symmetric positive definite matrix
     assert np.allclose(res["cov"], res["cov"].T, rtol=1e-8, atol=1e-14)
@@ -220,7 +239,8 @@ def test_levenberg_marquardt_extension(oracle, synth):
     L = 3
     f0 = O.Frame(p["gray0"], p["depth0"].astype(np.float64), *p["cam"], L)
     f1 = O.Frame(p["gray1"], p["depth1"].astype(np.float64), *p["cam"], L)
-    cfg = O.make_config(solver=O.SOLVER_LM, max_iterations=40, lm_lambda0=1e-2, lm_up=8.0, lm_down=0.25)
+    cfg = O.make_config(solver=O.SOLVER_LM, max_iterations=40, lm_lambda0=1e-2, lm_up=8.0, lm_down=0.25,
+                        chi2_mode=O.CHI2_WEIGHTED)  # accept / reject needs the weighted sum the steps minimise
     r = O.align(cfg, f0, O.IDENTITY, f1, O.IDENTITY, want_trace=True)
     assert r["status"] == 0
     ups = downs = 0
@@ -244,7 +264,7 @@ def test_levenberg_marquardt_extension(oracle, synth):
     assert ups > 0 and downs > 0
     d = O.se3_log(O.se3_mul(r["pose"], O.se3_inv(p["pose1"])))
     assert np.linalg.norm(d[:3]) < 0.01 and np.linalg.norm(d[3:]) < 0.01
-    gn = O.align(O.make_config(max_iterations=40), f0, O.IDENTITY, f1, O.IDENTITY)
+    gn = O.align(O.make_config(max_iterations=40, chi2_mode=O.CHI2_WEIGHTED), f0, O.IDENTITY, f1, O.IDENTITY)
     d = O.se3_log(O.se3_mul(r["pose"], O.se3_inv(gn["pose"])))
     assert np.linalg.norm(d) < 5e-3                             # both solvers end in the same basin
 
@@ -259,7 +279,7 @@ def test_bilinear_depth_extension(oracle, synth):
     L = 3
     f0 = O.Frame(p["gray0"], p["depth0"].astype(np.float64), *p["cam"], L)
     f1 = O.Frame(p["gray1"], p["depth1"].astype(np.float64), *p["cam"], L)
-    near = O.align(O.make_config(max_iterations=40), f0, O.IDENTITY, f1, O.IDENTITY)
+    near = O.align(O.make_config(max_iterations=40, chi2_mode=O.CHI2_WEIGHTED), f0, O.IDENTITY, f1, O.IDENTITY)
     res = {}
     for dw in (0.0, 1e6):
         cfg = O.make_config(max_iterations=40, sampling=O.SAMPLING_BILINEAR, depth_weight=dw)

@@ -19,6 +19,9 @@ RGB, BGR = 0, 1
 SOLVER_GN, SOLVER_LM = 0, 1
 SAMPLING_NEAREST, SAMPLING_BILINEAR = 0, 1
 KERNEL_AUTO, KERNEL_DENSE, KERNEL_MOMENTS = 0, 1, 2
+# chi2 of a view's normal equations: as the reference's Release build evaluates NormalEquations.cpp:58 (w_0 * sum r^2),
+# or the documented r^T W r (vslam_b200.h)
+CHI2_REFERENCE, CHI2_WEIGHTED = 0, 1
 R_NOT_INTEREST, R_INVISIBLE = -32768, -32767
 STOP_NAMES = ["maxiter", "constraints", "hessian", "chi2", "converged", "nan"]
 
@@ -28,7 +31,7 @@ class Config(C.Structure):
                 ("loss_v", C.c_double), ("scaler_kind", C.c_int), ("scaler_v", C.c_double),
                 ("min_step_size", C.c_double), ("max_iterations", C.c_int), ("include_prior", C.c_int),
                 ("solver_kind", C.c_int), ("lm_lambda0", C.c_double), ("lm_up", C.c_double), ("lm_down", C.c_double),
-                ("sampling", C.c_int), ("depth_weight", C.c_double), ("level_kernel", C.c_int),
+                ("sampling", C.c_int), ("depth_weight", C.c_double), ("chi2_mode", C.c_int), ("level_kernel", C.c_int),
                 ("cluster_size", C.c_int), ("stream_parts", C.c_int)]
 
 
@@ -119,7 +122,7 @@ def ptr(a):
 def make_config(min_gradient=30.0, loss=LOSS_TDIST, scaler=SCALER_TDIST, huber_c=1.345, v=5.0,
                 min_step_size=1e-7, max_iterations=100, include_prior=False, solver=SOLVER_GN, lm_lambda0=1e-3,
                 lm_up=10.0, lm_down=0.1, sampling=SAMPLING_NEAREST, depth_weight=0.0, level_kernel=None,
-                cluster_size=None, stream_parts=None):
+                cluster_size=None, stream_parts=None, chi2_mode=CHI2_REFERENCE):
     """level_kernel / cluster_size / stream_parts: execution choices (0 = automatic).  When not given they come from the
     environment (VSLAMB200_KERNEL = dense | moments, VSLAMB200_CLUSTER, VSLAMB200_PARTS): the switches of the tuning
     tools live in this binding, the library itself reads no environment variable."""
@@ -130,7 +133,7 @@ def make_config(min_gradient=30.0, loss=LOSS_TDIST, scaler=SCALER_TDIST, huber_c
     if stream_parts is None:
         stream_parts = int(os.environ.get("VSLAMB200_PARTS", "0"))
     return Config(min_gradient, loss, huber_c, v, scaler, v, min_step_size, max_iterations, int(include_prior), solver,
-                  lm_lambda0, lm_up, lm_down, sampling, depth_weight, level_kernel, cluster_size, stream_parts)
+                  lm_lambda0, lm_up, lm_down, sampling, depth_weight, chi2_mode, level_kernel, cluster_size, stream_parts)
 
 
 class Context:

@@ -376,6 +376,8 @@ static int check_cfg(const vslamb200_config * cfg)
   if (cfg->sampling != VSLAMB200_SAMPLING_NEAREST && cfg->sampling != VSLAMB200_SAMPLING_BILINEAR)
     return fail(VSLAMB200_EINVAL, "bad sampling");
   if (!(cfg->depth_weight >= 0.0)) return fail(VSLAMB200_EINVAL, "bad depth_weight");
+  if (cfg->chi2_mode != VSLAMB200_CHI2_REFERENCE && cfg->chi2_mode != VSLAMB200_CHI2_WEIGHTED)
+    return fail(VSLAMB200_EINVAL, "bad chi2_mode");
   if (cfg->level_kernel < 0 || cfg->level_kernel > VSLAMB200_KERNEL_MOMENTS) return fail(VSLAMB200_EINVAL, "bad level_kernel");
   if (cfg->cluster_size != 0 && cfg->cluster_size != 1 && cfg->cluster_size != 2 && cfg->cluster_size != 4 &&
       cfg->cluster_size != 8 && cfg->cluster_size != 16)
@@ -738,6 +740,7 @@ vb::SolverParams solver_params(const vslamb200_config & cfg)
   p.lmDown = cfg.lm_down;
   p.sampling = cfg.sampling;
   p.depthWeight = cfg.depth_weight;
+  p.chi2Mode = cfg.chi2_mode;
   return p;
 }
 

@@ -139,6 +139,7 @@ struct SolverParams
   double lmLambda0, lmUp, lmDown;
   int sampling;              // VSLAMB200_SAMPLING_*
   double depthWeight;
+  int chi2Mode;              // VSLAMB200_CHI2_*
 };
 
 // ------------------------------------------------------------------------------------------------

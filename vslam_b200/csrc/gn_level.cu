@@ -149,8 +149,19 @@ __device__ void compute_scale(
   offsetOut = s_offset;
 }
 
+// w_0 of VSLAMB200_CHI2_REFERENCE: the weight of the first interest point under the evaluation's scale (0 when it is not
+// visible or the list is empty).  V.r[0] was written in phase A by the cluster's leading CTA.
+__device__ __forceinline__ double first_point_weight(const SolverParams & p, const ViewState & V, double scale, double offset)
+{
+  if (V.nIp < 1) return 0.0;
+  const int code = *reinterpret_cast<const volatile int16_t *>(V.r);
+  if (code == R_CODE_INVISIBLE) return 0.0;
+  return p.lossKind == VSLAMB200_LOSS_NONE ? 1.0 : loss_weight(p, ((double)(code - 255) - offset) / scale);
+}
+
 // Weight table {sqrt(w(r)), sqrt(w(r)) r} per residual code (Loss.cpp:51-92); code 511 (not visible) -> {0, 0}.
-// Returns this thread's share of chi2 = sum_k w_k r_k^2 (NormalEquations.cpp:58) given its visible counts.
+// Returns this thread's share of sum_k w_k r_k^2 (VSLAMB200_CHI2_WEIGHTED) or of sum_k r_k^2 (VSLAMB200_CHI2_REFERENCE,
+// multiplied by the first point's weight afterwards: NormalEquations.cpp:58, see vslam_b200.h) given its visible counts.
 __device__ __forceinline__ double build_weights(
   const SolverParams & p, double scale, double offset, double2 * lut, const double (&nvis)[BPT])
 {
@@ -165,7 +176,7 @@ __device__ __forceinline__ double build_weights(
     // (sqrt(w) J)(sqrt(w) J)^T, which saves the six w * J_i products per point
     const double sw = sqrt(w);
     lut[b] = b == HIST_BINS - 1 ? make_double2(0.0, 0.0) : make_double2(sw, sw * r);
-    c2 = fma(nvis[j], wr * r, c2);
+    c2 = fma(nvis[j], p.chi2Mode == VSLAMB200_CHI2_WEIGHTED ? wr * r : r * r, c2);
   }
   return c2;
 }
@@ -433,8 +444,13 @@ __global__ void __launch_bounds__(GT, CTAS_PER_SM) gn_level_kernel(
         cluster.sync();
         sublap(8);
         const double c2 = build_weights(p, S.so[0], S.so[1], S.lut, nvis);
-        if (rank == 0) chi2View = block_sum(c2, S.red);  // contains the barrier that publishes the table
-        else __syncthreads();
+        if (rank == 0) {
+          chi2View = block_sum(c2, S.red);  // contains the barrier that publishes the table
+          if (p.chi2Mode == VSLAMB200_CHI2_REFERENCE)
+            chi2View *= first_point_weight(p, V, S.so[0], S.so[1]);  // this CTA wrote the code in phase A
+        } else {
+          __syncthreads();
+        }
         sublap(9);
         hb ^= 1;
         lap(2);

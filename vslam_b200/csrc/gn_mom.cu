@@ -649,9 +649,20 @@ static __device__ __noinline__ void scale_and_fold(
     wA[tid] = w;
     wB[tid] = wr;
     const int cnt = tid == 0 ? 0 : S.tot[255 + tid] + S.tot[255 - tid];
-    c2 = (double)cnt * (wr * r);
+    c2 = (double)cnt * (p.chi2Mode == VSLAMB200_CHI2_WEIGHTED ? wr * r : r * r);
   }
-  const double chi2 = block_sum(c2, S.red);  // contains the barriers that publish the tables
+  double chi2 = block_sum(c2, S.red);  // contains the barriers that publish the tables
+  if (p.chi2Mode == VSLAMB200_CHI2_REFERENCE && srank == 0) {
+    // NormalEquations.cpp:58 as the reference's Release build evaluates it (vslam_b200.h): the weight of the view's first
+    // interest point times the plain sum of squares.  This CTA owns the first slice and wrote the code itself.
+    double w0 = 0.0;
+    if (n > 0) {
+      const int code = *reinterpret_cast<const volatile int16_t *>(V.r);
+      if (code != R_CODE_INVISIBLE)
+        w0 = p.lossKind == VSLAMB200_LOSS_NONE ? 1.0 : loss_weight(p, (double)(code - 255) / S.sigma);
+    }
+    chi2 *= w0;
+  }
   lap(2);
   // A, b of the slice from its moments: warp g folds the magnitudes [32 g, 32 g + 32), lane t owns term t; fixed order
   if (lane < NTERM) {
