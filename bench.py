@@ -110,9 +110,9 @@ def dist_env():
 IDENT7 = np.array([0, 0, 0, 1, 0, 0, 0], np.float64)
 WORKLOAD_TEXT = {
     "pairs": "BASELINE configs[2]: {P} independent synthetic 640x480 frame pairs (seeds 1234..{last}), dealt round-robin over "
-             "the GPUs, t-distribution weights, 4 levels, GaussNewton(1e-7,100), minGradient 30, start at identity",
+             "the GPUs, t-distribution weights, 4 levels, GaussNewton(1e-7,100), minGradient 30, start at identity, chi2 as the reference's Release build evaluates it",
     "sequence": "BASELINE configs[1]: synthetic TUM-shape 640x480 sequence of {F} frames per GPU, frame-to-frame alignment "
-                "({P} pairs per batch), t-distribution weights, 4 levels, GaussNewton(1e-7,100), minGradient 30",
+                "({P} pairs per batch), t-distribution weights, 4 levels, GaussNewton(1e-7,100), minGradient 30, chi2 as the reference's Release build evaluates it",
 }
 
 
@@ -428,7 +428,10 @@ def main():
         checks["error_vs_ground_truth"] = {"max": float(errs.max()), "median": float(np.median(errs)),
                                            "pairs_within_0.01": int((errs < 0.01).sum()), "pairs": int(args.pairs),
                                            "worst_pair": int(errs.argmax())}
-        assert (errs < 0.01).mean() > 0.99, checks
+        # With the chi2 the reference's Release build computes (VSLAMB200_CHI2_REFERENCE: w[0] * sum r^2, vslam_b200.h) the
+        # levels stop earlier than with the weighted sum: about nine pairs in ten reach 0.01 (the CPU oracle and oracle/_ref
+        # give the same poses); every pair is within 0.02.
+        assert np.median(errs) < 0.01 and (errs < 0.02).mean() > 0.99, checks
 
     cpu = None
     if rank == 0 and not args.no_cpu:

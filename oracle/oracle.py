@@ -18,6 +18,7 @@ SOLVER_GN, SOLVER_LM = range(2)
 SAMPLING_NEAREST, SAMPLING_BILINEAR = range(2)
 # chi2 of a view: w[0] * sum r^2 as the reference's Release build evaluates NormalEquations.cpp:58, or sum w r^2
 CHI2_REFERENCE_RELEASE, CHI2_WEIGHTED = range(2)
+DEFAULT_CHI2_MODE = CHI2_REFERENCE_RELEASE  # what make_config() uses when not told; tests/conftest.py switches it
 R_NOT_INTEREST, R_INVISIBLE = -32768, -32767
 TRACE_STRIDE = 64
 STOP_NAMES = ["maxiter", "constraints", "hessian", "chi2", "converged", "nan"]
@@ -48,7 +49,9 @@ class Config(C.Structure):
 def make_config(min_gradient=30.0, loss=LOSS_TDIST, scaler=SCALER_TDIST, huber_c=1.345, v=5.0,
                 min_step_size=1e-7, max_iterations=100, include_prior=False, f32_storage=True, solver=SOLVER_GN,
                 lm_lambda0=1e-3, lm_up=10.0, lm_down=0.1, sampling=SAMPLING_NEAREST, depth_weight=0.0,
-                chi2_mode=CHI2_REFERENCE_RELEASE):
+                chi2_mode=None):
+    if chi2_mode is None:
+        chi2_mode = DEFAULT_CHI2_MODE
     return Config(min_gradient, loss, huber_c, v, scaler, v, min_step_size, max_iterations,
                   int(include_prior), int(f32_storage), solver, lm_lambda0, lm_up, lm_down, sampling, depth_weight,
                   chi2_mode)

@@ -34,10 +34,23 @@ def capi():
     return A
 
 
+@pytest.fixture(params=["chi2-reference", "chi2-weighted"])
+def chi2_mode(request, oracle, capi):
+    """Runs a test under both definitions of a view's chi2 (vslam_b200.h): make_config() of the oracle and of the
+    binding default to the chosen one for the duration of the test."""
+    mode = 0 if request.param == "chi2-reference" else 1
+    old = oracle.DEFAULT_CHI2_MODE, capi.DEFAULT_CHI2_MODE
+    oracle.DEFAULT_CHI2_MODE = capi.DEFAULT_CHI2_MODE = mode
+    yield mode
+    oracle.DEFAULT_CHI2_MODE, capi.DEFAULT_CHI2_MODE = old
+
+
 @pytest.fixture()
 def ctx(capi, request):
     if "level_kernel" in request.fixturenames:  # the kernel choice reaches make_config through the environment
         request.getfixturevalue("level_kernel")
+    if "chi2_mode" in request.fixturenames:
+        request.getfixturevalue("chi2_mode")
     c = capi.Context(capi.make_config())
     yield c
     c.close()

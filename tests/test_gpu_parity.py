@@ -49,7 +49,7 @@ def level_kernel(request, monkeypatch):
     return request.param
 
 
-def test_level_kernels_agree_and_repeat_on_a_multi_wave_batch(capi, synth):
+def test_level_kernels_agree_and_repeat_on_a_multi_wave_batch(capi, synth, chi2_mode):
     """512 small jobs (more CTAs than the device holds at once, so SMs are shared between jobs in different phases): the
     moment kernel and the dense kernel give the same iteration counts and poses, and the moment kernel is bit-identical
     run to run.  (This is the case that exposed a stage refill overtaking the loads of the stage: see start_chunk.)"""
@@ -123,7 +123,7 @@ def test_pyramid_and_gradients_exact_on_random_images(ctx, oracle, W, H, levels)
             assert np.array_equal(got["Z"].astype(np.float64), ref["Z"]), (k, l)
 
 
-def test_real_tum_frame_pair_matches_oracle(ctx, capi, oracle, level_kernel):
+def test_real_tum_frame_pair_matches_oracle(ctx, capi, oracle, level_kernel, chi2_mode):
     """The one real RGB-D frame the reference ships (odometry/test/resource; crops in tests/golden/tum_frame.npz, made by
     tests/golden/make_tum_frame.py): real texture and 40 % invalid depth.  Every pyramid level bit-exact, then the
     alignment of the two crops: same iteration counts, stop reasons and pose as the oracle, with every level kernel."""
@@ -200,7 +200,7 @@ def test_rgbd_ingestion_matches_the_node(ctx, oracle, synth, depth_kind, bgr):
 @pytest.mark.parametrize("loss,scaler", [("TDIST", "TDIST"), ("NONE", "IDENTITY"), ("HUBER", "MEAN"), ("TUKEY", "MEDIAN"),
                                          ("HUBER", "MEDIAN"), ("QUADRATIC", "IDENTITY")])
 @pytest.mark.parametrize("holes", [0, 50])
-def test_single_iteration_masks_and_normal_equations(ctx, capi, oracle, synth, loss, scaler, holes):
+def test_single_iteration_masks_and_normal_equations(ctx, capi, oracle, synth, loss, scaler, holes, chi2_mode):
     O, A = oracle, capi
     p = _pair(synth, 640, 480, 1234, holes)
     f0, f1 = _frames(O, p, 4)
@@ -258,7 +258,7 @@ def _teacher_forced_check(O, ocfg, frames_from, from_poses, f1, to_pose, multi, 
 
 @pytest.mark.parametrize("loss,scaler,prior", [("TDIST", "TDIST", False), ("TDIST", "TDIST", True), ("NONE", "IDENTITY", False),
                                                ("HUBER", "MEAN", False), ("TUKEY", "MEDIAN", True)])
-def test_align_matches_oracle_per_iteration(ctx, capi, oracle, synth, loss, scaler, prior, level_kernel):
+def test_align_matches_oracle_per_iteration(ctx, capi, oracle, synth, loss, scaler, prior, level_kernel, chi2_mode):
     O, A = oracle, capi
     p = _pair(synth, 640, 480, 1234)
     f0, f1 = _frames(O, p, 4)
@@ -287,7 +287,7 @@ def test_align_matches_oracle_per_iteration(ctx, capi, oracle, synth, loss, scal
     assert rel_fro(got["cov"], ref["cov"]) < 1e-3
 
 
-def test_batch_of_pairs_matches_oracle(ctx, capi, oracle, synth, level_kernel):
+def test_batch_of_pairs_matches_oracle(ctx, capi, oracle, synth, level_kernel, chi2_mode):
     """BASELINE configs[2] in small: independent pairs in ONE batched call, each against the oracle."""
     O, A = oracle, capi
     n, L = 6, 4
@@ -313,7 +313,7 @@ def test_batch_of_pairs_matches_oracle(ctx, capi, oracle, synth, level_kernel):
 
 
 @pytest.mark.parametrize("cluster", [0, 1, 2, 4])
-def test_moment_kernel_stays_exact_under_many_changes(capi, oracle, synth, cluster):
+def test_moment_kernel_stays_exact_under_many_changes(capi, oracle, synth, cluster, chi2_mode):
     """The moment-based kernel moves the moments of every point whose residual changed from the old to the new cell;
     the fixed-point cells must stay exactly what a fresh build would give.  Pairs with a deliberately bad initial guess
     (large per-level motion: many points change per iteration), depth holes, every pyramid level: every iteration's normal
@@ -351,7 +351,7 @@ def test_moment_kernel_stays_exact_under_many_changes(capi, oracle, synth, clust
                 a = traces[k][l, i]
                 assert a[0] == 1 and a[1] == e["n"], (k, l, i)
                 worst = max(worst, rel_fro(a[18:54].reshape(6, 6), e["A"]), rel_fro(a[12:18], e["b"]),
-                            abs(a[2] - e["chi2"]) / abs(e["chi2"]))
+                            abs(a[2] - e["chi2"]) / max(abs(e["chi2"]), 1e-300))
                 se3 = O.se3_mul(se3, O.se3_exp(-a[54:60]))
     assert worst < 1e-9, worst
     ocfg = O.make_config()
@@ -364,7 +364,7 @@ def test_moment_kernel_stays_exact_under_many_changes(capi, oracle, synth, clust
 
 
 @pytest.mark.parametrize("K,prior", [(2, True), (3, False)])
-def test_multi_keyframe_matches_oracle(ctx, capi, oracle, synth, K, prior):
+def test_multi_keyframe_matches_oracle(ctx, capi, oracle, synth, K, prior, chi2_mode):
     """SE3Alignment::align(vector<from>, to): stacked normal equations over K keyframes (320x240, 3 levels)."""
     O, A = oracle, capi
     W, H, L = 320, 240, 3
@@ -424,7 +424,7 @@ def test_config4_kitti_shape_five_levels(ctx, capi, oracle, synth, level_kernel)
         ctx.align([dict(to=12, to_pose=O.IDENTITY, frm=[11], from_poses=O.IDENTITY, multi=False)])
 
 
-def test_config5_one_frame_against_eight_keyframes_720p(ctx, capi, oracle, synth):
+def test_config5_one_frame_against_eight_keyframes_720p(ctx, capi, oracle, synth, chi2_mode):
     """BASELINE configs[4]: frame-to-multi-keyframe alignment, 1 frame against 8 keyframes jointly at 1280x720,
     keyframes on a circle of radius 0.03 m / 0.015 rad around the target, stacked normal equations
     (SE3Alignment.cpp:106-146, InverseCompositionalStacked.cpp:25-48)."""
@@ -654,12 +654,14 @@ def test_cpp_odometry_mirror_matches_the_oracle_loop(oracle, synth, capi, tmp_pa
 
 
 @pytest.mark.gpu
-def test_sequence_trajectory_rpe_and_ate_against_ground_truth(capi, oracle, synth, tmp_path):
+def test_sequence_trajectory_rpe_and_ate_against_ground_truth(capi, oracle, synth, tmp_path, chi2_mode):
     """BASELINE configs[1] in small, end to end on both sides of the path: a rendered 40-frame sequence, frame-to-frame
     alignment of all pairs in one batched call, relative poses chained into a trajectory (vslam_b200/shard.py),
     written as TUM files and scored with the RPE / ATE of the reference's evaluation scripts
-    (vslam_b200/evaluation.py).  The bounds are the CPU oracle's figures on the same sequence (RPE 4.6 mm / 1.9 mrad per
-    frame at 320x240 and 3 levels, ATE 25 mm over 40 frames) plus head-room; the reference's own tests ask < 0.01 per pair."""
+    (vslam_b200/evaluation.py).  The bounds are the CPU oracle's figures on the same sequence plus head-room: with the
+    weighted chi2 RPE 4.6 mm / 1.9 mrad per frame at 320x240 and 3 levels, ATE 25 mm over 40 frames; with the chi2 of the
+    reference's Release build (levels stop earlier) 7.1 mm / 3.3 mrad and 75 mm.  The reference's own tests ask < 0.01
+    per pair."""
     from vslam_b200 import evaluation as E, shard
     F, W, H, L = 40, 320, 240, 3
     cam = synth.cam_for(W, H)
@@ -678,10 +680,11 @@ def test_sequence_trajectory_rpe_and_ate_against_ground_truth(capi, oracle, synt
     tg, te = E.read_trajectory(str(tmp_path / "gt.txt")), E.read_trajectory(str(tmp_path / "est.txt"))
     rpe = E.relative_pose_error(tg, te, 1, "f")
     assert len(rpe) == F - 2                                         # the script leaves out pairs ending at the last pose
-    assert E.stats(rpe[:, 4])["rmse"] < 0.006 and E.stats(rpe[:, 5])["rmse"] < 0.003
-    assert E.stats(rpe[:, 4])["max"] < 0.01
+    t_rmse, r_rmse, t_max, ate_rmse = (0.006, 0.003, 0.01, 0.035) if chi2_mode == capi.CHI2_WEIGHTED else (0.009, 0.0045, 0.013, 0.1)
+    assert E.stats(rpe[:, 4])["rmse"] < t_rmse and E.stats(rpe[:, 5])["rmse"] < r_rmse
+    assert E.stats(rpe[:, 4])["max"] < t_max
     ate = E.absolute_trajectory_error(tg, te)
-    assert len(ate["matches"]) == F and ate["rmse"] < 0.035
+    assert len(ate["matches"]) == F and ate["rmse"] < ate_rmse
 
 
 @pytest.mark.gpu
@@ -702,7 +705,8 @@ def test_levenberg_marquardt_extension_matches_oracle(ctx, capi, oracle, synth, 
         frames.append(O.Frame(g, d.astype(np.float64), *cam, L))
         poses.append(synth.pose7(R, t))
     ctx.upload(np.arange(K + 1), np.stack([g for g, _ in raw]), np.stack([d for _, d in raw]), cam, L)
-    kw = dict(max_iterations=40, include_prior=prior, lm_lambda0=1e-2, lm_up=8.0, lm_down=0.25)
+    kw = dict(max_iterations=40, include_prior=prior, lm_lambda0=1e-2, lm_up=8.0, lm_down=0.25,
+              chi2_mode=O.CHI2_WEIGHTED)  # accept / reject needs the weighted sum the steps minimise
     ocfg = O.make_config(solver=O.SOLVER_LM, **kw)
     ctx.set_config(A.make_config(solver=A.SOLVER_LM, **kw))
     ctx.set_trace(True)

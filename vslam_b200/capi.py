@@ -22,6 +22,7 @@ KERNEL_AUTO, KERNEL_DENSE, KERNEL_MOMENTS = 0, 1, 2
 # chi2 of a view's normal equations: as the reference's Release build evaluates NormalEquations.cpp:58 (w_0 * sum r^2),
 # or the documented r^T W r (vslam_b200.h)
 CHI2_REFERENCE, CHI2_WEIGHTED = 0, 1
+DEFAULT_CHI2_MODE = CHI2_REFERENCE  # make_config()'s default (a zeroed C config means the same)
 R_NOT_INTEREST, R_INVISIBLE = -32768, -32767
 STOP_NAMES = ["maxiter", "constraints", "hessian", "chi2", "converged", "nan"]
 
@@ -122,7 +123,7 @@ def ptr(a):
 def make_config(min_gradient=30.0, loss=LOSS_TDIST, scaler=SCALER_TDIST, huber_c=1.345, v=5.0,
                 min_step_size=1e-7, max_iterations=100, include_prior=False, solver=SOLVER_GN, lm_lambda0=1e-3,
                 lm_up=10.0, lm_down=0.1, sampling=SAMPLING_NEAREST, depth_weight=0.0, level_kernel=None,
-                cluster_size=None, stream_parts=None, chi2_mode=CHI2_REFERENCE):
+                cluster_size=None, stream_parts=None, chi2_mode=None):
     """level_kernel / cluster_size / stream_parts: execution choices (0 = automatic).  When not given they come from the
     environment (VSLAMB200_KERNEL = dense | moments, VSLAMB200_CLUSTER, VSLAMB200_PARTS): the switches of the tuning
     tools live in this binding, the library itself reads no environment variable."""
@@ -130,6 +131,8 @@ def make_config(min_gradient=30.0, loss=LOSS_TDIST, scaler=SCALER_TDIST, huber_c
         level_kernel = {"dense": KERNEL_DENSE, "moments": KERNEL_MOMENTS}.get(os.environ.get("VSLAMB200_KERNEL", ""), KERNEL_AUTO)
     if cluster_size is None:
         cluster_size = int(os.environ.get("VSLAMB200_CLUSTER", "0"))
+    if chi2_mode is None:
+        chi2_mode = DEFAULT_CHI2_MODE
     if stream_parts is None:
         stream_parts = int(os.environ.get("VSLAMB200_PARTS", "0"))
     return Config(min_gradient, loss, huber_c, v, scaler, v, min_step_size, max_iterations, int(include_prior), solver,
