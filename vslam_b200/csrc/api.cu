@@ -871,8 +871,9 @@ int run_level(vslamb200_ctx * c, Problem & P, int level, const vb::SolverParams 
 
   if (c->timing) CK(cudaEventRecord(c->ev[0], stream));
   vb::launch_level_setup(table, dJobs, dViews, view0, nViews, level, stream);
+  const bool moments = sp.sampling != VSLAMB200_SAMPLING_BILINEAR && use_moments(c->cfg, P, sp, npx);
   vb::launch_build_lists(table, dViews, dJobs, view0, nViews, level, npx, sp.minGradient2, c->chunkCounts.as<int>(),
-                         listChunks, stream);
+                         listChunks, moments ? 1 : 0, stream);
   vb::launch_level_begin(dJobs, dViews, job0, nJobs, level, stream);
   if (c->timing) CK(cudaEventRecord(c->ev[1], stream));
   if (sp.sampling == VSLAMB200_SAMPLING_BILINEAR) {
@@ -891,7 +892,7 @@ int run_level(vslamb200_ctx * c, Problem & P, int level, const vb::SolverParams 
         if (active == 0) break;
       }
     }
-  } else if (use_moments(c->cfg, P, sp, npx)) {
+  } else if (moments) {
     c->stats.moment_launches++;
     CK(vb::launch_gn_mom(dJobs, dViews, job0, nJobs, P.maxViews, pick_cpv(c->cfg, npx, nJobs, P.maxViews), sp, level, maxEvals,
                          dTrace, traceJobStride, c->partials.as<double>(), stream));
@@ -901,7 +902,8 @@ int run_level(vslamb200_ctx * c, Problem & P, int level, const vb::SolverParams 
                            traceJobStride, c->partials.as<double>(), stream));
   }
   if (c->timing) CK(cudaEventRecord(c->ev[2], stream));
-  c->stats.kernel_launches += 6;
+  // level setup, list build, level begin, and the level kernel (the bilinear extension counted its own above)
+  c->stats.kernel_launches += sp.sampling == VSLAMB200_SAMPLING_BILINEAR ? 3 : 4;
   CK(cudaGetLastError());
   if (c->timing) {
     CK(cudaStreamSynchronize(stream));
@@ -1087,7 +1089,7 @@ int vslamb200_evaluate(
   const vb::FrameDev * table = c->dFrames.as<vb::FrameDev>();
   vb::launch_level_setup(table, dJobs, dViews, 0, nViews, level, c->stream);
   vb::launch_build_lists(table, dViews, dJobs, 0, nViews, level, npx, sp.minGradient2, c->chunkCounts.as<int>(),
-                         vb::list_chunks_for(npx), c->stream);
+                         vb::list_chunks_for(npx), use_moments(c->cfg, P, sp, npx) ? 1 : 0, c->stream);
   vb::launch_level_begin(dJobs, dViews, 0, nJobs, level, c->stream);
   vb::ViewState V;
   CK(cudaMemcpyAsync(&V, dViews, sizeof(V), cudaMemcpyDeviceToHost, c->stream));
@@ -1106,7 +1108,7 @@ int vslamb200_evaluate(
     CK(vb::launch_gn_level(dJobs, dViews, 0, nJobs, 1, pick_cluster(c->cfg, npx, 1), sp, level, 1, nullptr, 0,
                            c->partials.as<double>(), c->stream));
   }
-  c->stats.kernel_launches += 6;
+  c->stats.kernel_launches += 4;
   if (rcode) {
     CK(c->plane.ensure((size_t)npx * 2));
     vb::launch_scatter_rcode(dViews, 0, c->plane.as<int16_t>(), c->stream);

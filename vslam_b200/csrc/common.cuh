@@ -72,6 +72,7 @@ struct ViewState
   uint32_t * perm;          // moments kernel: list indices of a CTA's slice ordered by residual code (first evaluation)
   unsigned jstat[JSTAT];    // float bits (non-negative): bounds of the Jacobian components over the list (lists.cu)
   int nIp;                  // retained interest points (nConstraints of this view)
+  int listTicket;           // lists.cu: next chunk of this view to hand to a block (zero at the start of a level)
   // warp
   Pose poseRef;             // keyframe pose
   Pose se3;                 // poseCur * poseRef^-1
@@ -286,7 +287,8 @@ void launch_pyramid_level(const FrameDev * frames, const int * slots, int n, int
 void launch_gradients(const FrameDev * frames, const int * slots, int n, int level, int W, int H, cudaStream_t s);
 // lists.cu
 void launch_build_lists(const FrameDev * frames, ViewState * views, const JobState * jobs, int view0, int nViews, int level,
-                        int maxPixels, double minGradient2, int * chunkCounts, int maxChunksPerView, cudaStream_t s);
+                        int maxPixels, double minGradient2, int * chunkCounts, int maxChunksPerView, int wantJstat,
+                        cudaStream_t s);
 int list_chunks_for(int pixels);
 // level_misc.cu
 void launch_level_setup(const FrameDev * frames, JobState * jobs, ViewState * views, int view0, int nViews, int level,

@@ -51,6 +51,7 @@ __global__ void level_setup_kernel(
   V.fx32 = (float)V.fx;
   V.fy32 = (float)V.fy;
   V.nIp = 0;
+  V.listTicket = 0;
   for (int i = 0; i < JSTAT; i++) V.jstat[i] = 0u;
   V.scale = 1.0;
   V.offset = 0.0;

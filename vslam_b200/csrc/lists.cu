@@ -1,7 +1,7 @@
 // Interest-point lists: the compacted, row-major-ordered set of template pixels that take part in the
 // alignment of one (keyframe, level), built once per level like the reference does
 // (SE3Alignment.cpp:83-94 / :123-130 candidate mask; InverseCompositional.cpp:63-93 drops z <= 0).
-// Three passes: per-chunk count, per-view exclusive scan, ordered scatter.
+// One pass per level: count, look-back over the view's earlier chunks, ordered write-out (list_build_kernel).
 #include "common.cuh"
 
 namespace vb
@@ -10,179 +10,198 @@ constexpr int LTHREADS = 256;
 constexpr int LPER = 8;                       // pixels per thread
 constexpr int LCHUNK = LTHREADS * LPER;       // pixels per block
 
-__device__ __forceinline__ bool is_interest(
-  const FrameDev & f, int level, int multi, size_t i, double minGradient2, float & dOut, uint32_t & gOut)
-{
-  const int gx = f.gx[level][i], gy = f.gy[level][i];
-  const float d = multi ? f.Z[level][i] : f.Zsf[level][i];
-  dOut = d;
-  gOut = (uint32_t)(uint16_t)gx | ((uint32_t)(uint16_t)gy << 16);
-  const int g2 = gx * gx + gy * gy;
-  return ((double)g2 >= minGradient2) && (d > 0.f) && isfinite(d);
-}
+constexpr unsigned LREADY = 0x80000000u;
 
-__global__ void __launch_bounds__(LTHREADS) list_count_kernel(
-  const FrameDev * __restrict__ frames, const ViewState * __restrict__ views, const JobState * __restrict__ jobs,
-  int level, double minGradient2, int * __restrict__ chunkCounts, int maxChunks, int view0)
+// Single pass: a block takes the next chunk of ITS view from the view's ticket counter (so every chunk in front of it
+// belongs to a block that is already running: the look-back below cannot wait for a block that was never scheduled),
+// reads its 2048 pixels once with 128-bit loads, publishes its count, sums the counts in front of it, compacts its
+// points into shared memory in pixel order and writes tiles and records with consecutive threads on consecutive
+// entries.  chunkFlags (count | LREADY per view and chunk) starts at zero (launch_build_lists clears it).
+// WANT_JSTAT: also the bounds of the Jacobian components J_i = fxJ dIx P_i + fyJ dIy Q_i over the list (max |dIx P_i|,
+// max |dIy Q_i| in fp32), from which the moments kernel derives its fixed-point scales.
+template <bool WANT_JSTAT>
+__global__ void __launch_bounds__(LTHREADS) list_build_kernel(
+  const FrameDev * __restrict__ frames, ViewState * __restrict__ views, const JobState * __restrict__ jobs, int level,
+  double minGradient2, unsigned * chunkFlags, int maxChunks, int view0)
 {
-  const int vi = view0 + blockIdx.y;
-  const ViewState & V = views[vi];
-  const int npx = V.W * V.H;
-  const int base = blockIdx.x * LCHUNK;
-  if (base >= npx) return;
-  const FrameDev & f = frames[V.fromSlot];
-  const int multi = jobs[V.job].multi;
-  int cnt = 0;
-#pragma unroll
-  for (int k = 0; k < LPER; k++) {
-    const int i = base + k * LTHREADS + threadIdx.x;
-    float d;
-    uint32_t g;
-    if (i < npx && is_interest(f, level, multi, i, minGradient2, d, g)) cnt++;
-  }
-  cnt = __reduce_add_sync(0xffffffffu, cnt);
-  __shared__ int wsum[LTHREADS / 32];
-  if ((threadIdx.x & 31) == 0) wsum[threadIdx.x >> 5] = cnt;
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    int s = 0;
-    for (int w = 0; w < LTHREADS / 32; w++) s += wsum[w];
-    chunkCounts[vi * maxChunks + blockIdx.x] = s;
-  }
-}
-
-// one block per view: exclusive scan of the chunk counts (in place), nIp and nChunks of the view
-__global__ void __launch_bounds__(256) list_scan_kernel(
-  ViewState * __restrict__ views, int * __restrict__ chunkCounts, int maxChunks, int view0)
-{
-  const int vi = view0 + blockIdx.x;
-  ViewState & V = views[vi];
-  const int npx = V.W * V.H;
-  const int n = (npx + LCHUNK - 1) / LCHUNK;
-  int * c = chunkCounts + vi * maxChunks;
-  __shared__ int carry;
-  __shared__ int wsum[8];
-  if (threadIdx.x == 0) carry = 0;
-  __syncthreads();
-  for (int b = 0; b < n; b += 256) {
-    const int i = b + threadIdx.x;
-    const int v = i < n ? c[i] : 0;
-    int incl = v;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const int t = __shfl_up_sync(0xffffffffu, incl, o);
-      if ((threadIdx.x & 31) >= o) incl += t;
-    }
-    if ((threadIdx.x & 31) == 31) wsum[threadIdx.x >> 5] = incl;
-    __syncthreads();
-    int woff = 0;
-    for (int w = 0; w < (int)(threadIdx.x >> 5); w++) woff += wsum[w];
-    const int excl = carry + woff + incl - v;
-    if (i < n) c[i] = excl;
-    __syncthreads();
-    if (threadIdx.x == 255) carry = excl + v;
-    __syncthreads();
-  }
-  if (threadIdx.x == 0) V.nIp = carry;
-  // Padding of the last tile: zero gradient (hence a zero Jacobian row, which adds exact zeros whatever the weight),
-  // finite 1/depth, depth 1.  The Jacobian phase of the level kernel then needs no "is this entry real" test.
-  const int nIp = carry, padEnd = (nIp + LIST_TILE - 1) / LIST_TILE * LIST_TILE;
-  for (int o = nIp + (int)threadIdx.x; o < padEnd; o += 256) {
-    unsigned char * tile = V.tiles + (size_t)(o / LIST_TILE) * LIST_TILE_BYTES;
-    const int j = o % LIST_TILE;
-    reinterpret_cast<float *>(tile + TILE_OFF_D)[j] = 1.f;
-    reinterpret_cast<uint32_t *>(tile + TILE_OFF_UVT)[j] = 0u;
-    ListRec z;
-    z.uvt = 0u;
-    z.g = 0u;
-    z.zi = 0.0;
-    V.rec[o] = z;
-  }
-}
-
-__global__ void __launch_bounds__(LTHREADS) list_write_kernel(
-  const FrameDev * __restrict__ frames, ViewState * __restrict__ views, const JobState * __restrict__ jobs,
-  int level, double minGradient2, const int * __restrict__ chunkOffsets, int maxChunks, int view0)
-{
-  const int vi = view0 + blockIdx.y;
-  ViewState & V = views[vi];
-  const int npx = V.W * V.H;
-  const int base = blockIdx.x * LCHUNK;
-  if (base >= npx) return;
-  const FrameDev & f = frames[V.fromSlot];
-  const int multi = jobs[V.job].multi;
-  const int W = V.W;
+  __shared__ float sD[LCHUNK];
+  __shared__ uint32_t sUvt[LCHUNK];
+  __shared__ uint32_t sG[LCHUNK];
   __shared__ int wsum[LTHREADS / 32];
   __shared__ unsigned jmax[JSTAT];
-  if (threadIdx.x < JSTAT) jmax[threadIdx.x] = 0u;
-  int running = chunkOffsets[vi * maxChunks + blockIdx.x];
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  // bounds of the Jacobian components J_i = fxJ dIx P_i + fyJ dIy Q_i over the list (the moments kernel derives its
-  // fixed-point scales from them): max |dIx P_i|, max |dIy Q_i| in fp32
-  const float ifx = (float)V.ifx, ify = (float)V.ify, kx = (float)V.kx, ky = (float)V.ky;
-  float jm[JSTAT];
+  __shared__ int sChunk, sBase;
+  const int vi = view0 + blockIdx.y;
+  ViewState & V = views[vi];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int npx = V.W * V.H, nChunks = (npx + LCHUNK - 1) / LCHUNK;
+  if (tid == 0) sChunk = atomicAdd(&V.listTicket, 1);
+  if (WANT_JSTAT && tid < JSTAT) jmax[tid] = 0u;
+  __syncthreads();
+  const int chunk = sChunk;
+  if (chunk >= nChunks) return;
+  const FrameDev & f = frames[V.fromSlot];
+  const int16_t * __restrict__ gxp = f.gx[level];
+  const int16_t * __restrict__ gyp = f.gy[level];
+  const float * __restrict__ dp = jobs[V.job].multi ? f.Z[level] : f.Zsf[level];
+  const uint8_t * __restrict__ ip = f.I[level];
+  const int first = chunk * LCHUNK + tid * LPER;
+  alignas(16) int16_t gx[LPER], gy[LPER];
+  alignas(16) float d[LPER];
+  alignas(8) uint8_t t[LPER];
+  const bool vec = (npx % LPER) == 0 &&
+                   (((uintptr_t)gxp | (uintptr_t)gyp | (uintptr_t)dp | (uintptr_t)ip) & 15) == 0;
+  if (vec) {
+    if (first < npx) {
+      *reinterpret_cast<uint4 *>(gx) = __ldg(reinterpret_cast<const uint4 *>(gxp + first));
+      *reinterpret_cast<uint4 *>(gy) = __ldg(reinterpret_cast<const uint4 *>(gyp + first));
+      *reinterpret_cast<float4 *>(d) = __ldg(reinterpret_cast<const float4 *>(dp + first));
+      *reinterpret_cast<float4 *>(d + 4) = __ldg(reinterpret_cast<const float4 *>(dp + first + 4));
+      *reinterpret_cast<uint2 *>(t) = __ldg(reinterpret_cast<const uint2 *>(ip + first));
+    } else {
 #pragma unroll
-  for (int i = 0; i < JSTAT; i++) jm[i] = 0.f;
-  for (int k = 0; k < LPER; k++) {
-    const int i = base + k * LTHREADS + threadIdx.x;
-    float d = 0.f;
-    uint32_t g = 0;
-    const bool keep = i < npx && is_interest(f, level, multi, i, minGradient2, d, g);
-    const unsigned m = __ballot_sync(0xffffffffu, keep);
-    if (lane == 0) wsum[warp] = __popc(m);
-    __syncthreads();
-    int woff = 0, tot = 0;
+      for (int k = 0; k < LPER; k++) d[k] = 0.f, gx[k] = gy[k] = 0, t[k] = 0;
+    }
+  } else {
 #pragma unroll
-    for (int w = 0; w < LTHREADS / 32; w++) {
-      const int s = wsum[w];
-      if (w < warp) woff += s;
-      tot += s;
+    for (int k = 0; k < LPER; k++) {
+      const int i = first + k;
+      const bool in = i < npx;
+      gx[k] = in ? gxp[i] : (int16_t)0;
+      gy[k] = in ? gyp[i] : (int16_t)0;
+      d[k] = in ? dp[i] : 0.f;
+      t[k] = in ? ip[i] : (uint8_t)0;
     }
-    if (keep) {
-      const int o = running + woff + __popc(m & ((1u << lane) - 1u));
-      const int v = i / W, u = i - v * W;
-      unsigned char * tile = V.tiles + (size_t)(o / LIST_TILE) * LIST_TILE_BYTES;
-      const int j = o % LIST_TILE;
-      const uint32_t uvt = (uint32_t)u | ((uint32_t)v << 12) | ((uint32_t)f.I[level][i] << 24);
-      reinterpret_cast<float *>(tile + TILE_OFF_D)[j] = d;
-      reinterpret_cast<uint32_t *>(tile + TILE_OFF_UVT)[j] = uvt;
-      ListRec rc;
-      rc.uvt = uvt;
-      rc.g = g;
-      rc.zi = 1.0 / (double)d;  // Warp.cpp:170
-      V.rec[o] = rc;
-      const float ax = fabsf((float)(int16_t)(g & 0xffff)), ay = fabsf((float)(int16_t)(g >> 16));
-      const float xn = fabsf(fmaf(ifx, (float)u, kx)), yn = fabsf(fmaf(ify, (float)v, ky)), zi = 1.f / d;
-      jm[0] = fmaxf(jm[0], ax * zi);
-      jm[2] = fmaxf(jm[2], ax * xn * zi);
-      jm[3] = fmaxf(jm[3], ax * xn * yn);
-      jm[4] = fmaxf(jm[4], ax * fmaf(xn, xn, 1.f));
-      jm[5] = fmaxf(jm[5], ax * yn);
-      jm[7] = fmaxf(jm[7], ay * zi);
-      jm[8] = fmaxf(jm[8], ay * yn * zi);
-      jm[9] = fmaxf(jm[9], ay * fmaf(yn, yn, 1.f));
-      jm[10] = fmaxf(jm[10], ay * xn * yn);
-      jm[11] = fmaxf(jm[11], ay * xn);
-    }
-    running += tot;
-    __syncthreads();
   }
+  unsigned keep = 0;
 #pragma unroll
-  for (int i = 0; i < JSTAT; i++) {
-    const unsigned m = __reduce_max_sync(0xffffffffu, __float_as_uint(jm[i]));  // non-negative floats order like their bits
-    if (lane == 0 && m) atomicMax(&jmax[i], m);
+  for (int k = 0; k < LPER; k++) {
+    const int g2 = (int)gx[k] * gx[k] + (int)gy[k] * gy[k];
+    if ((double)g2 >= minGradient2 && d[k] > 0.f && isfinite(d[k]) && first + k < npx) keep |= 1u << k;
+  }
+  const int cnt = __popc(keep);
+  int incl = cnt;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int x = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += x;
+  }
+  if (lane == 31) wsum[warp] = incl;
+  __syncthreads();
+  int woff = 0, total = 0;
+#pragma unroll
+  for (int w = 0; w < LTHREADS / 32; w++) {
+    if (w < warp) woff += wsum[w];
+    total += wsum[w];
+  }
+  unsigned * flags = chunkFlags + (size_t)vi * maxChunks;
+  if (tid == 0) {
+    __threadfence();
+    atomicExch(&flags[chunk], (unsigned)total | LREADY);
+  }
+  if (warp == 0) {  // look-back over the view's chunks in front of this one
+    unsigned sum = 0;
+    for (int j = lane; j < chunk; j += 32) {
+      unsigned x;
+      do {
+        x = *reinterpret_cast<volatile unsigned *>(&flags[j]);
+      } while (!(x & LREADY));
+      sum += x & ~LREADY;
+    }
+    sum = __reduce_add_sync(0xffffffffu, sum);
+    if (lane == 0) sBase = (int)sum;
+  }
+  // compaction into shared memory, pixel order
+  float jm[JSTAT];
+  if (WANT_JSTAT) {
+#pragma unroll
+    for (int i = 0; i < JSTAT; i++) jm[i] = 0.f;
+  }
+  const int W = V.W;
+  int loc = woff + incl - cnt;
+  int v = first / W, u = first - v * W;
+  const float ifx = (float)V.ifx, ify = (float)V.ify, kx = (float)V.kx, ky = (float)V.ky;
+#pragma unroll
+  for (int k = 0; k < LPER; k++) {
+    if (keep & (1u << k)) {
+      sD[loc] = d[k];
+      sUvt[loc] = (uint32_t)u | ((uint32_t)v << 12) | ((uint32_t)t[k] << 24);
+      sG[loc] = (uint32_t)(uint16_t)gx[k] | ((uint32_t)(uint16_t)gy[k] << 16);
+      loc++;
+      if (WANT_JSTAT) {
+        const float ax = fabsf((float)gx[k]), ay = fabsf((float)gy[k]);
+        const float xn = fabsf(fmaf(ifx, (float)u, kx)), yn = fabsf(fmaf(ify, (float)v, ky)), zi = 1.f / d[k];
+        jm[0] = fmaxf(jm[0], ax * zi);
+        jm[2] = fmaxf(jm[2], ax * xn * zi);
+        jm[3] = fmaxf(jm[3], ax * xn * yn);
+        jm[4] = fmaxf(jm[4], ax * fmaf(xn, xn, 1.f));
+        jm[5] = fmaxf(jm[5], ax * yn);
+        jm[7] = fmaxf(jm[7], ay * zi);
+        jm[8] = fmaxf(jm[8], ay * yn * zi);
+        jm[9] = fmaxf(jm[9], ay * fmaf(yn, yn, 1.f));
+        jm[10] = fmaxf(jm[10], ay * xn * yn);
+        jm[11] = fmaxf(jm[11], ay * xn);
+      }
+    }
+    if (++u == W) u = 0, v++;
+  }
+  if (WANT_JSTAT) {
+#pragma unroll
+    for (int i = 0; i < JSTAT; i++) {
+      const unsigned m = __reduce_max_sync(0xffffffffu, __float_as_uint(jm[i]));  // non-negative floats order like their bits
+      if (lane == 0 && m) atomicMax(&jmax[i], m);
+    }
   }
   __syncthreads();
-  if (threadIdx.x < JSTAT && jmax[threadIdx.x]) atomicMax(&V.jstat[threadIdx.x], jmax[threadIdx.x]);
+  if (WANT_JSTAT && tid < JSTAT && jmax[tid]) atomicMax(&V.jstat[tid], jmax[tid]);
+  // write-out: consecutive threads, consecutive list entries
+  const int base = sBase;
+  unsigned char * tiles = V.tiles;
+  ListRec * rec = V.rec;
+  for (int j = tid; j < total; j += LTHREADS) {
+    const int o = base + j;
+    unsigned char * tile = tiles + (size_t)(o / LIST_TILE) * LIST_TILE_BYTES;
+    const int q = o % LIST_TILE;
+    const float dj = sD[j];
+    const uint32_t uvt = sUvt[j];
+    reinterpret_cast<float *>(tile + TILE_OFF_D)[q] = dj;
+    reinterpret_cast<uint32_t *>(tile + TILE_OFF_UVT)[q] = uvt;
+    ListRec rc;
+    rc.uvt = uvt;
+    rc.g = sG[j];
+    rc.zi = 1.0 / (double)dj;  // Warp.cpp:170
+    rec[o] = rc;
+  }
+  if (chunk == nChunks - 1) {
+    // the view's last chunk: nIp, and the padding of the last tile - zero gradient (hence a zero Jacobian row, which adds
+    // exact zeros whatever the weight), finite 1/depth, depth 1.  The Jacobian phase of the level kernel then needs no
+    // "is this entry real" test.
+    const int nIp = base + total, padEnd = (nIp + LIST_TILE - 1) / LIST_TILE * LIST_TILE;
+    if (tid == 0) V.nIp = nIp;
+    for (int o = nIp + tid; o < padEnd; o += LTHREADS) {
+      unsigned char * tile = tiles + (size_t)(o / LIST_TILE) * LIST_TILE_BYTES;
+      const int q = o % LIST_TILE;
+      reinterpret_cast<float *>(tile + TILE_OFF_D)[q] = 1.f;
+      reinterpret_cast<uint32_t *>(tile + TILE_OFF_UVT)[q] = 0u;
+      ListRec z;
+      z.uvt = 0u;
+      z.g = 0u;
+      z.zi = 0.0;
+      rec[o] = z;
+    }
+  }
 }
 
 void launch_build_lists(const FrameDev * frames, ViewState * views, const JobState * jobs, int view0, int nViews, int level,
-                        int maxPixels, double minGradient2, int * chunkCounts, int maxChunksPerView, cudaStream_t s)
+                        int maxPixels, double minGradient2, int * chunkCounts, int maxChunksPerView, int wantJstat,
+                        cudaStream_t s)
 {
   dim3 grid((maxPixels + LCHUNK - 1) / LCHUNK, nViews);
-  list_count_kernel<<<grid, LTHREADS, 0, s>>>(frames, views, jobs, level, minGradient2, chunkCounts, maxChunksPerView, view0);
-  list_scan_kernel<<<nViews, 256, 0, s>>>(views, chunkCounts, maxChunksPerView, view0);
-  list_write_kernel<<<grid, LTHREADS, 0, s>>>(frames, views, jobs, level, minGradient2, chunkCounts, maxChunksPerView, view0);
+  unsigned * flags = reinterpret_cast<unsigned *>(chunkCounts);
+  cudaMemsetAsync(flags + (size_t)view0 * maxChunksPerView, 0, (size_t)nViews * maxChunksPerView * sizeof(unsigned), s);
+  if (wantJstat)
+    list_build_kernel<true><<<grid, LTHREADS, 0, s>>>(frames, views, jobs, level, minGradient2, flags, maxChunksPerView, view0);
+  else
+    list_build_kernel<false><<<grid, LTHREADS, 0, s>>>(frames, views, jobs, level, minGradient2, flags, maxChunksPerView, view0);
 }
 
 int list_chunks_for(int pixels) { return (pixels + LCHUNK - 1) / LCHUNK; }
