@@ -550,6 +550,37 @@ def test_async_upload_pipeline_is_identical_to_the_synchronous_path(capi, oracle
 
 
 @pytest.mark.gpu
+def test_reupload_of_an_id_whose_asynchronous_upload_is_still_running(capi, oracle, synth):
+    """A frame id that is uploaded asynchronously and then, at once, synchronously with other content ends up holding the
+    second content (make_frames orders the frame-table update behind the pending upload); the same id twice in one call
+    is refused."""
+    import torch
+    F, W, H, L = 24, 640, 480, 4
+    cam = synth.cam_for(W, H)
+    gray, depth, _ = synth.make_sequence(2, W, H, seed=5, cam=cam)
+    first_g = torch.from_numpy(np.repeat(gray[:1], F, 0)).pin_memory()
+    first_d = torch.from_numpy(np.repeat(depth[:1], F, 0)).pin_memory()
+    ids = np.arange(F, dtype=np.uint64)
+    cams = np.tile(np.array(cam, np.float64), (F, 1))
+    want = oracle.Frame(gray[1], depth[1].astype(np.float64), *cam, L)
+    ctx = capi.Context(capi.make_config())
+    try:
+        for rep in range(3):
+            ctx.upload_async(ids, first_g.data_ptr(), first_d.data_ptr(), F, W, H, cams, L)
+            ctx.upload(ids[5:7], np.repeat(gray[1:], 2, 0), np.repeat(depth[1:], 2, 0), cam, L)   # other arena, same ids
+            for fid in (5, 6):
+                for lvl in (0, L - 1):
+                    got, ref = ctx.download(fid, lvl), want.level(lvl)
+                    assert np.array_equal(got["I"], ref["I"]) and np.array_equal(got["dIx"], ref["dIx"])
+                    assert np.array_equal(got["Z"], ref["Z"].astype(np.float32))
+            ctx.synchronize()
+        with pytest.raises(capi.VslamB200Error, match="twice"):
+            ctx.upload(np.array([3, 4, 3]), np.repeat(gray[:1], 3, 0), np.repeat(depth[:1], 3, 0), cam, L)
+    finally:
+        ctx.close()
+
+
+@pytest.mark.gpu
 def test_u16_depth_async_upload_matches_the_reference_ingestion(capi, oracle, synth):
     """vslamb200_frames_upload_u16_async: 16-bit sensor depth / 5000 (test_alignment_se3.cpp:99) converted on the device;
     every pyramid level equals the oracle's frame built from oracle.depth_ingest of the same values, the alignment is

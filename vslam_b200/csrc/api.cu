@@ -228,10 +228,23 @@ int make_frames(vslamb200_ctx * c, int n, const uint64_t * ids, int W, int H, co
   std::memset(&proto, 0, sizeof(proto));
   level_dims(W, H, nLevels, proto);
   const size_t frameBytes = layout_frame(proto, nullptr);
-  // frames re-uploaded under the same id are replaced (work in flight is ordered before the new upload on the stream)
+  {
+    std::vector<uint64_t> sorted(ids, ids + n);
+    std::sort(sorted.begin(), sorted.end());
+    if (std::adjacent_find(sorted.begin(), sorted.end()) != sorted.end())
+      return fail(VSLAMB200_EINVAL, "frames_upload: the same frame id appears twice in one call");
+  }
+  // Frames re-uploaded under the same id are replaced.  Work of the compute stream that still uses the old frame is
+  // ordered before the new upload on that stream; an asynchronous upload of the old frame that still runs on the copy
+  // stream (its preprocessing reads the frame table entry this call is about to overwrite) is waited for first.
   for (int i = 0; i < n; i++) {
     auto it = c->idToSlot.find(ids[i]);
-    if (it != c->idToSlot.end()) release_slot(c, it->second);
+    if (it == c->idToSlot.end()) continue;
+    Arena & old = c->arenas[c->frames[it->second].arena];
+    if (old.pending) {
+      CK(cudaStreamWaitEvent(c->stream, old.ready, 0));  // later copy-stream work is behind it by stream order
+    }
+    release_slot(c, it->second);
   }
   const size_t need = frameBytes * n;
   int arenaIdx = -1;
