@@ -105,7 +105,7 @@ def lib():
         L.vo_baseline_batch.restype = C.c_long
         L.vo_baseline_batch.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
                                         C.c_double, C.c_double, C.c_double, C.c_double, C.c_int, C.c_int,
-                                        C.c_void_p, C.c_void_p]
+                                        C.c_void_p, C.c_void_p, C.c_void_p]
         for n in ("vo_pyr_down_u8", "vo_blur3_u8"):
             getattr(L, n).argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
         L.vo_rgb_to_gray_u8.argtypes = [C.c_void_p, C.c_long, C.c_int, C.c_void_p]
@@ -307,9 +307,10 @@ def baseline_sequence(cfg, gray, depth, fx, fy, cx, cy, n_levels, n_threads=1):
     return poses, it
 
 
-def baseline_batch(cfg, gray, depth, fx, fy, cx, cy, n_levels, n_threads=1, stride=2, n_pairs=None):
+def baseline_batch(cfg, gray, depth, fx, fy, cx, cy, n_levels, n_threads=1, stride=2, n_pairs=None, start=None):
     """Independent pairs out of one frame array: pair i aligns frame i * stride + 1 against frame i * stride (stride 2:
     frames stored ref0, cur0, ref1, cur1, ...; stride 1: the consecutive pairs of a sequence).
+    start: the initial guess (pose7) of every pair's second frame, identity when None.
     -> (n_pairs, 7) poses, (n_pairs, n_levels) completed Gauss-Newton steps per level."""
     gray = np.ascontiguousarray(gray, np.uint8)
     depth = np.ascontiguousarray(depth, np.float32)
@@ -319,6 +320,7 @@ def baseline_batch(cfg, gray, depth, fx, fy, cx, cy, n_levels, n_threads=1, stri
     assert (n_pairs - 1) * stride + 1 < F
     poses = np.zeros((n_pairs, 7))
     iters = np.zeros((n_pairs, n_levels), np.int32)
+    start = None if start is None else np.ascontiguousarray(start, np.float64)
     lib().vo_baseline_batch(C.byref(cfg), n_pairs, stride, W, H, _p(gray), _p(depth), fx, fy, cx, cy, n_levels, n_threads,
-                            _p(poses), _p(iters))
+                            _p(poses), _p(iters), _p(start))
     return poses, iters

@@ -1448,11 +1448,13 @@ long vo_baseline_sequence(
 
 // Independent pairs out of one frame array: pair i aligns frame i * stride + 1 against frame i * stride (stride 1: the
 // consecutive pairs of a sequence, as vo_baseline_sequence; stride 2: BASELINE configs[2], frames stored ref0, cur0,
-// ref1, cur1, ...).  iters_out (may be null): nPairs x nLevels completed Gauss-Newton steps.
+// ref1, cur1, ...).  iters_out (may be null): nPairs x nLevels completed Gauss-Newton steps.  start_pose7 (may be null:
+// identity): the initial guess of every pair's second frame.
 long vo_baseline_batch(
   const vo_config * c, int nPairs, int stride, int W, int H, const uint8_t * gray, const float * depth, double fx,
-  double fy, double cx, double cy, int nLevels, int nThreads, double * poses_out, int * iters_out)
+  double fy, double cx, double cy, int nLevels, int nThreads, double * poses_out, int * iters_out, const double * start_pose7)
 {
+  const vo::SE3 start = start_pose7 ? to_se3(start_pose7) : vo::SE3();
   vo::Config cfg = to_cfg(c);
   long total = 0;
   const size_t npx = (size_t)W * H;
@@ -1467,7 +1469,7 @@ long vo_baseline_batch(
     std::unique_ptr<vo::Frame> f0(vo::frame_create(W, H, gray + a * npx, d0.data(), fx, fy, cx, cy, nLevels, cfg.f32Storage));
     std::unique_ptr<vo::Frame> f1(vo::frame_create(W, H, gray + b * npx, d1.data(), fx, fy, cx, cy, nLevels, cfg.f32Storage));
     vo::SE3 I;
-    vo::AlignOut o = vo::align(cfg, {f0.get()}, {I}, f1.get(), I, false, nullptr);
+    vo::AlignOut o = vo::align(cfg, {f0.get()}, {I}, f1.get(), start, false, nullptr);
     for (int k = 0; k < 4; k++) poses_out[7 * i + k] = o.pose.q[k];
     for (int k = 0; k < 3; k++) poses_out[7 * i + 4 + k] = o.pose.t[k];
     for (int l = 0; l < nLevels; l++) {
