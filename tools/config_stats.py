@@ -38,7 +38,7 @@ def pairs_case(name, W, H, L, n_frames, cfg):
     ctx.close()
 
 
-def keyframes_case(W=1280, H=720, L=4, K=8, n_targets=16):
+def keyframes_case(W=1280, H=720, L=4, K=8, n_targets=16, tag="", **cfg_kw):
     cam = synth.cam_for(W, H)
     xis = []
     for k in range(K):
@@ -52,23 +52,29 @@ def keyframes_case(W=1280, H=720, L=4, K=8, n_targets=16):
         R, t = synth.se3_exp(xi)
         g, d = synth.render(W, H, cam, R, t, scene_seed=505)
         gray.append(g); depth.append(d); poses.append(synth.pose7(R, t))
-    ctx = A.Context(A.make_config(max_iterations=60))
+    ctx = A.Context(A.make_config(max_iterations=60, **cfg_kw))
     ctx.upload(np.arange(len(xis)), np.stack(gray), np.stack(depth), cam, L)
     jobs = [dict(to=K + j, to_pose=poses[0], frm=list(range(K)), from_poses=np.stack(poses[:K]), multi=True)
             for j in range(n_targets)]
     t, res = timed(ctx, jobs)
     t1, _ = timed(ctx, jobs[:1], reps=10)
     it = np.mean([sum(r["iters"][:L]) for r in res])
-    print(f"config 5 (1 frame vs {K} keyframes, {W}x{H}, {L} levels): {n_targets} alignments in {t * 1e3:.2f} ms = "
+    print(f"config 5 (1 frame vs {K} keyframes, {W}x{H}, {L} levels{tag}): {n_targets} alignments in {t * 1e3:.2f} ms = "
           f"{n_targets / t:.0f} alignments/s, one alignment {t1 * 1e3:.2f} ms, mean iterations {it:.1f}")
     ctx.close()
 
 
 if __name__ == "__main__":
+    # chi2 as the reference's Release build evaluates it (the default) and the weighted sum (vslam_b200.h)
     pairs_case("config 4 (KITTI-shape 1232x368, 5 levels, GN)", 1232, 368, 5, 129, A.make_config(max_iterations=60))
-    pairs_case("config 4 (KITTI-shape 1232x368, 5 levels, LM extension)", 1232, 368, 5, 129,
-               A.make_config(max_iterations=60, solver=A.SOLVER_LM, lm_lambda0=1e-2, lm_up=8.0, lm_down=0.25))
+    pairs_case("config 4 (KITTI-shape 1232x368, 5 levels, GN, weighted chi2)", 1232, 368, 5, 129,
+               A.make_config(max_iterations=60, chi2_mode=A.CHI2_WEIGHTED))
+    pairs_case("config 4 (KITTI-shape 1232x368, 5 levels, LM extension, weighted chi2)", 1232, 368, 5, 129,
+               A.make_config(max_iterations=60, solver=A.SOLVER_LM, lm_lambda0=1e-2, lm_up=8.0, lm_down=0.25,
+                             chi2_mode=A.CHI2_WEIGHTED))
     keyframes_case()
+    keyframes_case(tag=", weighted chi2", chi2_mode=A.CHI2_WEIGHTED)
+    keyframes_case(tag=", weighted chi2, dense kernel", chi2_mode=A.CHI2_WEIGHTED, level_kernel=A.KERNEL_DENSE)
     pairs_case("extension (bilinear sampling, 640x480, 4 levels, GN)", 640, 480, 4, 65,
                A.make_config(max_iterations=30, sampling=A.SAMPLING_BILINEAR))
     pairs_case("extension (bilinear + depth residual, 640x480, 4 levels, GN)", 640, 480, 4, 65,
