@@ -65,6 +65,13 @@ def keyframes_case(W=1280, H=720, L=4, K=8, n_targets=16, tag="", **cfg_kw):
 
 
 if __name__ == "__main__":
+    only = sys.argv[1] if len(sys.argv) > 1 else ""
+    if only == "keyframes":
+        keyframes_case()
+        keyframes_case(tag=", dense kernel", level_kernel=A.KERNEL_DENSE)
+        keyframes_case(tag=", 64 targets", n_targets=64)
+        keyframes_case(tag=", 64 targets, dense kernel", n_targets=64, level_kernel=A.KERNEL_DENSE)
+        sys.exit(0)
     # chi2 as the reference's Release build evaluates it (the default) and the weighted sum (vslam_b200.h)
     pairs_case("config 4 (KITTI-shape 1232x368, 5 levels, GN)", 1232, 368, 5, 129, A.make_config(max_iterations=60))
     pairs_case("config 4 (KITTI-shape 1232x368, 5 levels, GN, weighted chi2)", 1232, 368, 5, 129,
@@ -73,6 +80,7 @@ if __name__ == "__main__":
                A.make_config(max_iterations=60, solver=A.SOLVER_LM, lm_lambda0=1e-2, lm_up=8.0, lm_down=0.25,
                              chi2_mode=A.CHI2_WEIGHTED))
     keyframes_case()
+    keyframes_case(tag=", dense kernel", level_kernel=A.KERNEL_DENSE)
     keyframes_case(tag=", weighted chi2", chi2_mode=A.CHI2_WEIGHTED)
     keyframes_case(tag=", weighted chi2, dense kernel", chi2_mode=A.CHI2_WEIGHTED, level_kernel=A.KERNEL_DENSE)
     pairs_case("extension (bilinear sampling, 640x480, 4 levels, GN)", 640, 480, 4, 65,
