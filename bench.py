@@ -331,7 +331,8 @@ def main():
             dist.all_gather_into_tensor(d_all, d_mine)
 
     def step_resident():
-        ctx.upload_device(ids, d_gray.data_ptr(), d_depth.data_ptr(), n_frames, W, H, cams, LEVELS)
+        # the resident frames are used in place (vslamb200_frames_attach_device): no device-to-device copy of the inputs
+        ctx.attach_device(ids, d_gray.data_ptr(), d_depth.data_ptr(), n_frames, W, H, cams, LEVELS)
         ctx.align_raw(jobs, n_jobs, results)
         gather()
 
@@ -390,6 +391,8 @@ def main():
     all_poses = d_all.cpu().numpy() if use_dist else None
 
     # end to end through the C ABI with host buffers (the raw device copies of the resident leg are no longer needed)
+    ctx.synchronize()
+    ctx.release_all()  # the attached frames point into these buffers
     del d_gray, d_depth
     torch.cuda.empty_cache()
     with torch.cuda.stream(stream):

@@ -173,6 +173,15 @@ int vslamb200_frames_upload_u16_async(
 int vslamb200_frames_upload_device(
   vslamb200_ctx * ctx, int n, const uint64_t * ids, int W, int H, const uint8_t * d_gray, const float * d_depth,
   const double * cams, int n_levels);
+/* Zero-copy variant of vslamb200_frames_upload_device: the level-0 planes of the n frames ARE the caller's device buffers
+ * (tightly packed, 16-byte aligned: frame i at d_gray + i*W*H and d_depth + i*W*H), read in place by the pyramid, gradient,
+ * list and level kernels; coarser levels and gradients live in the library's arena.  The buffers must stay valid and
+ * unchanged until the frames are released or replaced.  No counterpart in the reference, whose Frame copies its inputs
+ * (core/src/Frame.cpp:131-142); it saves the device-to-device copy of 5 bytes per pixel when a producer (decoder,
+ * simulator, another kernel) already left the images in HBM. */
+int vslamb200_frames_attach_device(
+  vslamb200_ctx * ctx, int n, const uint64_t * ids, int W, int H, const uint8_t * d_gray, const float * d_depth,
+  const double * cams, int n_levels);
 /* Frame ingestion as the node does it, fused into the upload (src/ros/nodes/NodeRgbdAlignment.cpp:177-199, replaces
  * cv::cvtColor(RGB2GRAY) :182, the NaN -> 0 select :190 and, for 16-bit sensor depth, loadDepth(...) / 5000.0 of
  * odometry/test/test_alignment_se3.cpp:99), followed by what vslamb200_frames_upload does.  rgb: n row-major H x W x 3

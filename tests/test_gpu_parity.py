@@ -550,6 +550,37 @@ def test_async_upload_pipeline_is_identical_to_the_synchronous_path(capi, oracle
 
 
 @pytest.mark.gpu
+def test_attached_device_frames_are_identical_to_copied_ones(capi, oracle, synth):
+    """vslamb200_frames_attach_device (level-0 planes used in place in the caller's device memory) gives the same
+    pyramids, gradients and poses as vslamb200_frames_upload_device, which copies them; a misaligned buffer is refused."""
+    import torch
+    F, W, H, L = 6, 320, 240, 3
+    cam = synth.cam_for(W, H)
+    gray, depth, _ = synth.make_sequence(F, W, H, seed=321, cam=cam)
+    d_gray, d_depth = torch.from_numpy(gray).cuda(), torch.from_numpy(depth).cuda()
+    ident = oracle.IDENTITY
+    jobs = [dict(to=i + 1, to_pose=ident, frm=[i], from_poses=ident, multi=False) for i in range(F - 1)]
+    jobs.append(dict(to=F - 1, to_pose=ident, frm=[0, 2], from_poses=np.stack([ident, ident]), multi=True))
+    out = {}
+    for how in ("copy", "attach"):
+        ctx = capi.Context(capi.make_config(max_iterations=30))
+        try:
+            up = ctx.upload_device if how == "copy" else ctx.attach_device
+            up(np.arange(F), d_gray.data_ptr(), d_depth.data_ptr(), F, W, H, cam, L)
+            out[how] = (ctx.align(jobs), [ctx.download(2, l) for l in range(L)])
+            if how == "attach":
+                with pytest.raises(capi.VslamB200Error, match="aligned"):
+                    ctx.attach_device(np.arange(F - 1) + 100, d_gray.data_ptr() + 1, d_depth.data_ptr(), F - 1, W, H, cam, L)
+        finally:
+            ctx.close()
+    for a, b in zip(out["copy"][0], out["attach"][0]):
+        assert np.array_equal(a["pose"], b["pose"]) and list(a["iters"]) == list(b["iters"])
+    for a, b in zip(out["copy"][1], out["attach"][1]):
+        for k in a:
+            assert np.array_equal(a[k], b[k]), k
+
+
+@pytest.mark.gpu
 def test_reupload_of_an_id_whose_asynchronous_upload_is_still_running(capi, oracle, synth):
     """A frame id that is uploaded asynchronously and then, at once, synchronously with other content ends up holding the
     second content (make_frames orders the frame-table update behind the pending upload); the same id twice in one call

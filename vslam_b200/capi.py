@@ -57,7 +57,8 @@ class Stats(C.Structure):
 
 EXPORTS = [
     "vslamb200_last_error", "vslamb200_version", "vslamb200_create", "vslamb200_destroy", "vslamb200_set_config",
-    "vslamb200_set_stream", "vslamb200_frames_upload", "vslamb200_frames_upload_device", "vslamb200_frames_ingest_rgbd",
+    "vslamb200_set_stream", "vslamb200_frames_upload", "vslamb200_frames_upload_device", "vslamb200_frames_attach_device",
+    "vslamb200_frames_ingest_rgbd",
     "vslamb200_frame_release",
     "vslamb200_frame_release_all", "vslamb200_frame_dims", "vslamb200_frame_download", "vslamb200_align",
     "vslamb200_set_trace", "vslamb200_get_trace", "vslamb200_evaluate", "vslamb200_get_stats",
@@ -93,6 +94,7 @@ def lib():
         L.vslamb200_frames_upload_async.argtypes = [vp, i, vp, i, i, vp, sz, vp, i, sz, i, vp, i]
         L.vslamb200_frames_upload_u16_async.argtypes = [vp, i, vp, i, i, vp, vp, C.c_double, vp, i]
         L.vslamb200_frames_upload_device.argtypes = [vp, i, vp, i, i, vp, vp, vp, i]
+        L.vslamb200_frames_attach_device.argtypes = [vp, i, vp, i, i, vp, vp, vp, i]
         L.vslamb200_frames_ingest_rgbd.argtypes = [vp, i, vp, i, i, vp, i, vp, i, C.c_double, vp, i]
         L.vslamb200_frame_release.argtypes = [vp, u64]
         L.vslamb200_frame_release_all.argtypes = [vp]
@@ -211,6 +213,14 @@ class Context:
         ids = np.ascontiguousarray(np.atleast_1d(ids), np.uint64)
         cams = np.ascontiguousarray(np.broadcast_to(np.asarray(cams, np.float64).reshape(-1, 4), (n, 4)))
         check(lib().vslamb200_frames_upload_device(self.h, n, ptr(ids), W, H, C.c_void_p(d_gray_ptr),
+                                                   C.c_void_p(d_depth_ptr), ptr(cams), n_levels))
+
+    def attach_device(self, ids, d_gray_ptr, d_depth_ptr, n, W, H, cams, n_levels):
+        """Zero-copy: the level-0 planes are the caller's device buffers (tightly packed u8 / f32, 16-byte aligned), which
+        must stay valid and unchanged while the frames are resident."""
+        ids = np.ascontiguousarray(np.atleast_1d(ids), np.uint64)
+        cams = np.ascontiguousarray(np.broadcast_to(np.asarray(cams, np.float64).reshape(-1, 4), (n, 4)))
+        check(lib().vslamb200_frames_attach_device(self.h, n, ptr(ids), W, H, C.c_void_p(d_gray_ptr),
                                                    C.c_void_p(d_depth_ptr), ptr(cams), n_levels))
 
     def release(self, fid):

@@ -215,8 +215,10 @@ int upload_table(vslamb200_ctx * c, const std::vector<int> & slots)
 }
 
 // allocate slots + one arena for n frames of identical geometry
+// borrowGray / borrowDepth (both or neither): the level-0 planes are the caller's tightly packed device buffers, used in
+// place (vslamb200_frames_attach_device)
 int make_frames(vslamb200_ctx * c, int n, const uint64_t * ids, int W, int H, const double * cams, int nLevels,
-                std::vector<int> & slots)
+                std::vector<int> & slots, const uint8_t * borrowGray = nullptr, const float * borrowDepth = nullptr)
 {
   if (n <= 0 || !ids || !cams) return fail(VSLAMB200_EINVAL, "frames_upload: bad arguments");
   if (nLevels < 1 || nLevels > vb::MAX_LEVELS) return fail(VSLAMB200_EINVAL, "frames_upload: n_levels out of range");
@@ -293,6 +295,10 @@ int make_frames(vslamb200_ctx * c, int n, const uint64_t * ids, int W, int H, co
     f.arena = arenaIdx;
     f.dev = proto;
     layout_frame(f.dev, (uint8_t *)a.ptr + frameBytes * i);
+    if (borrowGray) {
+      f.dev.I[0] = const_cast<uint8_t *>(borrowGray) + (size_t)W * H * i;
+      f.dev.Z[0] = f.dev.Zsf[0] = const_cast<float *>(borrowDepth) + (size_t)W * H * i;
+    }
     for (int l = 0; l < nLevels; l++) {
       const double s = std::pow(0.5, l);  // Camera::resize (Camera.cpp:53-57, Frame.cpp:267)
       for (int k = 0; k < 4; k++) f.dev.cam[l][k] = cams[4 * i + k] * s;
@@ -628,6 +634,19 @@ int vslamb200_frames_upload_device(
   const size_t frameStride = n > 1 ? (size_t)((uint8_t *)c->frames[slots[1]].dev.I[0] - (uint8_t *)f0.I[0]) : npx * 4;  // one frame: any pitch >= the widest row copied
   CK(cudaMemcpy2DAsync(f0.I[0], frameStride, dGray, npx, npx, n, cudaMemcpyDeviceToDevice, c->stream));
   CK(cudaMemcpy2DAsync(f0.Z[0], frameStride, dDepth, npx * 4, npx * 4, n, cudaMemcpyDeviceToDevice, c->stream));
+  return preprocess(c, slots, nLevels, true, c->stream);
+}
+
+int vslamb200_frames_attach_device(
+  vslamb200_ctx * c, int n, const uint64_t * ids, int W, int H, const uint8_t * dGray, const float * dDepth,
+  const double * cams, int nLevels)
+{
+  if (!c || !dGray || !dDepth) return fail(VSLAMB200_EINVAL, "frames_attach_device: null argument");
+  if ((((uintptr_t)dGray) | ((uintptr_t)dDepth)) & 15)
+    return fail(VSLAMB200_EINVAL, "frames_attach_device: the device buffers must be 16-byte aligned");
+  CK(cudaSetDevice(c->device));
+  std::vector<int> slots;
+  if (int e = make_frames(c, n, ids, W, H, cams, nLevels, slots, dGray, dDepth)) return e;
   return preprocess(c, slots, nLevels, true, c->stream);
 }
 
