@@ -270,6 +270,7 @@ def main():
     ap.add_argument("--impl", default="ours")
     ap.add_argument("--cpu-pairs", type=int, default=32, help="pairs timed on ONE host core for cpu_baseline")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--e2e-chunks", type=int, default=4, help="sub-batches a step's frames are uploaded in (end-to-end leg)")
     ap.add_argument("--distinct-sequences", action="store_true",
                     help="sequence workload: every rank renders its own sequence (seed 1234 + rank) instead of the same one")
     args = ap.parse_args()
@@ -344,16 +345,32 @@ def main():
     j1, k1 = make_jobs(capi, n_jobs, stride, id0=n_frames)
     jobs2, _keep2 = [jobs, j1], [_keep, k1]
 
-    def upload_set(q):
-        ctx.upload_u16_async(ids2[q], h_gray.data_ptr(), h_k16.data_ptr(), DEPTH_DIVISOR, n_frames, W, H, cams, LEVELS)
+    # A step's frames travel in `chunks` sub-batches (independent pairs only): the alignment of sub-batch c runs under the
+    # transfer of sub-batch c+1, so the first kernels start after 1/chunks of the step's bytes and the last step ends
+    # one sub-batch's compute after its last byte - what vslamb200_frames_upload_u16_async is for (vslam_b200.h).
+    chunks = max(1, min(args.e2e_chunks, n_jobs // 256)) if args.workload == "pairs" else 1
+    cuts = [n_jobs * c_ // chunks for c_ in range(chunks + 1)]
+    job_size, res_size = C.sizeof(capi.Job), C.sizeof(capi.Result)
+
+    def upload_part(q, c_):
+        a, b = stride * cuts[c_], stride * cuts[c_ + 1] + (0 if stride == 2 else 1)
+        ctx.upload_u16_async(ids2[q][a:b], h_gray.data_ptr() + a * W * H, h_k16.data_ptr() + 2 * a * W * H, DEPTH_DIVISOR,
+                             b - a, W, H, cams[a:b], LEVELS)
+
+    def align_part(q, c_):
+        a, b = cuts[c_], cuts[c_ + 1]
+        capi.check(capi.lib().vslamb200_align(ctx.h, C.c_void_p(C.addressof(jobs2[q]) + a * job_size), b - a,
+                                              C.c_void_p(C.addressof(results) + a * res_size)))
 
     def run_e2e(steps):
-        upload_set(0)
-        for st_ in range(steps):
-            if st_ + 1 < steps:
-                upload_set((st_ + 1) & 1)
-            ctx.align_raw(jobs2[st_ & 1], n_jobs, results)
-            gather()
+        work = [(st_, c_) for st_ in range(steps) for c_ in range(chunks)]
+        upload_part(0, 0)
+        for i, (st_, c_) in enumerate(work):
+            if i + 1 < len(work):
+                upload_part(work[i + 1][0] & 1, work[i + 1][1])
+            align_part(st_ & 1, c_)
+            if c_ == chunks - 1:
+                gather()
 
     def timed(fn, steps, loop=True):
         if use_dist:
@@ -526,8 +543,8 @@ def main():
             "e2e": {"value": e2e, "unit": "pairs/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": ms_e2e / args.steps, "max_pose_diff_vs_resident": e2e_diff,
                     "pipeline": "host frames are u8 grey + u16 depth (3 B per pixel, vslamb200_frames_upload_u16_async); "
-                                "the upload of step s+1 (copy stream) overlaps the alignment of step s; all uploads timed; "
-                                "bytes are per GPU"},
+                                f"a step travels in {chunks} sub-batches, the transfer of a sub-batch (copy stream) overlaps the "
+                                "alignment of the one before it; all uploads timed; bytes are per GPU"},
             "gpu_launches": int(st["kernel_launches"]),
             "latency": lat, "clocks": clocks, "ranks": ranks, "roofline": roofline, "cpu_baseline": cpu, "checks": checks,
         }))

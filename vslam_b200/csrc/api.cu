@@ -105,6 +105,11 @@ struct vslamb200_ctx
   // small ring of pinned buffers so that no launch needs a host synchronisation
   cudaStream_t copyStream = nullptr;
   cudaEvent_t copyDone = nullptr, computeMark = nullptr;
+  // asynchronous uploads: copies on copyStream; conversion, pyramids and gradients on prepStream behind copyDone, so the
+  // next transfer does not queue behind them; u16Done: the staged 16-bit depth of the last upload has been consumed
+  cudaStream_t prepStream = nullptr;
+  cudaEvent_t u16Done = nullptr;
+  bool u16Pending = false;
   static constexpr int kSlotRing = 4;
   int * hSlots[kSlotRing] = {nullptr, nullptr, nullptr, nullptr};
   size_t hSlotsCap[kSlotRing] = {0, 0, 0, 0};
@@ -326,7 +331,7 @@ int wait_frame_ready(vslamb200_ctx * c, int slot)
 // pyramid + gradients for uploaded level-0 planes; queued on `stream`, host-synchronised only if asked
 // stagedU16 != nullptr: the level-0 depth planes are first filled from 16-bit sensor depth staged on the device
 int preprocess(vslamb200_ctx * c, const std::vector<int> & slots, int nLevels, bool sync, cudaStream_t stream,
-               const uint16_t * stagedU16 = nullptr, double divisor = 1.0)
+               const uint16_t * stagedU16 = nullptr, double divisor = 1.0, cudaEvent_t afterU16 = nullptr)
 {
   const int n = (int)slots.size();
   const unsigned ring = c->slotsNext++ % vslamb200_ctx::kSlotRing;
@@ -348,6 +353,7 @@ int preprocess(vslamb200_ctx * c, const std::vector<int> & slots, int nLevels, b
   if (stagedU16) {
     vb::launch_depth_u16(stagedU16, divisor, f.W[0], f.H[0], table, dSlots, n, stream);
     c->stats.kernel_launches += 1;
+    if (afterU16) CK(cudaEventRecord(afterU16, stream));  // the staging buffer may be overwritten from here on
   }
   for (int l = 1; l < nLevels; l++) {
     vb::launch_pyramid_level(table, dSlots, n, l, f.W[l], f.H[l], f.Wd[l], f.Hd[l], f.W[l - 1], f.H[l - 1], f.Wd[l - 1],
@@ -438,6 +444,8 @@ int vslamb200_create(const vslamb200_config * cfg, int device, vslamb200_ctx ** 
   bool ok = cudaStreamCreateWithFlags(&c->copyStream, cudaStreamNonBlocking) == cudaSuccess;
   ok = ok && cudaEventCreateWithFlags(&c->copyDone, cudaEventDisableTiming) == cudaSuccess;
   ok = ok && cudaEventCreateWithFlags(&c->computeMark, cudaEventDisableTiming) == cudaSuccess;
+  ok = ok && cudaStreamCreateWithFlags(&c->prepStream, cudaStreamNonBlocking) == cudaSuccess;
+  ok = ok && cudaEventCreateWithFlags(&c->u16Done, cudaEventDisableTiming) == cudaSuccess;
   for (int i = 0; i < vslamb200_ctx::kSlotRing; i++)
     ok = ok && cudaEventCreateWithFlags(&c->slotsEv[i], cudaEventDisableTiming) == cudaSuccess;
   ok = ok && cudaEventCreateWithFlags(&c->forkEv, cudaEventDisableTiming) == cudaSuccess;
@@ -459,6 +467,7 @@ void vslamb200_destroy(vslamb200_ctx * c)
   cudaSetDevice(c->device);
   cudaStreamSynchronize(c->stream);
   if (c->copyStream) cudaStreamSynchronize(c->copyStream);
+  if (c->prepStream) cudaStreamSynchronize(c->prepStream);
   for (auto & a : c->arenas) {
     if (a.ready) cudaEventDestroy(a.ready);
     if (a.ptr) cudaFree(a.ptr);
@@ -470,6 +479,8 @@ void vslamb200_destroy(vslamb200_ctx * c)
     cudaStreamSynchronize(c->copyStream);
     cudaStreamDestroy(c->copyStream);
   }
+  if (c->prepStream) cudaStreamDestroy(c->prepStream);
+  if (c->u16Done) cudaEventDestroy(c->u16Done);
   if (c->copyDone) cudaEventDestroy(c->copyDone);
   if (c->forkEv) cudaEventDestroy(c->forkEv);
   for (int q = 0; q < vslamb200_ctx::kMaxParts; q++) {
@@ -511,6 +522,7 @@ int vslamb200_synchronize(vslamb200_ctx * c)
   if (!c) return fail(VSLAMB200_EINVAL, "ctx is null");
   CK(cudaSetDevice(c->device));
   CK(cudaStreamSynchronize(c->copyStream));
+  CK(cudaStreamSynchronize(c->prepStream));
   CK(cudaStreamSynchronize(c->stream));
   return 0;
 }
@@ -580,12 +592,15 @@ int vslamb200_frames_upload_async(
   CK(cudaMemcpy2DAsync(f0.I[0], frameStride, gray, grayStride, npx, n, cudaMemcpyHostToDevice, c->copyStream));
   CK(cudaMemcpy2DAsync(f0.Z[0], frameStride, depth, depthStride, npx * 4, n, cudaMemcpyHostToDevice, c->copyStream));
   c->stats.h2d_bytes += (uint64_t)n * npx * 5;
-  // pyramids and gradients follow the copies on the copy stream, so the compute stream is not held up by an upload
-  // it does not depend on; whoever reads these frames first waits for the arena's event
-  if (int e = preprocess(c, slots, nLevels, false, c->copyStream)) return e;
+  // pyramids and gradients run on the preparation stream behind the copies: neither the compute stream (which does not
+  // depend on this upload) nor the next transfer is held up by them; whoever reads these frames first waits for the
+  // arena's event
+  CK(cudaEventRecord(c->copyDone, c->copyStream));
+  CK(cudaStreamWaitEvent(c->prepStream, c->copyDone, 0));
+  if (int e = preprocess(c, slots, nLevels, false, c->prepStream)) return e;
   Arena & a = c->arenas[c->frames[slots[0]].arena];
   if (!a.ready) CK(cudaEventCreateWithFlags(&a.ready, cudaEventDisableTiming));
-  CK(cudaEventRecord(a.ready, c->copyStream));
+  CK(cudaEventRecord(a.ready, c->prepStream));
   a.pending = true;
   return 0;
 }
@@ -602,21 +617,27 @@ int vslamb200_frames_upload_u16_async(
   const size_t npx = (size_t)W * H;
   const vb::FrameDev & f0 = c->frames[slots[0]].dev;
   const size_t frameStride = n > 1 ? (size_t)((uint8_t *)c->frames[slots[1]].dev.I[0] - (uint8_t *)f0.I[0]) : npx * 4;
-  // the 16-bit planes land in a staging buffer of the context (grown once; the copy stream orders its reuse), the grey
-  // planes go straight into the frames; conversion, pyramids and gradients follow on the copy stream
+  // the 16-bit planes land in a staging buffer of the context (grown once), the grey planes go straight into the frames;
+  // conversion, pyramids and gradients run on the preparation stream behind the copies, so the next upload's transfer
+  // starts as soon as this one's ends (the staging buffer is free again once the conversion kernel has run: u16Done)
   if (npx * 2 * (size_t)n > c->stageU16.cap) {
     CK(cudaStreamSynchronize(c->copyStream));
+    CK(cudaStreamSynchronize(c->prepStream));
     CK(c->stageU16.ensure(npx * 2 * (size_t)n));
   }
   CK(cudaEventRecord(c->computeMark, c->stream));
   CK(cudaStreamWaitEvent(c->copyStream, c->computeMark, 0));
   CK(cudaMemcpy2DAsync(f0.I[0], frameStride, gray, npx, npx, n, cudaMemcpyHostToDevice, c->copyStream));
+  if (c->u16Pending) CK(cudaStreamWaitEvent(c->copyStream, c->u16Done, 0));
   CK(cudaMemcpyAsync(c->stageU16.p, depth, npx * 2 * (size_t)n, cudaMemcpyHostToDevice, c->copyStream));
   c->stats.h2d_bytes += (uint64_t)n * npx * 3;
-  if (int e = preprocess(c, slots, nLevels, false, c->copyStream, c->stageU16.as<uint16_t>(), depthDivisor)) return e;
+  CK(cudaEventRecord(c->copyDone, c->copyStream));
+  CK(cudaStreamWaitEvent(c->prepStream, c->copyDone, 0));
+  if (int e = preprocess(c, slots, nLevels, false, c->prepStream, c->stageU16.as<uint16_t>(), depthDivisor, c->u16Done)) return e;
+  c->u16Pending = true;
   Arena & a = c->arenas[c->frames[slots[0]].arena];
   if (!a.ready) CK(cudaEventCreateWithFlags(&a.ready, cudaEventDisableTiming));
-  CK(cudaEventRecord(a.ready, c->copyStream));
+  CK(cudaEventRecord(a.ready, c->prepStream));
   a.pending = true;
   return 0;
 }
@@ -690,6 +711,7 @@ int vslamb200_frame_release(vslamb200_ctx * c, uint64_t id)
   if (it == c->idToSlot.end()) return fail(VSLAMB200_ENOFRAME, "frame_release: unknown frame id");
   CK(cudaSetDevice(c->device));
   CK(cudaStreamSynchronize(c->copyStream));
+  CK(cudaStreamSynchronize(c->prepStream));
   CK(cudaStreamSynchronize(c->stream));
   return release_slot(c, it->second);
 }
@@ -699,6 +721,7 @@ int vslamb200_frame_release_all(vslamb200_ctx * c)
   if (!c) return fail(VSLAMB200_EINVAL, "ctx is null");
   CK(cudaSetDevice(c->device));
   CK(cudaStreamSynchronize(c->copyStream));
+  CK(cudaStreamSynchronize(c->prepStream));
   CK(cudaStreamSynchronize(c->stream));
   for (size_t i = 0; i < c->frames.size(); i++) release_slot(c, (int)i);
   trim_spares(c, 0);
