@@ -170,6 +170,68 @@ def result_poses(capi, results, n):
     return raw[:n, :56].copy().view(np.float64).reshape(n, 7)
 
 
+def odometry_leg(capi, synth, shard, cam, n_frames=150):
+    """The shape of the reference's OWN caller (odometry/src/Odometry.cpp:21-62, NodeRgbdAlignment.cpp:121-150): frames
+    arrive one at a time from host memory, each is aligned - motion prior on, starting from the constant-velocity
+    prediction - against {last key frame, last frame} stacked (or the last frame alone when it is the key frame), key
+    frame every second frame (KeyFrameSelectionIdx).  Sequential by construction, so this is a latency figure: frames/s
+    of the loop and p50 / p95 from "frame in host memory" to "pose on the host" (upload, pyramids, gradients, alignment)."""
+    import torch
+    gray, depth, gt = synth.make_sequence(n_frames, W, H, seed=1234, cam=cam)
+    k16 = np.clip(np.rint(depth.astype(np.float64) * DEPTH_DIVISOR), 0, 65535).astype(np.uint16)
+    hg, hk = torch.from_numpy(gray).pin_memory(), torch.from_numpy(k16.view(np.int16)).pin_memory()
+    ctx = capi.Context(capi.make_config(include_prior=True))
+    cams = np.array(cam, np.float64).reshape(1, 4)
+    npx = W * H
+
+    def inv(p):
+        q = p[:4] * np.array([-1.0, -1.0, -1.0, 1.0])
+        return np.concatenate([q, -shard.quat_rot(q, p[4:])])
+
+    poses, lat, steps = [IDENT7.copy()], [], 0
+    last_kf, res1 = 0, (capi.Result * 1)()
+    ctx.upload_u16_async(np.array([0], np.uint64), hg.data_ptr(), hk.data_ptr(), DEPTH_DIVISOR, 1, W, H, cams, LEVELS)
+    ctx.synchronize()
+    t_start = time.perf_counter()
+    for t in range(1, n_frames):
+        t0 = time.perf_counter()
+        ctx.upload_u16_async(np.array([t], np.uint64), hg.data_ptr() + t * npx, hk.data_ptr() + 2 * t * npx, DEPTH_DIVISOR, 1, W, H,
+                             cams, LEVELS)
+        # constant velocity over equal time steps: exp(log(p_k p_{k-1}^-1)) p_k (MotionPrediction.cpp:38-55)
+        guess = poses[-1] if t < 2 else shard.pose_mul(shard.pose_mul(poses[-1], inv(poses[-2])), poses[-1])
+        frm = [last_kf, t - 1] if last_kf != t - 1 else [t - 1]
+        job = (capi.Job * 1)()
+        ids = np.array(frm, np.uint64)
+        fp = np.ascontiguousarray(np.stack([poses[k] for k in frm]))
+        job[0].to = t
+        job[0].to_pose = (C.c_double * 7)(*guess)
+        job[0].n_from = len(frm)
+        job[0].multi = int(len(frm) > 1)
+        job[0].from_ = ids.ctypes.data_as(C.POINTER(C.c_uint64))
+        job[0].from_poses = fp.ctypes.data_as(C.POINTER(C.c_double))
+        ctx.align_raw(job, 1, res1)
+        poses.append(np.array(list(res1[0].pose)))
+        steps += sum(res1[0].iters[:LEVELS])
+        lat.append((time.perf_counter() - t0) * 1e3)
+        if t % 2 == 0:
+            last_kf = t
+        if t >= 16:
+            ctx.release(t - 16)  # out of the reference's rings of 7 frames / 7 key frames
+    total = time.perf_counter() - t_start
+    ctx.close()
+    traj = np.array(poses)
+    # frame-to-frame translation error against the rendered motion (P_frame = pose * P_world)
+    rel = [shard.pose_mul(traj[k + 1], inv(traj[k])) for k in range(n_frames - 1)]
+    rel_gt = [shard.pose_mul(gt[k + 1], inv(gt[k])) for k in range(n_frames - 1)]
+    err = np.array([np.linalg.norm(shard.pose_mul(a, inv(b))[4:]) for a, b in zip(rel, rel_gt)])
+    return {"frames_per_s": (n_frames - 1) / total, "p50_ms": float(np.percentile(lat, 50)), "p95_ms": float(np.percentile(lat, 95)),
+            "frames": n_frames - 1, "mean_gn_iterations_per_frame": steps / (n_frames - 1),
+            "rpe_translation_rmse_per_frame": float(np.sqrt(np.mean(err ** 2))),
+            "what": "sequential odometry-shaped loop: one 640x480 frame (u8 + u16) from pinned host memory per step, stacked "
+                    "alignment against {last key frame, last frame} with the motion prior, constant-velocity start, key frame "
+                    "every 2nd frame; wall time per frame from host memory to the pose on the host"}
+
+
 def cpu_leg(n_pairs, threads, gray, depth, cam, stride):
     """Times the CPU oracle (frame preparation + alignment) on the first n_pairs pairs of the frame array."""
     from oracle import oracle as O
@@ -501,6 +563,7 @@ def main():
         # give the same poses); every pair is within 0.02.
         assert np.median(errs) < 0.01 and (errs < 0.02).mean() > 0.99, checks
 
+    odo = odometry_leg(capi, synth, shard, cam) if rank == 0 and args.workload == "pairs" else None
     cpu = None
     if rank == 0 and not args.no_cpu:
         from oracle import oracle as O
@@ -546,7 +609,7 @@ def main():
                                 f"a step travels in {chunks} sub-batches, the transfer of a sub-batch (copy stream) overlaps the "
                                 "alignment of the one before it; all uploads timed; bytes are per GPU"},
             "gpu_launches": int(st["kernel_launches"]),
-            "latency": lat, "clocks": clocks, "ranks": ranks, "roofline": roofline, "cpu_baseline": cpu, "checks": checks,
+            "latency": lat, "odometry_shaped": odo, "clocks": clocks, "ranks": ranks, "roofline": roofline, "cpu_baseline": cpu, "checks": checks,
         }))
     ctx.close()
     if use_dist:
