@@ -38,8 +38,8 @@ ALGORITHM_FUNCTIONS = [  # signatures inside namespace pd::vslam::algorithm of c
     r"double median\(const Eigen::VectorXd & d, bool isSorted\)",
     r"double median\(std::vector<double> & v, bool isSorted\)",
 ]
-INCLUDES = ["core/src", "least_squares/src", "least_squares/include", "lukas_kanade/src",
-            "odometry/src/direct_image_alignment", "odometry/src"]
+INCLUDES = ["core/src", "core/include", "least_squares/src", "least_squares/include", "lukas_kanade/src",
+            "lukas_kanade/include", "odometry/src/direct_image_alignment", "odometry/src"]
 # -DNDEBUG: the reference's Dockerfile builds Release; -ffp-contract=off: no fused multiply-adds, like the oracle
 CXXFLAGS = ["-std=c++17", "-O2", "-DNDEBUG", "-fPIC", "-ffp-contract=off", "-fno-fast-math", "-w"]
 
