@@ -905,10 +905,13 @@ bool use_moments(const vslamb200_config & cfg, const Problem & P, const vb::Solv
 int pick_cpv(const vslamb200_config & cfg, int npx, int nJobs, int K)
 {
   int c = npx > 160000 ? 4 : npx > 40000 ? 2 : 1;
-  if (nJobs <= 8) c = npx > 12000 ? 16 : npx > 3000 ? 8 : 4;
+  // few jobs: as long as 16-CTA clusters (the non-portable maximum) for all of them fit on the device at once (two
+  // 256-thread CTAs per SM), a job spreads over 16 CTAs - 16 alignments against 8 key frames are 128 CTAs otherwise
+  const bool few = nJobs <= 8 || nJobs * 16 <= 2 * 148;
+  if (few) c = npx > 12000 ? 16 : npx > 3000 ? 8 : 4;
   const int o = cfg.cluster_size;
   if (o == 1 || o == 2 || o == 4 || o == 8 || o == 16) c = o;
-  const int cap = nJobs <= 8 ? 16 : 8;
+  const int cap = few ? 16 : 8;
   while (c > 1 && c * K > cap) c >>= 1;
   return c;
 }
