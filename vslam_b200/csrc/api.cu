@@ -879,7 +879,8 @@ int pick_cluster(const vslamb200_config & cfg, int npx, int nJobs)
   // span (16 CTAs is the non-portable cluster maximum of sm_100; the launcher opts in).  Measured on one 640x480
   // pair, 4 levels: 3.43 ms with the throughput sizes 8/4/2/1, 2.88 ms with 8 everywhere, 2.13 ms with 16 everywhere.
   // Throughput batches keep the smaller clusters: there the per-CTA work amortises the serial sections better.
-  if (nJobs <= 8) c = npx > 12000 ? 16 : npx > 3000 ? 8 : 4;
+  // (the same for any batch whose 16-CTA clusters all fit on the device at once: four 128-thread CTAs per SM)
+  if (nJobs <= 8 || nJobs * 16 <= 4 * 148) c = npx > 12000 ? 16 : npx > 3000 ? 8 : 4;
   // Small batches (what one GPU of a strong-scaling run gets): a launch ends with its slowest job, whose Gauss-Newton steps
   // run one after the other, so the middle levels take clusters twice as large.  Measured on 512 pairs: level 1 4.7 ms
   // instead of 6.3 ms, level 2 1.9 instead of 2.2; on 2048 pairs and more the smaller clusters win (10.4 against 12.1 ms).
