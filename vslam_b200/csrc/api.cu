@@ -881,6 +881,9 @@ int pick_cluster(const vslamb200_config & cfg, int npx, int nJobs)
   // Throughput batches keep the smaller clusters: there the per-CTA work amortises the serial sections better.
   // (the same for any batch whose 16-CTA clusters all fit on the device at once: four 128-thread CTAs per SM)
   if (nJobs <= 8 || nJobs * 16 <= 4 * 148) c = npx > 12000 ? 16 : npx > 3000 ? 8 : 4;
+  // up to two such waves still gain on the two fine levels (64 pairs: 1.81 + 1.93 ms instead of 2.14 + 2.44 ms; the coarse
+  // levels and 128 pairs lose)
+  else if (nJobs * 16 <= 8 * 148 && npx > 40000) c = 16;
   // Small batches (what one GPU of a strong-scaling run gets): a launch ends with its slowest job, whose Gauss-Newton steps
   // run one after the other, so the middle levels take clusters twice as large.  Measured on 512 pairs: level 1 4.7 ms
   // instead of 6.3 ms, level 2 1.9 instead of 2.2; on 2048 pairs and more the smaller clusters win (10.4 against 12.1 ms).
