@@ -225,3 +225,20 @@ def test_f32_depth_storage_against_the_reference(oracle, ref, synth):
     for l in range(L):
         assert np.array_equal(o["trace"][l, : o["iters"][l], 1], r["trace"][l, : r["pushed"][l], 1])   # same point counts
     assert np.abs(oracle.se3_log(o["pose"]) - r["twist"]).max() < 1e-6
+
+
+def test_bench_workload_pairs_follow_the_reference(oracle, ref, synth):
+    """Two pairs of bench.py's default workload (BASELINE configs[2]: 640x480, 4 levels, 16-bit depth / 5000, the bench's
+    start guess, t-distribution weights, chi2 of the Release build) through the oracle's batch helper - what bench.py times
+    on the CPU and checks the GPU against - and through the reference build."""
+    import bench
+    cam = synth.cam_for(bench.W, bench.H)
+    gray, depth, _ = bench.render_pairs(synth, range(2), cam)
+    depth = bench.quantise_depth(depth)
+    cfg = oracle.make_config()
+    poses, iters = oracle.baseline_batch(cfg, gray, depth, *cam, bench.LEVELS, 2, stride=2, n_pairs=2, start=bench.start_pose7())
+    for k in range(2):
+        r = ref.align(ref.config_from(cfg), gray[2 * k: 2 * k + 2], depth[2 * k: 2 * k + 2].astype(np.float64), np.array(cam, float),
+                      np.stack([np.zeros(6), bench.START_TWIST]), bench.LEVELS, want_trace=False)
+        assert r["pushed"].tolist() == iters[k].tolist()
+        assert np.allclose(oracle.se3_log(poses[k]), r["twist"], rtol=0, atol=1e-12)
