@@ -242,3 +242,12 @@ def test_bench_workload_pairs_follow_the_reference(oracle, ref, synth):
                       np.stack([np.zeros(6), bench.START_TWIST]), bench.LEVELS, want_trace=False)
         assert r["pushed"].tolist() == iters[k].tolist()
         assert np.allclose(oracle.se3_log(poses[k]), r["twist"], rtol=0, atol=1e-12)
+
+
+def test_kitti_shape_five_levels_follows_the_reference(oracle, ref, synth):
+    """BASELINE configs[3]'s shape: 1232 x 368, five pyramid levels (77 x 23 at the coarsest)."""
+    p = synth.make_pair(1232, 368, 77)
+    gray = np.stack([p["gray0"], p["gray1"]])
+    depth = _punch(np.stack([p["depth0"], p["depth1"]]).astype(np.float64))
+    o, r = _run_both(oracle, ref, gray, depth, np.array(p["cam"], float), 5, max_iterations=30)
+    _assert_same_run(oracle, o, r, 5)
