@@ -875,6 +875,10 @@ int pick_cluster(const vslamb200_config & cfg, int npx, int nJobs)
   const int o = cfg.cluster_size;  // tuning override
   if (o == 1 || o == 2 || o == 4 || o == 8 || o == 16) return o;
   int c = npx > 160000 ? 8 : npx > 40000 ? 4 : npx > 12000 ? 2 : 1;
+  // Large launches (many waves of clusters): half the size on the two fine levels - the serial sections of an evaluation
+  // cost CTA time in proportion to the cluster size.  Measured on 4096 pairs (two launches of 2048 jobs per level):
+  // level 0 49.4 ms with 4 CTAs against 50.6 with 8 (53.2 with 2), level 1 18.2 ms with 2 against 19.4-20.0 with 4.
+  if (nJobs >= 1024) c = npx > 160000 ? 4 : npx > 12000 ? 2 : 1;
   // Latency mode: a handful of jobs cannot fill the device, so each job spreads over as many SMs as a cluster can
   // span (16 CTAs is the non-portable cluster maximum of sm_100; the launcher opts in).  Measured on one 640x480
   // pair, 4 levels: 3.43 ms with the throughput sizes 8/4/2/1, 2.88 ms with 8 everywhere, 2.13 ms with 16 everywhere.
