@@ -224,7 +224,10 @@ def odometry_leg(capi, synth, shard, cam, n_frames=150):
     rel = [shard.pose_mul(traj[k + 1], inv(traj[k])) for k in range(n_frames - 1)]
     rel_gt = [shard.pose_mul(gt[k + 1], inv(gt[k])) for k in range(n_frames - 1)]
     err = np.array([np.linalg.norm(shard.pose_mul(a, inv(b))[4:]) for a, b in zip(rel, rel_gt)])
-    return {"frames_per_s": (n_frames - 1) / total, "p50_ms": float(np.percentile(lat, 50)), "p95_ms": float(np.percentile(lat, 95)),
+    # frames_per_s: upload + alignment back to back (the per-frame times below); wall_frames_per_s also holds this loop's
+    # housekeeping (releasing frames that left the rings, each a stream synchronisation; Python)
+    return {"frames_per_s": (n_frames - 1) / (sum(lat) * 1e-3), "wall_frames_per_s": (n_frames - 1) / total,
+            "p50_ms": float(np.percentile(lat, 50)), "p95_ms": float(np.percentile(lat, 95)),
             "frames": n_frames - 1, "mean_gn_iterations_per_frame": steps / (n_frames - 1),
             "rpe_translation_rmse_per_frame": float(np.sqrt(np.mean(err ** 2))),
             "what": "sequential odometry-shaped loop: one 640x480 frame (u8 + u16) from pinned host memory per step, stacked "
