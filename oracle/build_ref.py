@@ -8,8 +8,9 @@ Compiled UNCHANGED, straight from the reference tree:
   core/src           Camera.cpp PoseWithCovariance.cpp Frame.cpp Feature2D.cpp Point3D.cpp
   lukas_kanade/src   Warp.cpp InverseCompositional.cpp InverseCompositionalStacked.cpp
   odometry/src/direct_image_alignment  SE3Alignment.cpp
+  odometry/src       Odometry.cpp MotionPrediction.cpp KeyFrameSelection.cpp mapping/Map.cpp   (the aligner's caller)
 core/src/algorithm.cpp also holds eigenvalue / quaternion helpers that need Eigen modules the stand-in does not have, so
-only the four functions the path calls (median x2, resize x2) are cut out of it, by signature, into a temporary file
+only the five functions the path calls (median x2, resize x2, computeRelativeTransform) are cut out of it, by signature, into a temporary file
 that is compiled and deleted: no reference source is ever written into the repository.
 
 The GPU box has no /root/reference: there the prebuilt .so (git-ignored, not gpurun-ignored) is used as it is.
@@ -31,15 +32,19 @@ UNCHANGED = [
     "core/src/Feature2D.cpp", "core/src/Point3D.cpp", "lukas_kanade/src/Warp.cpp",
     "lukas_kanade/src/InverseCompositional.cpp", "lukas_kanade/src/InverseCompositionalStacked.cpp",
     "odometry/src/direct_image_alignment/SE3Alignment.cpp",
+    # the aligner's direct caller: odometry update, motion prediction, key-frame selection, map rings
+    "odometry/src/Odometry.cpp", "odometry/src/MotionPrediction.cpp", "odometry/src/KeyFrameSelection.cpp",
+    "odometry/src/mapping/Map.cpp",
 ]
 ALGORITHM_FUNCTIONS = [  # signatures inside namespace pd::vslam::algorithm of core/src/algorithm.cpp
     r"Image resize\(const Image & mat, double scale\)",
     r"Eigen::MatrixXd resize\(const Eigen::MatrixXd & mat, double scale\)",
     r"double median\(const Eigen::VectorXd & d, bool isSorted\)",
     r"double median\(std::vector<double> & v, bool isSorted\)",
+    r"Sophus::SE3d computeRelativeTransform\(const Sophus::SE3d & t0, const Sophus::SE3d & t1\)",
 ]
 INCLUDES = ["core/src", "core/include", "least_squares/src", "least_squares/include", "lukas_kanade/src",
-            "lukas_kanade/include", "odometry/src/direct_image_alignment", "odometry/src"]
+            "lukas_kanade/include", "odometry/src/direct_image_alignment", "odometry/src", "kalman/include", "kalman/src"]
 # -DNDEBUG: the reference's Dockerfile builds Release; -ffp-contract=off: no fused multiply-adds, like the oracle
 CXXFLAGS = ["-std=c++17", "-O2", "-DNDEBUG", "-fPIC", "-ffp-contract=off", "-fno-fast-math", "-w"]
 

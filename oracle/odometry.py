@@ -10,8 +10,9 @@ Follows, relative to /root/reference/src/:
   vslam/src/odometry/src/mapping/Map.cpp:19-33  rings of at most 7 frames / 7 key frames, newest first
   vslam/src/odometry/src/KeyFrameSelection.h:36-51  KeyFrameSelectionIdx: counter, key frame iff ctr % period == 0
   vslam/src/odometry/src/MotionPrediction.cpp:38-55, MotionPrediction.h:41-76  NoMotion / ConstantMotion
-The alignment itself is oracle.align (vslam_oracle.cpp).  Parity: unpinned (the reference ships no golden
-trajectory for this loop and cannot be built here); the GPU host mirror is compared with this restatement.
+The alignment itself is oracle.align (vslam_oracle.cpp).  Parity: pinned - tests/test_oracle_ref_cpu.py runs this loop
+against the reference's own Odometry.cpp / MotionPrediction.cpp / KeyFrameSelection.cpp / Map.cpp (oracle/_ref, compiled
+unchanged against the stand-in headers); the GPU host mirror is compared with this restatement.
 """
 import numpy as np
 

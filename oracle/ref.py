@@ -50,6 +50,8 @@ def lib():
         _lib.ref_align.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int] + [C.c_void_p] * 4 + [C.c_int, C.c_int] + \
             [C.c_void_p] * 6 + [C.c_char_p, C.c_int]
         _lib.ref_frame_level.argtypes = [C.c_int, C.c_int] + [C.c_void_p] * 3 + [C.c_int, C.c_int] + [C.c_void_p] * 7
+        _lib.ref_odometry.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int] + [C.c_void_p] * 4 + [C.c_int] * 3 + \
+            [C.c_void_p] * 2 + [C.c_char_p, C.c_int]
     return _lib
 
 
@@ -110,3 +112,21 @@ def frame_level(gray, depth, cam4, n_levels, level):
     if st != 0:
         raise RuntimeError("reference frame: failed")
     return dict(I=I, Z=Z, dIx=dIx, dIy=dIy, pcl=pcl, cam=cam)
+
+
+def odometry(cfg, gray, depth, cam4, stamps_ns, n_levels, motion_model="ConstantMotion", kf_period=2):
+    """The reference's OdometryRgbd + MotionPrediction + KeyFrameSelectionIdx + Map over a frame sequence, in the order of
+    the ROS node's processFrame.  gray (F, H, W) u8, depth (F, H, W) f64, stamps in nanoseconds.
+    -> poses (F, 6) and speeds (F, 6) as twists (speed per second)."""
+    gray = np.ascontiguousarray(gray, np.uint8)
+    depth = np.ascontiguousarray(depth, np.float64)
+    cam4 = np.ascontiguousarray(cam4, np.float64)
+    stamps = np.ascontiguousarray(stamps_ns, np.uint64)
+    F, H, W = gray.shape
+    poses, speeds = np.empty((F, 6)), np.empty((F, 6))
+    err = C.create_string_buffer(512)
+    st = lib().ref_odometry(C.byref(cfg), F, W, H, _p(gray), _p(depth), _p(cam4), _p(stamps), n_levels,
+                            int(motion_model == "ConstantMotion"), kf_period, _p(poses), _p(speeds), err, 512)
+    if st != 0:
+        raise RuntimeError("reference odometry: " + err.value.decode())
+    return poses, speeds

@@ -11,6 +11,9 @@
 #include <memory>
 #include <vector>
 
+#include "KeyFrameSelection.h"
+#include "MotionPrediction.h"
+#include "Odometry.h"
 #include "SE3Alignment.h"
 #include "core/core.h"
 #include "least_squares/least_squares.h"
@@ -25,6 +28,27 @@ namespace pd::vslam::algorithm
 Eigen::MatrixXi gradX(const Image &) { throw pd::Exception("ref_harness: algorithm::gradX is not built"); }
 Eigen::MatrixXi gradY(const Image &) { throw pd::Exception("ref_harness: algorithm::gradY is not built"); }
 }  // namespace pd::vslam::algorithm
+
+// Declared by headers the odometry sources include, never run here: the Kalman motion model (kalman/src needs more of
+// Eigen than the stand-in has) and the PCL-based ICP aligner.  Odometry.cpp / MotionPrediction.cpp reference them.
+namespace pd::vslam::kalman
+{
+EKFConstantVelocitySE3::State::UnPtr EKFConstantVelocitySE3::predict(Timestamp) const
+{
+  throw pd::Exception("ref_harness: the Kalman motion model is not built");
+}
+void EKFConstantVelocitySE3::update(const Vec6d &, const Matd<6, 6> &, Timestamp)
+{
+  throw pd::Exception("ref_harness: the Kalman motion model is not built");
+}
+}  // namespace pd::vslam::kalman
+namespace pd::vslam
+{
+PoseWithCovariance::UnPtr IterativeClosestPoint::align(Frame::ConstShPtr, Frame::ConstShPtr) const
+{
+  throw pd::Exception("ref_harness: the ICP aligner is not built");
+}
+}  // namespace pd::vslam
 
 namespace
 {
@@ -201,6 +225,61 @@ int ref_frame_level(
     camOut4[3] = f->camera(level)->principalPoint().y();
     return 0;
   } catch (const std::exception &) {
+    return -1;
+  }
+}
+
+// The aligner's direct caller, SURVEY.md 8(f)-2: the reference's OdometryRgbd (Odometry.cpp:21-62), MotionPrediction
+// (MotionPrediction.cpp:22-55), KeyFrameSelectionIdx (KeyFrameSelection.h:36-51) and Map (Map.cpp:19-33), driven in the
+// order of the ROS node's processFrame (src/ros/nodes/NodeRgbdAlignment.cpp:121-150 - the node itself is ROS and cannot
+// be built; these six calls are its loop body).  motionModel: 0 NoMotion, 1 ConstantMotion.  stamps in nanoseconds.
+// Out: per frame the pose (twist) the frame ends up with and the speed (twist per second).
+int ref_odometry(
+  const ref_config * c, int nFrames, int W, int H, const uint8_t * gray, const double * depth, const double * cam4,
+  const uint64_t * stamps, int nLevels, int motionModel, int kfPeriod, double * poses6, double * speeds6, char * err, int errLen)
+{
+  try {
+    auto solver = std::make_shared<ls::GaussNewton>(c->min_step_size, (size_t)c->max_iterations);
+    auto loss = make_loss(c->loss_kind, c->huber_c, c->loss_v, make_scaler(c->scaler_kind, c->scaler_v));
+    auto map = std::make_shared<Map>();
+    auto odometry = std::make_shared<OdometryRgbd>(c->min_gradient, solver, loss, map);
+    MotionPrediction::ShPtr prediction = MotionPrediction::make(motionModel ? "ConstantMotion" : "NoMotion");
+    auto keyFrameSelection = std::make_shared<KeyFrameSelectionIdx>((uint64_t)kfPeriod);
+    const size_t npx = (size_t)W * H;
+    const double zero[6] = {0, 0, 0, 0, 0, 0};
+    for (int i = 0; i < nFrames; i++) {
+      Image I(H, W);
+      DepthMap Z(H, W);
+      for (int v = 0; v < H; v++)
+        for (int u = 0; u < W; u++) {
+          I(v, u) = gray[i * npx + (size_t)v * W + u];
+          Z(v, u) = depth[i * npx + (size_t)v * W + u];
+        }
+      Vec6d x0;
+      for (int k = 0; k < 6; k++) x0(k) = zero[k];
+      auto cam = std::make_shared<Camera>(cam4[0], cam4[1], cam4[2], cam4[3]);
+      auto frame = std::make_shared<Frame>(I, Z, cam, stamps[i], PoseWithCovariance(x0));
+      frame->computePyramid((size_t)nLevels);  // createFrame (NodeRgbdAlignment.cpp:194-197)
+      frame->computeDerivatives();
+      frame->computePcl();
+      frame->set(*prediction->predict(frame->t()));
+      odometry->update(frame);
+      frame->set(*odometry->pose());
+      prediction->update(odometry->pose(), frame->t());
+      keyFrameSelection->update(frame);
+      map->insert(frame, keyFrameSelection->isKeyFrame());
+      const Vec6d p = odometry->pose()->pose().log(), s = odometry->speed()->pose().log();
+      for (int k = 0; k < 6; k++) {
+        poses6[6 * i + k] = p(k);
+        speeds6[6 * i + k] = s(k);
+      }
+    }
+    return 0;
+  } catch (const std::exception & e) {
+    if (err && errLen > 0) {
+      std::strncpy(err, e.what(), (size_t)errLen - 1);
+      err[errLen - 1] = 0;
+    }
     return -1;
   }
 }

@@ -22,6 +22,7 @@ struct NullLog
 }  // namespace ref_shim
 
 #define CLOG(level, name) ::ref_shim::NullLog()
+#define LOG(level) ::ref_shim::NullLog()
 #define SYSTEM(loglevel) CLOG(loglevel, "system")
 #define IMAGE_ALIGNMENT(loglevel) CLOG(loglevel, "image_alignment")
 #define SOLVER(loglevel) CLOG(loglevel, "solver")

@@ -251,3 +251,31 @@ def test_kitti_shape_five_levels_follows_the_reference(oracle, ref, synth):
     depth = _punch(np.stack([p["depth0"], p["depth1"]]).astype(np.float64))
     o, r = _run_both(oracle, ref, gray, depth, np.array(p["cam"], float), 5, max_iterations=30)
     _assert_same_run(oracle, o, r, 5)
+
+
+@pytest.mark.parametrize("model,period", [("ConstantMotion", 2), ("NoMotion", 3)])
+def test_odometry_loop_follows_the_reference(oracle, ref, synth, model, period):
+    """SURVEY.md 8(f)-2, the aligner's caller: the reference's own OdometryRgbd (Odometry.cpp:21-62: prior always on, stacked
+    alignment against {last key frame, last frame} when they differ), MotionPrediction (MotionPrediction.cpp:22-55),
+    KeyFrameSelectionIdx and Map, driven like the node's processFrame, against oracle/odometry.py - the restatement the
+    GPU host mirror (include/vslam_b200_odometry.hpp) is tested against.  The first alignment of the loop starts at the exact
+    identity, where the visibility of border pixels is a matter of rounding order (see the header of this file), so the
+    frames carry a blank border that keeps every interest point away from it."""
+    from oracle import odometry as OD
+    F, W, H, L = 7, 320, 240, 3
+    cam = synth.cam_for(W, H)
+    gray, depth, _ = synth.make_sequence(F, W, H, seed=4242, cam=cam)
+    gray = gray.copy()
+    gray[:, :40] = gray[:, -40:] = 90
+    gray[:, :, :40] = gray[:, :, -40:] = 90
+    depth = depth.astype(np.float64)
+    stamps = (1305031100.0e9 + np.arange(F) * 1e9 / 30.0).astype(np.uint64)
+    cfg = oracle.make_config(f32_storage=False, max_iterations=30, include_prior=True)
+    frames = [oracle.Frame(gray[i], depth[i], *cam, L, f32_storage=False) for i in range(F)]
+    poses, speeds, kinds = OD.run(cfg, frames, stamps, prediction=model, kf_period=period)
+    assert "stacked" in kinds and "single" in kinds
+    rposes, rspeeds = ref.odometry(ref.config_from(cfg), gray, depth, np.array(cam, float), stamps, L, model, period)
+    for i in range(F):
+        assert np.allclose(oracle.se3_log(poses[i]), rposes[i], rtol=0, atol=1e-11), i
+        assert np.allclose(speeds[i], rspeeds[i], rtol=0, atol=1e-9), i
+    assert np.abs(rposes[-1]).max() > 1e-3                                 # the sequence moves
