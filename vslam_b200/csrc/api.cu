@@ -877,7 +877,8 @@ int pick_cluster(const vslamb200_config & cfg, int npx, int nJobs)
   int c = npx > 160000 ? 8 : npx > 40000 ? 4 : npx > 12000 ? 2 : 1;
   // Large launches (many waves of clusters): half the size on the two fine levels - the serial sections of an evaluation
   // cost CTA time in proportion to the cluster size.  Measured on 4096 pairs (two launches of 2048 jobs per level):
-  // level 0 49.4 ms with 4 CTAs against 50.6 with 8 (53.2 with 2), level 1 18.2 ms with 2 against 19.4-20.0 with 4.
+  // level 0 49.4 ms with 4 CTAs against 50.6 with 8 (53.2 with 2, 67.7 with 1), level 1 18.2 ms with 2 against 19.4-20.0
+  // with 4 (21.0 with 1), level 2 4.9 ms with 2 against 5.3 with 1 and 6.3 with 4.
   if (nJobs >= 1024) c = npx > 160000 ? 4 : npx > 12000 ? 2 : 1;
   // Latency mode: a handful of jobs cannot fill the device, so each job spreads over as many SMs as a cluster can
   // span (16 CTAs is the non-portable cluster maximum of sm_100; the launcher opts in).  Measured on one 640x480
